@@ -1,0 +1,71 @@
+"""ctypes binding of libencdiff_b200.so (include/encdiff_b200.h).
+
+There is no CPU fallback: if the library cannot be loaded, every entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+from . import _build
+
+_lib = None
+
+c_void_p, c_int, c_ll, c_float_p = C.c_void_p, C.c_int, C.c_longlong, C.c_void_p
+
+# name -> (restype, argtypes).  Kept in sync with include/encdiff_b200.h; tests/test_abi.py checks that every
+# symbol the header declares is exported and listed here.
+PROTOTYPES = {
+    "encdiff_last_error": (C.c_char_p, []),
+    "encdiff_op_sgemm": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int), c_int, c_int, c_int,
+                                 c_void_p, c_ll, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
+                                 c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "encdiff_op_wgrad": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_ll,
+                                 c_ll, c_int, c_int, c_int, c_void_p]),
+}
+
+
+def lib_path() -> Path:
+    return _build.LIB_PATH
+
+
+def load(build_if_missing: bool = True):
+    """Load (building first if the sources changed and nvcc is available) and return the ctypes library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if build_if_missing and os.environ.get("ENCDIFF_B200_NO_BUILD") != "1":
+        try:
+            _build.build()
+        except Exception as e:  # a stale-but-present library on a box without nvcc is still usable
+            if not path.exists():
+                raise RuntimeError(f"encdiff_b200: cannot build the CUDA library and none is present: {e}") from e
+    if not path.exists():
+        raise RuntimeError(
+            f"encdiff_b200: {path} is missing. Run `python -c 'import __graft_entry__ as g; g.build()'`; "
+            "this package has no CPU fallback.")
+    lib = C.CDLL(str(path))
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported: loud by design
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str = "") -> None:
+    if status != 0:
+        msg = load().encdiff_last_error().decode(errors="replace")
+        raise RuntimeError(f"encdiff_b200 {what} failed (status {status}): {msg}")
+
+
+def ptr(t) -> int:
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return 0 if t is None else t.data_ptr()
+
+
+def current_stream() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream

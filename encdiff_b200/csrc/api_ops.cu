@@ -1,0 +1,77 @@
+// C-ABI, operator level: the two tensor-core GEMM families exposed with raw pointers so that each can be checked
+// against the reference nn.Conv2d / nn.Linear call sites on its own (tests/test_gemm_gpu.py).
+#include "../../include/encdiff_b200.h"
+#include <string.h>
+
+#include "gemm.cuh"
+#include "host.cuh"
+
+using namespace edb;
+
+extern "C" const char* encdiff_last_error(void) { return last_error(); }
+
+extern "C" int encdiff_op_sgemm(int nsrc, const void* const* a_ptrs, const int* a_channels, const int* a_taps, int H,
+                                int W, int B, const void* w_packed, long long w_rows, int N, int tap_sign,
+                                const float* bias, const void* res, int ldres, int act, int out_fp32, void* out0,
+                                int ld0, int split_col, void* out1, int ld1, int bn, void* stream) {
+  EDB_REQUIRE(nsrc >= 1 && nsrc <= 3, "sgemm: 1..3 A sources");
+  SgemmParams p;
+  memset(&p, 0, sizeof(p));
+  EDB_REQUIRE(make_geom(H, W, &p.g), "sgemm: H*W must be a power of two with W <= 128");
+  long long K = 0;
+  for (int s = 0; s < nsrc; ++s) {
+    EDB_REQUIRE(a_taps[s] == 1 || a_taps[s] == 9, "sgemm: taps must be 1 or 9");
+    EDB_REQUIRE(a_channels[s] % 8 == 0, "sgemm: channels must be a multiple of 8");
+    int rc = make_act_tmap(&p.amap[s], a_ptrs[s], a_channels[s], H, W, B, p.g);
+    if (rc) return rc;
+    p.src_chunks[s] = (a_channels[s] + 63) / 64;
+    p.src_taps[s] = a_taps[s];
+    K += 64LL * p.src_chunks[s] * a_taps[s];
+  }
+  if (bn <= 0) bn = sgemm_pick_bn(N);
+  EDB_REQUIRE(w_rows >= ((N + bn - 1) / bn) * bn, "sgemm: packed weight rows must be padded to the N tile");
+  int rc = make_w_tmap(&p.bmap, w_packed, K, w_rows, bn);
+  if (rc) return rc;
+  p.nsrc = nsrc;
+  p.tap_sign = tap_sign;
+  p.M = B * H * W;
+  p.N = N;
+  p.bias = bias;
+  p.res = res;
+  p.ldres = ldres;
+  p.act = act;
+  p.out_fp32 = out_fp32;
+  p.out0 = out0;
+  p.ld0 = ld0;
+  p.split_col = out1 ? split_col : (1 << 30);
+  p.out1 = out1;
+  p.ld1 = ld1;
+  EDB_REQUIRE(!out1 || (split_col % 32) == 0, "sgemm: split_col must be a multiple of 32");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_sgemm(p, bn, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_op_wgrad(const void* dy, int Cp, const void* x, int Cq, int H, int W, int B, int taps,
+                                float* out, long long stride_p, long long stride_q, long long stride_tap, int q_off,
+                                int bn, int splits, void* stream) {
+  WgradParams p;
+  memset(&p, 0, sizeof(p));
+  EDB_REQUIRE(taps == 1 || taps == 9, "wgrad: taps must be 1 or 9");
+  EDB_REQUIRE(make_geom(H, W, &p.g), "wgrad: H*W must be a power of two with W <= 128");
+  int rc = make_act_tmap(&p.pmap, dy, Cp, H, W, B, p.g);
+  if (rc) return rc;
+  rc = make_act_tmap(&p.qmap, x, Cq, H, W, B, p.g);
+  if (rc) return rc;
+  p.taps = taps;
+  p.m_tiles = (B * H * W + 127) / 128;
+  p.Cp = Cp;
+  p.Cq = Cq;
+  p.out = out;
+  p.stride_p = stride_p;
+  p.stride_q = stride_q;
+  p.stride_tap = stride_tap;
+  p.q_off = q_off;
+  if (bn <= 0) bn = Cq <= 64 ? 64 : 128;
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_wgrad(p, bn, splits, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
