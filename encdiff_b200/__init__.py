@@ -1,2 +1,9 @@
-"""encdiff_b200 — B200-native (sm_100a) implementation of EncDiff's latent-diffusion denoising hot path."""
+"""encdiff_b200 — B200-native (sm_100a) implementation of EncDiff's latent-diffusion denoising hot path.
+
+Drop-in classes (select with ``target: encdiff_b200.UNetModel`` in the reference's unet_config):
+``UNetModel``, ``SpatialTransformer``, ``CrossAttention``, ``DDIMSampler``.
+"""
 __version__ = "0.1.0"
+
+from .modules import CrossAttention, SpatialTransformer  # noqa: F401
+from .unet import UNetModel  # noqa: F401

@@ -23,7 +23,34 @@ PROTOTYPES = {
                                  c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
     "encdiff_op_wgrad": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_ll,
                                  c_ll, c_int, c_int, c_int, c_void_p]),
+    "encdiff_unet_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
+    "encdiff_unet_destroy": (c_int, [c_void_p]),
+    "encdiff_unet_num_params": (c_int, [c_void_p]),
+    "encdiff_unet_param_info": (c_int, [c_void_p, c_int, C.c_char_p, c_int, C.POINTER(c_ll), C.POINTER(c_int)]),
+    "encdiff_unet_packed_bytes": (c_ll, [c_void_p]),
+    "encdiff_unet_workspace_bytes": (c_ll, [c_void_p, c_int, c_int]),
+    "encdiff_unet_bind": (c_int, [c_void_p, C.POINTER(c_void_p), C.POINTER(c_void_p), c_void_p, c_void_p]),
+    "encdiff_unet_pack_weights": (c_int, [c_void_p, c_void_p]),
+    "encdiff_unet_plan": (c_int, [c_void_p, c_int, c_void_p, c_int]),
+    "encdiff_unet_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p]),
+    "encdiff_unet_backward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "encdiff_l1_loss": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
+    "encdiff_ddim_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, C.c_float, c_void_p, c_void_p, c_ll,
+                                    c_void_p]),
+    "encdiff_timestep_embedding": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "encdiff_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, C.c_float, C.c_float,
+                                   C.c_float, C.c_float, C.c_float, c_int, C.c_float, c_void_p]),
 }
+
+
+class UNetConfigStruct(C.Structure):
+    """Mirror of ``encdiff_unet_config`` (include/encdiff_b200.h)."""
+    _fields_ = [("image_size", c_int), ("in_channels", c_int), ("model_channels", c_int), ("out_channels", c_int),
+                ("num_res_blocks", c_int), ("n_attention_resolutions", c_int), ("attention_resolutions", c_int * 8),
+                ("n_channel_mult", c_int), ("channel_mult", c_int * 8), ("num_heads", c_int), ("context_dim", c_int),
+                ("latent_unit", c_int), ("transformer_depth", c_int), ("use_scale_shift_norm", c_int),
+                ("resblock_updown", c_int)]
 
 
 def lib_path() -> Path:

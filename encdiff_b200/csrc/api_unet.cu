@@ -1,0 +1,148 @@
+// C-ABI, model level: the UNet denoiser handle and the diffusion glue kernels (see include/encdiff_b200.h).
+#include <string.h>
+
+#include <new>
+
+#include "host.cuh"
+#include "unet.cuh"
+
+using namespace edb;
+
+struct encdiff_unet {
+  UNet u;
+};
+
+extern "C" int encdiff_unet_create(const encdiff_unet_config* cfg, encdiff_unet** out) {
+  EDB_REQUIRE(cfg && out, "unet_create: null argument");
+  encdiff_unet* h = new (std::nothrow) encdiff_unet();
+  EDB_REQUIRE(h, "unet_create: out of host memory");
+  int rc = unet_build(&h->u, cfg);
+  if (rc) {
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return EDB_OK;
+}
+
+extern "C" int encdiff_unet_destroy(encdiff_unet* h) {
+  delete h;
+  return EDB_OK;
+}
+
+extern "C" int encdiff_unet_num_params(const encdiff_unet* h) { return h ? static_cast<int>(h->u.params.size()) : -1; }
+
+extern "C" int encdiff_unet_param_info(const encdiff_unet* h, int i, char* name, int name_cap, long long* shape4,
+                                       int* ndim) {
+  EDB_REQUIRE(h && i >= 0 && i < static_cast<int>(h->u.params.size()), "param_info: bad index");
+  const ParamInfo& p = h->u.params[i];
+  if (name && name_cap > 0) {
+    strncpy(name, p.name.c_str(), name_cap - 1);
+    name[name_cap - 1] = 0;
+  }
+  if (shape4)
+    for (int k = 0; k < 4; ++k) shape4[k] = p.shape[k];
+  if (ndim) *ndim = p.ndim;
+  return EDB_OK;
+}
+
+extern "C" long long encdiff_unet_packed_bytes(const encdiff_unet* h) {
+  return h ? static_cast<long long>(h->u.table_bytes + h->u.bf16_bytes + h->u.f32_bytes) : -1;
+}
+
+extern "C" long long encdiff_unet_workspace_bytes(encdiff_unet* h, int batch, int training) {
+  if (!h || batch <= 0) return -1;
+  return static_cast<long long>(unet_workspace_bytes(&h->u, batch, training != 0));
+}
+
+extern "C" int encdiff_unet_bind(encdiff_unet* h, const float* const* params, float* const* grads, void* packed,
+                                 void* stream) {
+  EDB_REQUIRE(h && params && packed, "unet_bind: null argument");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 1023) == 0, "unet_bind: packed arena must be 1 KB aligned");
+  UNet& u = h->u;
+  const size_t n = u.params.size();
+  u.pptr.assign(params, params + n);
+  if (grads) u.gptr.assign(grads, grads + n);
+  else u.gptr.clear();
+  for (size_t i = 0; i < n; ++i) {
+    EDB_REQUIRE(u.pptr[i] != nullptr, "unet_bind: null parameter pointer");
+    EDB_REQUIRE((reinterpret_cast<uintptr_t>(u.pptr[i]) & 3) == 0, "unet_bind: parameter pointer not 4-byte aligned");
+  }
+  for (size_t i = 0; i < u.table.size(); ++i) {
+    u.table[i].src = u.pptr[u.table_src[i]];
+    u.table[i].src2 = u.table_src2[i] >= 0 ? u.pptr[u.table_src2[i]] : nullptr;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  u.packed = static_cast<char*>(packed);
+  EDB_CHECK_CUDA(cudaMemsetAsync(packed, 0, u.table_bytes + u.bf16_bytes + u.f32_bytes, s));
+  EDB_CHECK_CUDA(cudaMemcpyAsync(packed, u.table.data(), u.table.size() * sizeof(PackEntry), cudaMemcpyHostToDevice, s));
+  EDB_CHECK_CUDA(cudaStreamSynchronize(s));   // the host table may be re-bound later; bind is not a hot call
+  u.w_maps.clear();
+  u.bound = true;
+  return EDB_OK;
+}
+
+extern "C" int encdiff_unet_pack_weights(encdiff_unet* h, void* stream) {
+  EDB_REQUIRE(h && h->u.bound, "pack_weights before bind");
+  UNet& u = h->u;
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_pack(reinterpret_cast<const PackEntry*>(u.packed),
+                                                      static_cast<int>(u.table.size()), u.pack_total, u.pbf(), u.pf32(),
+                                                      static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_unet_plan(encdiff_unet* h, int batch, void* workspace, int training) {
+  EDB_REQUIRE(h && workspace && batch > 0, "unet_plan: bad argument");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, "unet_plan: workspace must be 1 KB aligned");
+  return unet_plan(&h->u, batch, static_cast<char*>(workspace), training != 0);
+}
+
+extern "C" int encdiff_unet_forward(encdiff_unet* h, int batch, const float* x, const float* noise, const float* sqrt_acp,
+                                    const float* sqrt_1macp, const float* t, const float* ctx, float* out, float* x_t,
+                                    void* stream) {
+  EDB_REQUIRE(h && x && t && ctx && out, "unet_forward: null argument");
+  EDB_REQUIRE(!noise || (sqrt_acp && sqrt_1macp), "unet_forward: q_sample needs both coefficient arrays");
+  return unet_forward(&h->u, batch, x, noise, sqrt_acp, sqrt_1macp, t, ctx, out, x_t, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int encdiff_unet_backward(encdiff_unet* h, int batch, const float* dout, const float* ctx, float* dx,
+                                     float* dctx, void* stream) {
+  EDB_REQUIRE(h, "unet_backward: null handle");
+  return unet_backward(&h->u, batch, dout, ctx, dx, dctx, static_cast<cudaStream_t>(stream));
+}
+
+// ---- diffusion glue ---------------------------------------------------------------------------------------------
+extern "C" int encdiff_l1_loss(const float* eps_hat, const float* noise, float* loss, float* deps, long long n,
+                               void* stream) {
+  EDB_REQUIRE(eps_hat && noise && loss && n > 0, "l1_loss: bad argument");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  EDB_CHECK_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), s));
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_l1_loss(eps_hat, noise, loss, deps, n, s)));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_ddim_update(const float* x, const float* e_t, const float* noise, const float* coef4,
+                                   float temperature, float* x_prev, float* pred_x0, long long n, void* stream) {
+  EDB_REQUIRE(x && e_t && coef4 && x_prev && n > 0, "ddim_update: bad argument");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(
+      launch_ddim_update(x, e_t, noise, coef4, temperature, x_prev, pred_x0, n, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_timestep_embedding(const float* t, void* out_bf16, int batch, int dim, void* stream) {
+  EDB_REQUIRE(t && out_bf16 && batch > 0 && dim > 1, "timestep_embedding: bad argument");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(
+      launch_temb(t, static_cast<bf16*>(out_bf16), batch, dim, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_adamw_step(float* p, const float* g, float* m, float* v, float* ema, long long n, float lr,
+                                  float beta1, float beta2, float eps, float weight_decay, int step, float ema_decay,
+                                  void* stream) {
+  EDB_REQUIRE(p && g && m && v && n > 0 && step >= 1, "adamw_step: bad argument");
+  const float bc1 = 1.f - powf(beta1, static_cast<float>(step));
+  const float bc2 = 1.f - powf(beta2, static_cast<float>(step));
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_adamw(p, g, m, v, ema, n, lr, beta1, beta2, eps, weight_decay, bc1, bc2,
+                                                       ema_decay, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}

@@ -1,0 +1,340 @@
+// Elementwise / layout glue kernels (all HBM-bound, vectorised where the layout allows).
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace edb {
+
+static inline int grid_for(long long n, int block, int cap = 148 * 16) {
+  long long g = (n + block - 1) / block;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+// ---- timestep embedding (util.py:179-199): [cos(t f_i) | sin(t f_i)], f_i = exp(-ln(1e4) i / half) ---------------
+__global__ void temb_kernel(const float* __restrict__ t, bf16* __restrict__ out, int B, int dim) {
+  const int half = dim / 2;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < B * half; idx += gridDim.x * blockDim.x) {
+    const int b = idx / half, i = idx - b * half;
+    const float freq = expf(-9.210340371976184f * static_cast<float>(i) / static_cast<float>(half));
+    const float a = t[b] * freq;
+    out[b * dim + i] = __float2bfloat16(cosf(a));
+    out[b * dim + half + i] = __float2bfloat16(sinf(a));
+    if ((dim & 1) && i == 0) out[b * dim + dim - 1] = __float2bfloat16(0.f);
+  }
+}
+int launch_temb(const float* t, bf16* out, int B, int dim, cudaStream_t s) {
+  temb_kernel<<<grid_for(static_cast<long long>(B) * (dim / 2), 256), 256, 0, s>>>(t, out, B, dim);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- SiLU on the (tiny) embedding MLP ------------------------------------------------------------------------------
+__global__ void silu_fwd_kernel(const float* __restrict__ x, bf16* __restrict__ y, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    y[i] = __float2bfloat16(silu_f(x[i]));
+}
+__global__ void silu_bwd_kernel(const float* __restrict__ x, const bf16* __restrict__ dy, bf16* __restrict__ dx,
+                                long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    dx[i] = __float2bfloat16(__bfloat162float(dy[i]) * silu_grad_f(x[i]));
+}
+int launch_silu_fwd(const float* x, bf16* y, long long n, cudaStream_t s) {
+  silu_fwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, y, n);
+  return static_cast<int>(cudaGetLastError());
+}
+int launch_silu_bwd(const float* x, const bf16* dy, bf16* dx, long long n, cudaStream_t s) {
+  silu_bwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, dy, dx, n);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- GEGLU (attention.py:37-45) -------------------------------------------------------------------------------------
+__global__ void geglu_fwd_kernel(const bf16* __restrict__ g, bf16* __restrict__ out, long long M, int inner) {
+  const int nv = inner >> 3;
+  const long long total = M * nv;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = idx / nv;
+    const int c = static_cast<int>(idx - row * nv) * 8;
+    float v[8], gt[8];
+    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + c), v);
+    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + inner + c), gt);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] *= gelu_erf_f(gt[k]);
+    *reinterpret_cast<uint4*>(out + row * inner + c) = pack8(v);
+  }
+}
+__global__ void geglu_bwd_kernel(const bf16* __restrict__ g, const bf16* __restrict__ dout, bf16* __restrict__ dg,
+                                 long long M, int inner) {
+  const int nv = inner >> 3;
+  const long long total = M * nv;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = idx / nv;
+    const int c = static_cast<int>(idx - row * nv) * 8;
+    float v[8], gt[8], d[8], dv[8], dgt[8];
+    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + c), v);
+    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + inner + c), gt);
+    unpack8(*reinterpret_cast<const uint4*>(dout + row * inner + c), d);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      dv[k] = d[k] * gelu_erf_f(gt[k]);
+      dgt[k] = d[k] * v[k] * gelu_erf_grad_f(gt[k]);
+    }
+    *reinterpret_cast<uint4*>(dg + row * 2 * inner + c) = pack8(dv);
+    *reinterpret_cast<uint4*>(dg + row * 2 * inner + inner + c) = pack8(dgt);
+  }
+}
+int launch_geglu_fwd(const bf16* g, bf16* out, long long M, int inner, cudaStream_t s) {
+  if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
+  geglu_fwd_kernel<<<grid_for(M * (inner / 8), 256), 256, 0, s>>>(g, out, M, inner);
+  return static_cast<int>(cudaGetLastError());
+}
+int launch_geglu_bwd(const bf16* g, const bf16* dout, bf16* dg, long long M, int inner, cudaStream_t s) {
+  if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
+  geglu_bwd_kernel<<<grid_for(M * (inner / 8), 256), 256, 0, s>>>(g, dout, dg, M, inner);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- bias gradient: column sums -------------------------------------------------------------------------------------
+// block = (32 column-lanes) x (8 row-lanes); grid.x tiles columns by 32, grid.y splits rows
+__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, long long M, int ld, int col0, int N,
+                                                     float* __restrict__ dst0, float* __restrict__ dst1) {
+  __shared__ float red[8][33];
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + cl;
+  float a = 0.f;
+  if (col < N) {
+    for (long long r = blockIdx.y * 8 + rl; r < M; r += static_cast<long long>(gridDim.y) * 8)
+      a += __bfloat162float(x[r * ld + col0 + col]);
+  }
+  red[rl][cl] = a;
+  __syncthreads();
+  if (rl == 0 && col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][cl];
+    atomicAdd(dst0 + col, t);
+    if (dst1) atomicAdd(dst1 + col, t);
+  }
+}
+int launch_colsum(const bf16* x, long long M, int ld, int col0, int N, float* dst0, float* dst1, cudaStream_t s) {
+  const int gx = (N + 31) / 32;
+  long long gy = (M + 8 * 32 - 1) / (8 * 32);   // >= 32 rows per thread
+  const long long cap = (148 * 8 + gx - 1) / gx;
+  if (gy > cap) gy = cap;
+  if (gy < 1) gy = 1;
+  colsum_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, 0, s>>>(x, M, ld, col0, N, dst0, dst1);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- input stem: (optional q_sample) + NCHW fp32 -> im2col bf16 [B*H*W, 64], column ci*9 + tap ----------------------
+__global__ void stem_im2col_kernel(const float* __restrict__ x, const float* __restrict__ noise,
+                                   const float* __restrict__ sa, const float* __restrict__ sb, float* __restrict__ xt,
+                                   bf16* __restrict__ cols, int B, int Cin, int H, int W) {
+  const long long total = static_cast<long long>(B) * H * W;
+  for (long long pix = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; pix < total;
+       pix += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(pix / (H * W));
+    const int rem = static_cast<int>(pix - static_cast<long long>(b) * H * W);
+    const int y = rem / W, xx = rem - y * W;
+    bf16 row[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) row[i] = __float2bfloat16(0.f);
+    for (int ci = 0; ci < Cin; ++ci) {
+      const long long plane = (static_cast<long long>(b) * Cin + ci) * H * W;
+      for (int t = 0; t < 9; ++t) {
+        const int yy = y + t / 3 - 1, xs = xx + t % 3 - 1;
+        float v = 0.f;
+        if (yy >= 0 && yy < H && xs >= 0 && xs < W) {
+          v = x[plane + yy * W + xs];
+          if (noise) v = sa[b] * v + sb[b] * noise[plane + yy * W + xs];
+        }
+        if (ci * 9 + t < 64) row[ci * 9 + t] = __float2bfloat16(v);
+        if (t == 4 && xt) xt[plane + y * W + xx] = v;
+      }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(cols + pix * 64);
+    const uint4* src = reinterpret_cast<const uint4*>(row);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) dst[i] = src[i];
+  }
+}
+int launch_stem_im2col(const float* x, const float* noise, const float* sa, const float* sb, float* xt, bf16* cols,
+                       int B, int Cin, int H, int W, cudaStream_t s) {
+  if (Cin * 9 > 64) return static_cast<int>(cudaErrorInvalidValue);
+  stem_im2col_kernel<<<grid_for(static_cast<long long>(B) * H * W, 128), 128, 0, s>>>(x, noise, sa, sb, xt, cols, B,
+                                                                                      Cin, H, W);
+  return static_cast<int>(cudaGetLastError());
+}
+
+__global__ void stem_col2im_kernel(const bf16* __restrict__ dcols, float* __restrict__ dx, int B, int Cin, int H, int W) {
+  const long long total = static_cast<long long>(B) * Cin * H * W;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int xx = static_cast<int>(idx % W);
+    const int y = static_cast<int>((idx / W) % H);
+    const int ci = static_cast<int>((idx / (static_cast<long long>(W) * H)) % Cin);
+    const int b = static_cast<int>(idx / (static_cast<long long>(W) * H * Cin));
+    float a = 0.f;
+    // input pixel (y, xx) was read by output pixel (y - dy, xx - dx) through tap (dy, dx)
+    for (int t = 0; t < 9; ++t) {
+      const int oy = y - (t / 3 - 1), ox = xx - (t % 3 - 1);
+      if (oy >= 0 && oy < H && ox >= 0 && ox < W)
+        a += __bfloat162float(dcols[((static_cast<long long>(b) * H + oy) * W + ox) * 64 + ci * 9 + t]);
+    }
+    dx[idx] = a;
+  }
+}
+int launch_stem_col2im(const bf16* dcols, float* dx, int B, int Cin, int H, int W, cudaStream_t s) {
+  stem_col2im_kernel<<<grid_for(static_cast<long long>(B) * Cin * H * W, 256), 256, 0, s>>>(dcols, dx, B, Cin, H, W);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- layout converters for the 3-channel head ------------------------------------------------------------------------
+__global__ void nhwc_to_nchw_kernel(const float* __restrict__ y, float* __restrict__ out, int B, int C, int HW) {
+  const long long total = static_cast<long long>(B) * C * HW;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int p = static_cast<int>(idx % HW);
+    const int c = static_cast<int>((idx / HW) % C);
+    const long long b = idx / (static_cast<long long>(HW) * C);
+    out[idx] = y[(b * HW + p) * C + c];
+  }
+}
+int launch_nhwc_to_nchw(const float* y, float* out, int B, int C, int H, int W, cudaStream_t s) {
+  nhwc_to_nchw_kernel<<<grid_for(static_cast<long long>(B) * C * H * W, 256), 256, 0, s>>>(y, out, B, C, H * W);
+  return static_cast<int>(cudaGetLastError());
+}
+__global__ void nchw_to_nhwc_bf16_kernel(const float* __restrict__ x, bf16* __restrict__ out, int B, int C, int HW,
+                                         int Cpad) {
+  const long long total = static_cast<long long>(B) * HW * Cpad;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(idx % Cpad);
+    const int p = static_cast<int>((idx / Cpad) % HW);
+    const long long b = idx / (static_cast<long long>(Cpad) * HW);
+    out[idx] = __float2bfloat16(c < C ? x[(b * C + c) * HW + p] : 0.f);
+  }
+}
+int launch_nchw_to_nhwc_bf16(const float* x, bf16* out, int B, int C, int H, int W, int Cpad, cudaStream_t s) {
+  nchw_to_nhwc_bf16_kernel<<<grid_for(static_cast<long long>(B) * H * W * Cpad, 256), 256, 0, s>>>(x, out, B, C, H * W,
+                                                                                                  Cpad);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- L1 loss + its gradient (ddpm_enc.py:297-301,1198-1213) -----------------------------------------------------------
+__global__ void l1_loss_kernel(const float* __restrict__ e, const float* __restrict__ n, float* __restrict__ loss,
+                               float* __restrict__ de, long long cnt, float inv) {
+  float a = 0.f;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < cnt;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float d = e[i] - n[i];
+    a += fabsf(d);
+    if (de) de[i] = d > 0.f ? inv : (d < 0.f ? -inv : 0.f);
+  }
+  a = warp_sum(a);
+  __shared__ float red[32];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) atomicAdd(loss, t * inv);
+  }
+}
+int launch_l1_loss(const float* eps_hat, const float* noise, float* loss, float* deps, long long n, cudaStream_t s) {
+  l1_loss_kernel<<<grid_for(n, 256, 148 * 4), 256, 0, s>>>(eps_hat, noise, loss, deps, n, 1.0f / static_cast<float>(n));
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- DDIM update (ddim.py:197-206), same operation order in fp32 ------------------------------------------------------
+__global__ void ddim_update_kernel(const float* __restrict__ x, const float* __restrict__ e, const float* __restrict__ nz,
+                                   const float* __restrict__ coef, float temperature, float* __restrict__ x_prev,
+                                   float* __restrict__ pred_x0, long long n) {
+  const float a_t = coef[0], a_prev = coef[1], sigma = coef[2], somat = coef[3];
+  const float sqrt_at = sqrtf(a_t), sqrt_ap = sqrtf(a_prev);
+  const float dir = sqrtf(__fsub_rn(__fsub_rn(1.f, a_prev), __fmul_rn(sigma, sigma)));
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float et = e[i];
+    const float p0 = __fdiv_rn(x[i] - __fmul_rn(somat, et), sqrt_at);
+    const float d = __fmul_rn(dir, et);
+    const float noise = nz ? __fmul_rn(__fmul_rn(sigma, nz[i]), temperature) : 0.f;
+    x_prev[i] = __fadd_rn(__fadd_rn(__fmul_rn(sqrt_ap, p0), d), noise);
+    if (pred_x0) pred_x0[i] = p0;
+  }
+}
+int launch_ddim_update(const float* x, const float* e_t, const float* noise, const float* coef, float temperature,
+                       float* x_prev, float* pred_x0, long long n, cudaStream_t s) {
+  ddim_update_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, e_t, noise, coef, temperature, x_prev, pred_x0, n);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- weight packing: fp32 reference-layout parameters -> bf16 GEMM operands (and fused fp32 biases) -------------------
+__global__ void pack_kernel(const PackEntry* __restrict__ tab, int n_entries, long long total, bf16* __restrict__ abf,
+                            float* __restrict__ af32) {
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    int lo = 0, hi = n_entries - 1;   // last entry with prefix <= idx
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (tab[mid].prefix <= idx) lo = mid; else hi = mid - 1;
+    }
+    const PackEntry& en = tab[lo];
+    const long long e = idx - en.prefix;
+    const float v = en.src[e];
+    if (en.kind == 2) {
+      af32[en.dst_off + en.col0 + e] = v;
+    } else if (en.kind == 3) {
+      af32[en.dst_off + en.col0 + e] = v + en.src2[e];
+    } else {
+      const int per_row = en.cin * en.taps;
+      const int r = static_cast<int>(e / per_row);
+      const int rem = static_cast<int>(e - static_cast<long long>(r) * per_row);
+      const int ci = rem / en.taps, tap = rem - ci * en.taps;
+      long long row, col;
+      switch (en.kind) {
+        case 0: row = en.row0 + r; col = en.col0 + tap * en.cin_pad + ci; break;
+        case 1: row = en.row0 + ci; col = en.col0 + tap * en.rows_pad + r; break;
+        case 4: row = en.row0 + r; col = en.col0 + rem; break;
+        default: row = en.row0 + rem; col = en.col0 + r; break;   // 5
+      }
+      abf[en.dst_off + row * en.dst_ld + col] = __float2bfloat16(v);
+    }
+  }
+}
+int launch_pack(const PackEntry* table_dev, int n_entries, long long total, bf16* arena_bf16, float* arena_f32,
+                cudaStream_t s) {
+  pack_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, s>>>(table_dev, n_entries, total, arena_bf16, arena_f32);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- fused AdamW (+EMA) over flat fp32 buffers (torch.optim.AdamW semantics: decoupled decay) --------------------------
+__global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                             float* __restrict__ v, float* __restrict__ ema, long long n, float lr, float b1, float b2,
+                             float eps, float wd, float bc1, float bc2, float ema_decay) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float w = p[i];
+    const float gi = g[i];
+    w *= (1.f - lr * wd);
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / sqrtf(bc2) + eps;
+    w -= (lr / bc1) * (mi / denom);
+    p[i] = w;
+    if (ema) ema[i] -= (1.f - ema_decay) * (ema[i] - w);   // ema.py:38-42
+  }
+}
+int launch_adamw(float* p, const float* g, float* m, float* v, float* ema, long long n, float lr, float beta1,
+                 float beta2, float eps, float wd, float bc1, float bc2, float ema_decay, cudaStream_t s) {
+  adamw_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, s>>>(p, g, m, v, ema, n, lr, beta1, beta2, eps, wd, bc1, bc2,
+                                                          ema_decay);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace edb

@@ -265,8 +265,8 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ Wgra
         mbar_wait(&empty_bar[st], ph ^ 1);
         uint8_t* sp = smem + st * STAGE_BYTES;
         mbar_arrive_expect_tx(&full_bar[st], STAGE_BYTES);
-        tma_load_4d(sp, &p.pmap, &full_bar[st], p_tile * 128, 0, y0, b0);
-        tma_load_4d(sp + kABytes, &p.pmap, &full_bar[st], p_tile * 128 + 64, 0, y0, b0);
+        tma_load_4d(sp, &p.pmap, &full_bar[st], p.p_off + p_tile * 128, 0, y0, b0);
+        tma_load_4d(sp + kABytes, &p.pmap, &full_bar[st], p.p_off + p_tile * 128 + 64, 0, y0, b0);
 #pragma unroll
         for (int j = 0; j < BN / 64; ++j)
           tma_load_4d(sp + P_BYTES + j * kABytes, &p.qmap, &full_bar[st], q_tile * BN + j * 64, dx, y0 + dy, b0);

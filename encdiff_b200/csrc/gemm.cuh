@@ -54,6 +54,7 @@ struct WgradParams {
   int m_tiles;          // number of 128-pixel tiles (reduction length / 128)
   int tiles_per_split;  // reduction tiles handled by one CTA (blockIdx.z)
   int Cp, Cq;           // valid channels on each side
+  int p_off;            // first channel of the dY slice (dY may hold several stacked outputs, e.g. q|k|v)
   float* out;           // fp32 gradient, element (p, q, tap) at out[p*stride_p + (q+q_off)*stride_q + tap*stride_tap]
   long long stride_p, stride_q, stride_tap;
   int q_off;

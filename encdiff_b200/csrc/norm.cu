@@ -1,0 +1,579 @@
+// GroupNorm (+FiLM +SiLU +2x resample) and LayerNorm, forward and backward.  HBM-bound kernels: one read of the
+// input slab from HBM (the second pass hits L1/L2), one write of the result.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace edb {
+
+// ---------------------------------------------------------------------------------------------------------------
+// GroupNorm: one CTA per sample; thread = (8-channel chunk, pixel lane)
+// ---------------------------------------------------------------------------------------------------------------
+struct GnThread {
+  int C, nv, HW, chunk, prow, rp, c0;
+  const bf16* src;  // sample base of the source holding this thread's chunk
+  int ld, cofs;
+};
+
+__device__ __forceinline__ GnThread gn_thread(const GnParams& p, int b) {
+  GnThread t;
+  t.C = p.C0 + p.C1;
+  t.nv = t.C >> 3;
+  t.HW = p.H * p.W;
+  t.chunk = threadIdx.x % t.nv;
+  t.prow = threadIdx.x / t.nv;
+  t.rp = blockDim.x / t.nv;
+  t.c0 = t.chunk * 8;
+  if (t.c0 < p.C0) {
+    t.src = p.x0 + static_cast<long long>(b) * t.HW * p.C0;
+    t.ld = p.C0;
+    t.cofs = t.c0;
+  } else {
+    t.src = p.x1 + static_cast<long long>(b) * t.HW * p.C1;
+    t.ld = p.C1;
+    t.cofs = t.c0 - p.C0;
+  }
+  return t;
+}
+
+__device__ __forceinline__ void load8(const bf16* p, float* f) { unpack8(*reinterpret_cast<const uint4*>(p), f); }
+__device__ __forceinline__ void store8(bf16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
+
+__global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x;
+  const GnThread t = gn_thread(p, b);
+  const int C = t.C;
+  float* chsum = sm;
+  float* chsq = sm + C;
+  float* cA = sm + 2 * C;
+  float* cB = sm + 3 * C;
+  float* gstat = sm + 4 * C;  // [64]
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const bool active = t.prow < t.rp;  // threads beyond nv*rp idle (blockDim is a multiple of nv, so all active)
+  {
+    float s[8], q[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+    if (active) {
+      for (int pix = t.prow; pix < t.HW; pix += t.rp) {
+        float f[8];
+        load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          s[k] += f[k];
+          q[k] += f[k] * f[k];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        atomicAdd(&chsum[t.c0 + k], s[k]);
+        atomicAdd(&chsq[t.c0 + k], q[k]);
+      }
+    }
+  }
+  __syncthreads();
+  const int cpg = C / 32;
+  if (threadIdx.x < 32) {
+    const int g = threadIdx.x;
+    float S = 0.f, Q = 0.f;
+    for (int c = g * cpg; c < (g + 1) * cpg; ++c) {
+      S += chsum[c];
+      Q += chsq[c];
+    }
+    const float n = static_cast<float>(cpg) * t.HW;
+    const float mean = S / n;
+    const float var = fmaxf(Q / n - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + p.eps);
+    gstat[g] = mean;
+    gstat[32 + g] = rstd;
+    p.stats[(b * 32 + g) * 2] = mean;
+    p.stats[(b * 32 + g) * 2 + 1] = rstd;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / cpg;
+    float ga = p.gamma[c] * gstat[32 + g];
+    float be = p.beta[c] - gstat[g] * ga;
+    if (p.film) {
+      const float* fr = p.film + static_cast<long long>(b) * p.ldfilm + p.film_off;
+      const float sc = 1.f + fr[c];
+      ga *= sc;
+      be = be * sc + fr[C + c];
+    }
+    cA[c] = ga;
+    cB[c] = be;
+  }
+  __syncthreads();
+  if (!active) return;
+  float a[8], bb[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    a[k] = cA[t.c0 + k];
+    bb[k] = cB[t.c0 + k];
+  }
+  const int W = p.W, H = p.H;
+  if (p.resample == RESAMPLE_NONE) {
+    bf16* dst = p.act + static_cast<long long>(b) * t.HW * C + t.c0;
+    for (int pix = t.prow; pix < t.HW; pix += t.rp) {
+      float f[8];
+      load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float y = a[k] * f[k] + bb[k];
+        f[k] = p.silu ? silu_f(y) : y;
+      }
+      store8(dst + static_cast<long long>(pix) * C, f);
+    }
+  } else if (p.resample == RESAMPLE_DOWN) {
+    const int Wo = W / 2, HWo = (H / 2) * Wo;
+    bf16* dst = p.act + static_cast<long long>(b) * HWo * C + t.c0;
+    bf16* dxs = p.xs ? p.xs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
+    for (int op = t.prow; op < HWo; op += t.rp) {
+      const int oy = op / Wo, ox = op - oy * Wo;
+      float ya[8], xa[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) ya[k] = xa[k] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int pix = (2 * oy + (i >> 1)) * W + 2 * ox + (i & 1);
+        float f[8];
+        load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float y = a[k] * f[k] + bb[k];
+          ya[k] += p.silu ? silu_f(y) : y;
+          xa[k] += f[k];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        ya[k] *= 0.25f;
+        xa[k] *= 0.25f;
+      }
+      store8(dst + static_cast<long long>(op) * C, ya);
+      if (dxs) store8(dxs + static_cast<long long>(op) * C, xa);
+    }
+  } else {  // RESAMPLE_UP
+    const int Wo = W * 2, HWo = 4 * t.HW;
+    bf16* dst = p.act + static_cast<long long>(b) * HWo * C + t.c0;
+    bf16* dxs = p.xs ? p.xs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
+    for (int pix = t.prow; pix < t.HW; pix += t.rp) {
+      const int y = pix / W, x = pix - y * W;
+      float f[8], ya[8];
+      load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float v = a[k] * f[k] + bb[k];
+        ya[k] = p.silu ? silu_f(v) : v;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const long long op = static_cast<long long>(2 * y + (i >> 1)) * Wo + 2 * x + (i & 1);
+        store8(dst + op * C, ya);
+        if (dxs) store8(dxs + op * C, f);
+      }
+    }
+  }
+}
+
+// gradient arriving at input pixel (y, x) of a tensor that was resampled AFTER this point
+__device__ __forceinline__ void gather_resampled(const bf16* g, int C, int resample, int y, int x, int W, float* d) {
+  if (resample == RESAMPLE_NONE) {
+    load8(g + static_cast<long long>(y * W + x) * C, d);
+  } else if (resample == RESAMPLE_DOWN) {
+    load8(g + static_cast<long long>((y >> 1) * (W >> 1) + (x >> 1)) * C, d);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) d[k] *= 0.25f;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) d[k] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float f[8];
+      load8(g + (static_cast<long long>(2 * y + (i >> 1)) * (2 * W) + 2 * x + (i & 1)) * C, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) d[k] += f[k];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x;
+  const GnThread t = gn_thread(p, b);
+  const int C = t.C;
+  float* cA = sm;           // u = cA*x + cB   (pre-activation)
+  float* cB = sm + C;
+  float* cM = sm + 2 * C;   // mean per channel
+  float* cR = sm + 3 * C;   // rstd per channel
+  float* S1 = sm + 4 * C;   // sum dyp          -> later k1
+  float* S2 = sm + 5 * C;   // sum dyp * xhat   -> later k2
+  float* K3 = sm + 6 * C;
+  float* gAB = sm + 7 * C;  // [64] group sums
+  const int cpg = C / 32;
+  const int W = p.W;
+  int HWo = t.HW;
+  if (p.resample == RESAMPLE_DOWN) HWo = t.HW / 4;
+  if (p.resample == RESAMPLE_UP) HWo = t.HW * 4;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / cpg;
+    const float mean = p.stats[(b * 32 + g) * 2], rstd = p.stats[(b * 32 + g) * 2 + 1];
+    float ga = p.gamma[c] * rstd;
+    float be = p.beta[c] - mean * ga;
+    if (p.film) {
+      const float* fr = p.film + static_cast<long long>(b) * p.ldfilm + p.film_off;
+      const float sc = 1.f + fr[c];
+      ga *= sc;
+      be = be * sc + fr[C + c];
+    }
+    cA[c] = ga;
+    cB[c] = be;
+    cM[c] = mean;
+    cR[c] = rstd;
+    S1[c] = 0.f;
+    S2[c] = 0.f;
+  }
+  __syncthreads();
+  const bf16* dact = p.dact + static_cast<long long>(b) * HWo * C + t.c0;
+  float a[8], bb[8], mu[8], rs[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    a[k] = cA[t.c0 + k];
+    bb[k] = cB[t.c0 + k];
+    mu[k] = cM[t.c0 + k];
+    rs[k] = cR[t.c0 + k];
+  }
+  {
+    float s1[8], s2[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+    for (int pix = t.prow; pix < t.HW; pix += t.rp) {
+      const int y = pix / W, x = pix - y * W;
+      float f[8], d[8];
+      load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+      gather_resampled(dact, C, p.resample, y, x, W, d);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float dyp = p.silu ? d[k] * silu_grad_f(a[k] * f[k] + bb[k]) : d[k];
+        s1[k] += dyp;
+        s2[k] += dyp * (f[k] - mu[k]) * rs[k];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      atomicAdd(&S1[t.c0 + k], s1[k]);
+      atomicAdd(&S2[t.c0 + k], s2[k]);
+    }
+  }
+  __syncthreads();
+  // per-channel parameter gradients; turn S1/S2 into gsc-weighted values for the group sums
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float s1 = S1[c], s2 = S2[c];
+    const float gam = p.gamma[c], bet = p.beta[c];
+    float sc = 1.f;
+    if (p.film) {
+      sc = 1.f + p.film[static_cast<long long>(b) * p.ldfilm + p.film_off + c];
+      if (p.dfilm) {
+        bf16* df = p.dfilm + static_cast<long long>(b) * p.lddfilm + p.film_off;
+        df[c] = __float2bfloat16(gam * s2 + bet * s1);   // d scale
+        df[C + c] = __float2bfloat16(s1);                // d shift
+      }
+    }
+    if (p.dgamma) atomicAdd(&p.dgamma[c], sc * s2);
+    if (p.dbeta) atomicAdd(&p.dbeta[c], sc * s1);
+    const float gsc = gam * sc;
+    S1[c] = gsc * s1;
+    S2[c] = gsc * s2;
+    K3[c] = gsc;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int g = threadIdx.x;
+    float A = 0.f, Bv = 0.f;
+    for (int c = g * cpg; c < (g + 1) * cpg; ++c) {
+      A += S1[c];
+      Bv += S2[c];
+    }
+    const float n = static_cast<float>(cpg) * t.HW;
+    gAB[g] = A / n;
+    gAB[32 + g] = Bv / n;
+  }
+  __syncthreads();
+  float k1[8], k2[8], k3[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = t.c0 + k, g = c / cpg;
+    k1[k] = rs[k] * K3[c];
+    k2[k] = rs[k] * gAB[g];
+    k3[k] = rs[k] * gAB[32 + g];
+  }
+  bf16* dxp;
+  int acc;
+  if (t.c0 < p.C0) {
+    dxp = p.dx0 + static_cast<long long>(b) * t.HW * p.C0 + t.cofs;
+    acc = p.acc0;
+  } else {
+    dxp = p.dx1 + static_cast<long long>(b) * t.HW * p.C1 + t.cofs;
+    acc = p.acc1;
+  }
+  const bf16* dxs = p.dxs ? p.dxs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
+  for (int pix = t.prow; pix < t.HW; pix += t.rp) {
+    const int y = pix / W, x = pix - y * W;
+    float f[8], d[8], o[8];
+    load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+    gather_resampled(dact, C, p.resample, y, x, W, d);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float dyp = p.silu ? d[k] * silu_grad_f(a[k] * f[k] + bb[k]) : d[k];
+      const float xh = (f[k] - mu[k]) * rs[k];
+      o[k] = k1[k] * dyp - k2[k] - xh * k3[k];
+    }
+    if (dxs) {
+      float e[8];
+      gather_resampled(dxs, C, p.resample, y, x, W, e);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] += e[k];
+    }
+    bf16* q = dxp + static_cast<long long>(pix) * t.ld;
+    if (acc) {
+      float e[8];
+      load8(q, e);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] += e[k];
+    }
+    store8(q, o);
+  }
+}
+
+static int gn_threads(int C) {
+  const int nv = C / 8;
+  int rp = 512 / nv;
+  if (rp < 1) rp = 1;
+  return nv * rp;
+}
+
+int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s) {
+  const int C = p.C0 + p.C1;
+  if (C % 32 != 0 || (p.C0 % 8) != 0 || C > 8192) return static_cast<int>(cudaErrorInvalidValue);
+  const size_t smem = (4 * C + 64) * sizeof(float);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(gn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = smem;
+  }
+  gn_fwd_kernel<<<B, gn_threads(C), smem, s>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_gn_bwd(const GnParams& p, int B, cudaStream_t s) {
+  const int C = p.C0 + p.C1;
+  if (C % 32 != 0 || (p.C0 % 8) != 0 || C > 4096) return static_cast<int>(cudaErrorInvalidValue);
+  const size_t smem = (7 * C + 64) * sizeof(float);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(gn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = smem;
+  }
+  gn_bwd_kernel<<<B, gn_threads(C), smem, s>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// LayerNorm: LPR lanes per row (8/16/32), each lane owns up to CPL 8-channel chunks
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float group_sum(float v, int lpr) {
+  for (int o = lpr >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <int CPL>
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, float eps, bf16* __restrict__ y,
+                                                     float* __restrict__ stats, int M, int C, int lpr) {
+  const int nchunks = C >> 3;
+  const int rows_per_block = blockDim.x / lpr;
+  const int lane_in_row = threadIdx.x % lpr;
+  const long long row = static_cast<long long>(blockIdx.x) * rows_per_block + threadIdx.x / lpr;
+  const bool ok = row < M;
+  float v[CPL][8];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < CPL; ++j) {
+    const int ch = lane_in_row + j * lpr;
+    if (ok && ch < nchunks) {
+      unpack8(*reinterpret_cast<const uint4*>(x + row * C + ch * 8), v[j]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += v[j][k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[j][k] = 0.f;
+    }
+  }
+  const float mean = group_sum(s, lpr) / C;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < CPL; ++j) {
+    const int ch = lane_in_row + j * lpr;
+    if (ch < nchunks) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float d = v[j][k] - mean;
+        q += d * d;
+      }
+    }
+  }
+  const float rstd = rsqrtf(group_sum(q, lpr) / C + eps);
+  if (!ok) return;
+  if (lane_in_row == 0) {
+    stats[row * 2] = mean;
+    stats[row * 2 + 1] = rstd;
+  }
+#pragma unroll
+  for (int j = 0; j < CPL; ++j) {
+    const int ch = lane_in_row + j * lpr;
+    if (ch < nchunks) {
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = (v[j][k] - mean) * rstd * __ldg(gamma + ch * 8 + k) + __ldg(beta + ch * 8 + k);
+      *reinterpret_cast<uint4*>(y + row * C + ch * 8) = pack8(o);
+    }
+  }
+}
+
+template <int CPL>
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ stats,
+                                                     const float* __restrict__ gamma, const bf16* __restrict__ dy,
+                                                     const bf16* __restrict__ dres, bf16* __restrict__ dx,
+                                                     float* __restrict__ dgamma, float* __restrict__ dbeta, int M, int C,
+                                                     int lpr) {
+  extern __shared__ float sm[];  // [2*C] block partial sums of dgamma / dbeta
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const int nchunks = C >> 3;
+  const int rows_per_block = blockDim.x / lpr;
+  const int lane_in_row = threadIdx.x % lpr;
+  float ag[CPL][8], ab[CPL][8];
+#pragma unroll
+  for (int j = 0; j < CPL; ++j)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) ag[j][k] = ab[j][k] = 0.f;
+  for (long long row0 = static_cast<long long>(blockIdx.x) * rows_per_block; row0 < M;
+       row0 += static_cast<long long>(gridDim.x) * rows_per_block) {
+    const long long row = row0 + threadIdx.x / lpr;
+    const bool ok = row < M;
+    float xh[CPL][8], g[CPL][8];
+    float s1 = 0.f, s2 = 0.f;
+    float mean = 0.f, rstd = 0.f;
+    if (ok) {
+      mean = stats[row * 2];
+      rstd = stats[row * 2 + 1];
+    }
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      const int ch = lane_in_row + j * lpr;
+      if (ok && ch < nchunks) {
+        float xv[8], dv[8];
+        unpack8(*reinterpret_cast<const uint4*>(x + row * C + ch * 8), xv);
+        unpack8(*reinterpret_cast<const uint4*>(dy + row * C + ch * 8), dv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          xh[j][k] = (xv[k] - mean) * rstd;
+          ag[j][k] += dv[k] * xh[j][k];
+          ab[j][k] += dv[k];
+          g[j][k] = dv[k] * __ldg(gamma + ch * 8 + k);
+          s1 += g[j][k];
+          s2 += g[j][k] * xh[j][k];
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) xh[j][k] = g[j][k] = 0.f;
+      }
+    }
+    s1 = group_sum(s1, lpr) / C;
+    s2 = group_sum(s2, lpr) / C;
+    if (ok) {
+#pragma unroll
+      for (int j = 0; j < CPL; ++j) {
+        const int ch = lane_in_row + j * lpr;
+        if (ch < nchunks) {
+          float o[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) o[k] = rstd * (g[j][k] - s1 - xh[j][k] * s2);
+          if (dres) {
+            float r[8];
+            unpack8(*reinterpret_cast<const uint4*>(dres + row * C + ch * 8), r);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] += r[k];
+          }
+          *reinterpret_cast<uint4*>(dx + row * C + ch * 8) = pack8(o);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < CPL; ++j) {
+    const int ch = lane_in_row + j * lpr;
+    if (ch < nchunks) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        atomicAdd(&sm[ch * 8 + k], ag[j][k]);
+        atomicAdd(&sm[C + ch * 8 + k], ab[j][k]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    atomicAdd(&dgamma[c], sm[c]);
+    atomicAdd(&dbeta[c], sm[C + c]);
+  }
+}
+
+static void ln_shape(int C, int* lpr, int* cpl) {
+  const int nchunks = C / 8;
+  int l = 8;
+  if (nchunks >= 32) l = 32;
+  else if (nchunks >= 16) l = 16;
+  *lpr = l;
+  *cpl = (nchunks + l - 1) / l;
+}
+
+int launch_ln_fwd(const bf16* x, const float* gamma, const float* beta, float eps, bf16* y, float* stats, int M, int C,
+                  cudaStream_t s) {
+  if (C % 8 != 0 || C < 64 || C > 1024) return static_cast<int>(cudaErrorInvalidValue);
+  int lpr, cpl;
+  ln_shape(C, &lpr, &cpl);
+  const int rows_per_block = 256 / lpr;
+  const int grid = (M + rows_per_block - 1) / rows_per_block;
+  switch (cpl) {
+    case 1: ln_fwd_kernel<1><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    case 2: ln_fwd_kernel<2><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    case 3: ln_fwd_kernel<3><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    case 4: ln_fwd_kernel<4><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    default: return static_cast<int>(cudaErrorInvalidValue);
+  }
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_ln_bwd(const bf16* x, const float* stats, const float* gamma, const bf16* dy, const bf16* dres, bf16* dx,
+                  float* dgamma, float* dbeta, int M, int C, cudaStream_t s) {
+  if (C % 8 != 0 || C < 64 || C > 1024) return static_cast<int>(cudaErrorInvalidValue);
+  int lpr, cpl;
+  ln_shape(C, &lpr, &cpl);
+  const int rows_per_block = 256 / lpr;
+  int grid = (M + rows_per_block - 1) / rows_per_block;
+  if (grid > 148 * 4) grid = 148 * 4;
+  const size_t smem = 2 * C * sizeof(float);
+  switch (cpl) {
+    case 1: ln_bwd_kernel<1><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
+    case 2: ln_bwd_kernel<2><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
+    case 3: ln_bwd_kernel<3><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
+    case 4: ln_bwd_kernel<4><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
+    default: return static_cast<int>(cudaErrorInvalidValue);
+  }
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace edb

@@ -1,0 +1,123 @@
+// Host-side description of the EncDiff UNet denoiser: architecture walk, parameter inventory, packed-weight layout,
+// activation plan and the forward / backward launch sequences.  Mirrors UNetModel.__init__ / forward
+// (ldm/modules/diffusionmodules/openaimodel_enc.py:443-748) for the spatial-transformer + resblock_updown branch.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <map>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/encdiff_b200.h"
+#include "gemm.cuh"
+#include "kernels.cuh"
+
+namespace edb {
+
+struct ParamInfo {
+  std::string name;
+  int ndim;
+  long long shape[4];
+  long long numel;
+};
+
+// a block-level activation (NHWC bf16) with its gradient buffer
+struct Tn {
+  bf16* p = nullptr;
+  bf16* g = nullptr;
+  int C = 0, H = 0, W = 0;
+  bool ginit = false;
+};
+
+// one packed GEMM operand: bf16 [rows_pad, K] at element offset `off` of the packed bf16 arena
+struct Packed {
+  long long off = 0;
+  long long rows = 0;   // padded rows
+  long long K = 0;
+};
+
+struct ResLayer {
+  std::string prefix;
+  int c0 = 0, c1 = 0, cout = 0;       // input channels (main, concat skip), output channels
+  bool up = false, down = false, skipconv = false;
+  int Hin = 0, Win = 0, Hout = 0, Wout = 0;
+  int film_off = 0;
+  // parameter indices
+  int gn1_w, gn1_b, conv1_w, conv1_b, emb_w, emb_b, gn2_w, gn2_b, conv2_w, conv2_b, skip_w = -1, skip_b = -1;
+  Packed w1f, w1t, w2f, w2t, wst;     // conv1 fwd/T, conv2(+skip) fwd, conv2 T, skip T
+  long long bias2_off = -1;           // fused conv2+skip bias in the fp32 arena (skipconv only)
+  // plan
+  Tn *x0 = nullptr, *x1 = nullptr, *y = nullptr;
+  bf16 *a1 = nullptr, *xs = nullptr, *h1 = nullptr, *a2 = nullptr;
+  float *st1 = nullptr, *st2 = nullptr;
+};
+
+struct StLayer {
+  std::string prefix;
+  int C = 0, heads = 0, D = 0, H = 0, W = 0;
+  int norm_w, norm_b, pin_w, pin_b, q1_w, k1_w, v1_w, o1_w, o1_b, ff1_w, ff1_b, ff2_w, ff2_b, q2_w, k2_w, v2_w, o2_w, o2_b,
+      ln1_w, ln1_b, ln2_w, ln2_b, ln3_w, ln3_b, pout_w, pout_b;
+  Packed pinf, pint, qkvf, qkvt, o1f, o1t, q2f, q2t, o2f, o2t, ff1f, ff1t, ff2f, ff2t, poutf, poutt;
+  Tn *x = nullptr, *y = nullptr;
+  bf16 *n = nullptr, *t0 = nullptr, *l1 = nullptr, *qkv = nullptr, *att = nullptr, *t1 = nullptr, *l2 = nullptr,
+       *q2 = nullptr, *att2 = nullptr, *t2 = nullptr, *l3 = nullptr, *g = nullptr, *gg = nullptr, *t3 = nullptr;
+  float *stn = nullptr, *ls1 = nullptr, *ls2 = nullptr, *ls3 = nullptr, *lse = nullptr;
+};
+
+struct Layer {
+  int kind;   // 0 stem conv, 1 res, 2 st
+  int idx;    // index into res / st vectors
+};
+
+struct UNet {
+  encdiff_unet_config cfg;
+  std::vector<ParamInfo> params;
+  std::vector<ResLayer> res;
+  std::vector<StLayer> st;
+  std::vector<std::vector<Layer>> in_blocks, out_blocks;
+  std::vector<Layer> mid;
+  int head_ch = 0;
+  int film_cols = 0;         // F = sum 2*cout
+  int emb_ch = 0;            // 4 * model_channels
+  // stem / head / time-embed parameters
+  int stem_w, stem_b, te0_w, te0_b, te2_w, te2_b, hn_w, hn_b, hc_w, hc_b;
+  Packed stemf, stemt, te0f, te0t, te2f, te2t, filmf, filmt, headf, headt;
+  long long film_bias_off = 0;
+  // packed arena layout
+  std::vector<PackEntry> table;     // src pointers resolved at bind()
+  std::vector<int> table_src, table_src2;   // parameter index of each entry
+  long long pack_total = 0;         // total source elements walked by the pack kernel
+  size_t table_bytes = 0, bf16_bytes = 0, f32_bytes = 0;
+  // binding
+  std::vector<const float*> pptr;
+  std::vector<float*> gptr;
+  char* packed = nullptr;
+  bool bound = false;
+  // plan (per batch / workspace)
+  int planB = -1;
+  char* plan_ws = nullptr;
+  bool plan_training = false;
+  size_t ws_bytes_persist = 0, ws_bytes_scratch = 0;
+  std::vector<Tn> tn;               // block-level tensors; [0] = stem output
+  std::vector<int> hs_of_in_block;  // tn index of each input block's output
+  bf16 *temb = nullptr, *a1e = nullptr, *a2e = nullptr, *cols = nullptr, *aH = nullptr, *dyH = nullptr, *dfilm = nullptr;
+  float *z1 = nullptr, *z2 = nullptr, *film = nullptr, *stH = nullptr, *yH = nullptr;
+  char* scratch = nullptr;
+  // tensor-map caches
+  std::map<std::tuple<const void*, int, int, int, int>, CUtensorMap> act_maps;
+  std::map<std::tuple<const void*, long long, long long, int>, CUtensorMap> w_maps;
+
+  bf16* pbf() const { return reinterpret_cast<bf16*>(packed + table_bytes); }
+  float* pf32() const { return reinterpret_cast<float*>(packed + table_bytes + bf16_bytes); }
+};
+
+int unet_build(UNet* u, const encdiff_unet_config* cfg);          // architecture + params + pack table
+int unet_plan(UNet* u, int B, char* ws, bool training);           // assign workspace pointers
+size_t unet_workspace_bytes(UNet* u, int B, bool training);
+int unet_forward(UNet* u, int B, const float* x, const float* noise, const float* sa, const float* sb, const float* t,
+                 const float* ctx, float* out, float* xt, cudaStream_t s);
+int unet_backward(UNet* u, int B, const float* dout, const float* ctx, float* dx, float* dctx, cudaStream_t s);
+
+}  // namespace edb

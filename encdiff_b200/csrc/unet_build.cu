@@ -1,0 +1,318 @@
+// Architecture walk, parameter inventory and packed-weight layout of the UNet (host only).
+#include <string.h>
+
+#include "host.cuh"
+#include "unet.cuh"
+
+namespace edb {
+
+static long long ceil_to(long long v, long long m) { return (v + m - 1) / m * m; }
+
+struct Builder {
+  UNet* u;
+  long long bf_off = 0;    // bf16 arena cursor (elements)
+  long long f32_off = 0;   // fp32 arena cursor (elements)
+
+  int add_param(const std::string& name, std::initializer_list<long long> shape) {
+    ParamInfo p;
+    p.name = name;
+    p.ndim = static_cast<int>(shape.size());
+    p.numel = 1;
+    int i = 0;
+    for (long long s : shape) {
+      p.shape[i++] = s;
+      p.numel *= s;
+    }
+    for (; i < 4; ++i) p.shape[i] = 1;
+    u->params.push_back(p);
+    return static_cast<int>(u->params.size()) - 1;
+  }
+
+  Packed alloc(long long rows, long long K) {
+    Packed pk;
+    pk.rows = ceil_to(rows, 128);
+    pk.K = K;
+    pk.off = bf_off;
+    bf_off += ceil_to(pk.rows * pk.K, 512);   // keep every operand 1 KB aligned
+    return pk;
+  }
+
+  void entry(int kind, int src, int src2, long long dst_off, int rows, int cin, int taps, int cin_pad, int rows_pad,
+             long long dst_ld, int row0, int col0) {
+    PackEntry e;
+    memset(&e, 0, sizeof(e));
+    e.kind = kind;
+    e.dst_off = dst_off;
+    e.rows = rows;
+    e.cin = cin;
+    e.taps = taps;
+    e.cin_pad = cin_pad;
+    e.rows_pad = rows_pad;
+    e.dst_ld = static_cast<int>(dst_ld);
+    e.row0 = row0;
+    e.col0 = col0;
+    e.prefix = u->pack_total;
+    u->pack_total += u->params[src].numel;
+    u->table.push_back(e);
+    u->table_src.push_back(src);
+    u->table_src2.push_back(src2);
+  }
+
+  // weight [rows, cin, taps] -> forward operand [rows_pad, taps*ceil64(cin)] placed at (row0, col0) of `dst`
+  void pack_fwd(const Packed& dst, int src, int rows, int cin, int taps, int row0, int col0) {
+    entry(0, src, -1, dst.off, rows, cin, taps, static_cast<int>(ceil_to(cin, 64)), 0, dst.K, row0, col0);
+  }
+  // transposed operand: dst[row0 + ci][col0 + tap*ceil64(rows) + r]
+  void pack_t(const Packed& dst, int src, int rows, int cin, int taps, int row0, int col0) {
+    entry(1, src, -1, dst.off, rows, cin, taps, 0, static_cast<int>(ceil_to(rows, 64)), dst.K, row0, col0);
+  }
+};
+
+static void build_res(Builder& b, ResLayer& l, int emb_ch) {
+  UNet* u = b.u;
+  const std::string& p = l.prefix;
+  const int cin = l.c0 + l.c1;
+  l.gn1_w = b.add_param(p + ".in_layers.0.weight", {cin});
+  l.gn1_b = b.add_param(p + ".in_layers.0.bias", {cin});
+  l.conv1_w = b.add_param(p + ".in_layers.2.weight", {l.cout, cin, 3, 3});
+  l.conv1_b = b.add_param(p + ".in_layers.2.bias", {l.cout});
+  l.emb_w = b.add_param(p + ".emb_layers.1.weight", {2 * l.cout, emb_ch});
+  l.emb_b = b.add_param(p + ".emb_layers.1.bias", {2 * l.cout});
+  l.gn2_w = b.add_param(p + ".out_layers.0.weight", {l.cout});
+  l.gn2_b = b.add_param(p + ".out_layers.0.bias", {l.cout});
+  l.conv2_w = b.add_param(p + ".out_layers.3.weight", {l.cout, l.cout, 3, 3});
+  l.conv2_b = b.add_param(p + ".out_layers.3.bias", {l.cout});
+  l.skipconv = cin != l.cout;
+  if (l.skipconv) {
+    l.skip_w = b.add_param(p + ".skip_connection.weight", {l.cout, cin, 1, 1});
+    l.skip_b = b.add_param(p + ".skip_connection.bias", {l.cout});
+  }
+  l.film_off = u->film_cols;
+  u->film_cols += 2 * l.cout;
+  const long long cin64 = ceil_to(cin, 64), cout64 = ceil_to(l.cout, 64);
+  l.w1f = b.alloc(l.cout, 9 * cin64);
+  b.pack_fwd(l.w1f, l.conv1_w, l.cout, cin, 9, 0, 0);
+  l.w1t = b.alloc(cin, 9 * cout64);
+  b.pack_t(l.w1t, l.conv1_w, l.cout, cin, 9, 0, 0);
+  l.w2f = b.alloc(l.cout, 9 * cout64 + (l.skipconv ? cin64 : 0));
+  b.pack_fwd(l.w2f, l.conv2_w, l.cout, l.cout, 9, 0, 0);
+  l.w2t = b.alloc(l.cout, 9 * cout64);
+  b.pack_t(l.w2t, l.conv2_w, l.cout, l.cout, 9, 0, 0);
+  if (l.skipconv) {
+    b.pack_fwd(l.w2f, l.skip_w, l.cout, cin, 1, 0, static_cast<int>(9 * cout64));
+    l.wst = b.alloc(cin, cout64);
+    b.pack_t(l.wst, l.skip_w, l.cout, cin, 1, 0, 0);
+    l.bias2_off = b.f32_off;
+    b.f32_off += ceil_to(l.cout, 64);
+    b.entry(3, l.conv2_b, l.skip_b, l.bias2_off, l.cout, 1, 1, 0, 0, 0, 0, 0);
+  }
+}
+
+static void build_st(Builder& b, StLayer& l, int ctx_dim) {
+  const std::string& p = l.prefix;
+  const int C = l.C;
+  l.norm_w = b.add_param(p + ".norm.weight", {C});
+  l.norm_b = b.add_param(p + ".norm.bias", {C});
+  l.pin_w = b.add_param(p + ".proj_in.weight", {C, C, 1, 1});
+  l.pin_b = b.add_param(p + ".proj_in.bias", {C});
+  const std::string t = p + ".transformer_blocks.0";
+  l.q1_w = b.add_param(t + ".attn1.to_q.weight", {C, C});
+  l.k1_w = b.add_param(t + ".attn1.to_k.weight", {C, C});
+  l.v1_w = b.add_param(t + ".attn1.to_v.weight", {C, C});
+  l.o1_w = b.add_param(t + ".attn1.to_out.0.weight", {C, C});
+  l.o1_b = b.add_param(t + ".attn1.to_out.0.bias", {C});
+  l.ff1_w = b.add_param(t + ".ff.net.0.proj.weight", {8 * C, C});
+  l.ff1_b = b.add_param(t + ".ff.net.0.proj.bias", {8 * C});
+  l.ff2_w = b.add_param(t + ".ff.net.2.weight", {C, 4 * C});
+  l.ff2_b = b.add_param(t + ".ff.net.2.bias", {C});
+  l.q2_w = b.add_param(t + ".attn2.to_q.weight", {C, C});
+  l.k2_w = b.add_param(t + ".attn2.to_k.weight", {C, ctx_dim});
+  l.v2_w = b.add_param(t + ".attn2.to_v.weight", {C, ctx_dim});
+  l.o2_w = b.add_param(t + ".attn2.to_out.0.weight", {C, C});
+  l.o2_b = b.add_param(t + ".attn2.to_out.0.bias", {C});
+  l.ln1_w = b.add_param(t + ".norm1.weight", {C});
+  l.ln1_b = b.add_param(t + ".norm1.bias", {C});
+  l.ln2_w = b.add_param(t + ".norm2.weight", {C});
+  l.ln2_b = b.add_param(t + ".norm2.bias", {C});
+  l.ln3_w = b.add_param(t + ".norm3.weight", {C});
+  l.ln3_b = b.add_param(t + ".norm3.bias", {C});
+  l.pout_w = b.add_param(p + ".proj_out.weight", {C, C, 1, 1});
+  l.pout_b = b.add_param(p + ".proj_out.bias", {C});
+  auto lin = [&](Packed& f, Packed& tt, int src, int rows, int cin) {
+    f = b.alloc(rows, ceil_to(cin, 64));
+    b.pack_fwd(f, src, rows, cin, 1, 0, 0);
+    tt = b.alloc(cin, ceil_to(rows, 64));
+    b.pack_t(tt, src, rows, cin, 1, 0, 0);
+  };
+  lin(l.pinf, l.pint, l.pin_w, C, C);
+  l.qkvf = b.alloc(3 * C, C);
+  l.qkvt = b.alloc(C, 3 * C);
+  const int qkv_src[3] = {l.q1_w, l.k1_w, l.v1_w};
+  for (int i = 0; i < 3; ++i) {
+    b.pack_fwd(l.qkvf, qkv_src[i], C, C, 1, i * C, 0);
+    b.pack_t(l.qkvt, qkv_src[i], C, C, 1, 0, i * C);
+  }
+  lin(l.o1f, l.o1t, l.o1_w, C, C);
+  lin(l.q2f, l.q2t, l.q2_w, C, C);
+  lin(l.o2f, l.o2t, l.o2_w, C, C);
+  lin(l.ff1f, l.ff1t, l.ff1_w, 8 * C, C);
+  lin(l.ff2f, l.ff2t, l.ff2_w, C, 4 * C);
+  lin(l.poutf, l.poutt, l.pout_w, C, C);
+}
+
+int unet_build(UNet* u, const encdiff_unet_config* c) {
+  u->cfg = *c;
+  EDB_REQUIRE(c->model_channels > 0 && c->model_channels % 64 == 0, "model_channels must be a multiple of 64");
+  EDB_REQUIRE(c->use_scale_shift_norm == 1, "only use_scale_shift_norm=True is implemented");
+  EDB_REQUIRE(c->resblock_updown == 1, "only resblock_updown=True is implemented");
+  EDB_REQUIRE(c->transformer_depth == 1, "only transformer_depth=1 is implemented");
+  EDB_REQUIRE(c->in_channels * 9 <= 64, "in_channels*9 must fit one 64-wide K chunk");
+  EDB_REQUIRE(c->out_channels <= 8, "out_channels must be <= 8");
+  EDB_REQUIRE(c->n_channel_mult >= 1 && c->n_channel_mult <= 8 && c->n_attention_resolutions <= 8, "bad config");
+  EDB_REQUIRE(c->num_heads > 0 && c->latent_unit >= 1 && c->latent_unit <= 32, "latent_unit must be in 1..32");
+  Builder b;
+  b.u = u;
+  const int mc = c->model_channels;
+  u->emb_ch = 4 * mc;
+  u->te0_w = b.add_param("time_embed.0.weight", {u->emb_ch, mc});
+  u->te0_b = b.add_param("time_embed.0.bias", {u->emb_ch});
+  u->te2_w = b.add_param("time_embed.2.weight", {u->emb_ch, u->emb_ch});
+  u->te2_b = b.add_param("time_embed.2.bias", {u->emb_ch});
+  auto in_attn = [&](int ds) {
+    for (int i = 0; i < c->n_attention_resolutions; ++i)
+      if (c->attention_resolutions[i] == ds) return true;
+    return false;
+  };
+  auto new_res = [&](const std::string& prefix, int c0, int c1, int cout, bool up, bool down, int H) {
+    ResLayer l;
+    l.prefix = prefix;
+    l.c0 = c0;
+    l.c1 = c1;
+    l.cout = cout;
+    l.up = up;
+    l.down = down;
+    l.Hin = l.Win = H;
+    l.Hout = l.Wout = up ? 2 * H : (down ? H / 2 : H);
+    u->res.push_back(l);
+    return Layer{1, static_cast<int>(u->res.size()) - 1};
+  };
+  auto new_st = [&](const std::string& prefix, int C, int H) {
+    StLayer l;
+    l.prefix = prefix;
+    l.C = C;
+    l.heads = c->num_heads;
+    l.D = C / c->num_heads;
+    l.H = l.W = H;
+    u->st.push_back(l);
+    return Layer{2, static_cast<int>(u->st.size()) - 1};
+  };
+  // ---- structure (openaimodel_enc.py:516-682) -----------------------------------------------------------------
+  std::vector<int> chans;
+  int ch = mc, ds = 1, H = c->image_size;
+  u->in_blocks.push_back({Layer{0, 0}});
+  chans.push_back(ch);
+  for (int level = 0; level < c->n_channel_mult; ++level) {
+    const int mult = c->channel_mult[level];
+    for (int r = 0; r < c->num_res_blocks; ++r) {
+      const std::string pre = "input_blocks." + std::to_string(u->in_blocks.size());
+      std::vector<Layer> blk;
+      blk.push_back(new_res(pre + ".0", ch, 0, mult * mc, false, false, H));
+      ch = mult * mc;
+      if (in_attn(ds)) blk.push_back(new_st(pre + ".1", ch, H));
+      u->in_blocks.push_back(blk);
+      chans.push_back(ch);
+    }
+    if (level != c->n_channel_mult - 1) {
+      const std::string pre = "input_blocks." + std::to_string(u->in_blocks.size());
+      u->in_blocks.push_back({new_res(pre + ".0", ch, 0, ch, false, true, H)});
+      chans.push_back(ch);
+      ds *= 2;
+      H /= 2;
+    }
+  }
+  u->mid.push_back(new_res("middle_block.0", ch, 0, ch, false, false, H));
+  u->mid.push_back(new_st("middle_block.1", ch, H));
+  u->mid.push_back(new_res("middle_block.2", ch, 0, ch, false, false, H));
+  for (int level = c->n_channel_mult - 1; level >= 0; --level) {
+    const int mult = c->channel_mult[level];
+    for (int i = 0; i <= c->num_res_blocks; ++i) {
+      const int ich = chans.back();
+      chans.pop_back();
+      const std::string pre = "output_blocks." + std::to_string(u->out_blocks.size());
+      std::vector<Layer> blk;
+      blk.push_back(new_res(pre + ".0", ch, ich, mc * mult, false, false, H));
+      ch = mc * mult;
+      if (in_attn(ds)) blk.push_back(new_st(pre + ".1", ch, H));
+      if (level && i == c->num_res_blocks) {
+        blk.push_back(new_res(pre + "." + std::to_string(blk.size()), ch, 0, ch, true, false, H));
+        ds /= 2;
+        H *= 2;
+      }
+      u->out_blocks.push_back(blk);
+    }
+  }
+  u->head_ch = ch;
+  // ---- parameters in reference registration order + packed layout ---------------------------------------------
+  u->stem_w = b.add_param("input_blocks.0.0.weight", {mc, c->in_channels, 3, 3});
+  u->stem_b = b.add_param("input_blocks.0.0.bias", {mc});
+  auto build_layers = [&](std::vector<Layer>& ls) -> int {
+    for (Layer& l : ls) {
+      if (l.kind == 1) {
+        ResLayer& r = u->res[l.idx];
+        if (r.c1 > 0 && (r.c0 % 64) != 0) return 1;
+        build_res(b, r, u->emb_ch);
+      } else if (l.kind == 2) {
+        StLayer& s = u->st[l.idx];
+        if (s.D != 8 && s.D != 16 && s.D != 32 && s.D != 64) return 2;
+        build_st(b, s, c->context_dim);
+      }
+    }
+    return 0;
+  };
+  for (size_t i = 1; i < u->in_blocks.size(); ++i)
+    EDB_REQUIRE(build_layers(u->in_blocks[i]) == 0, "unsupported channel / head configuration");
+  EDB_REQUIRE(build_layers(u->mid) == 0, "unsupported channel / head configuration");
+  for (auto& blk : u->out_blocks) EDB_REQUIRE(build_layers(blk) == 0, "unsupported channel / head configuration");
+  u->hn_w = b.add_param("out.0.weight", {ch});
+  u->hn_b = b.add_param("out.0.bias", {ch});
+  u->hc_w = b.add_param("out.2.weight", {c->out_channels, mc, 3, 3});
+  u->hc_b = b.add_param("out.2.bias", {c->out_channels});
+  EDB_REQUIRE(ch == mc, "head expects model_channels inputs (channel_mult[0] must be 1)");
+  // stem: reference-order flat K (ci*9 + tap), one 64-wide chunk
+  const int k_stem = c->in_channels * 9;
+  u->stemf = b.alloc(mc, 64);
+  b.entry(4, u->stem_w, -1, u->stemf.off, mc, c->in_channels, 9, 0, 0, 64, 0, 0);
+  u->stemt = b.alloc(k_stem, ceil_to(mc, 64));
+  b.entry(5, u->stem_w, -1, u->stemt.off, mc, c->in_channels, 9, 0, 0, u->stemt.K, 0, 0);
+  // time embedding MLP
+  auto lin = [&](Packed& f, Packed& tt, int src, int rows, int cin) {
+    f = b.alloc(rows, ceil_to(cin, 64));
+    b.pack_fwd(f, src, rows, cin, 1, 0, 0);
+    tt = b.alloc(cin, ceil_to(rows, 64));
+    b.pack_t(tt, src, rows, cin, 1, 0, 0);
+  };
+  lin(u->te0f, u->te0t, u->te0_w, u->emb_ch, mc);
+  lin(u->te2f, u->te2t, u->te2_w, u->emb_ch, u->emb_ch);
+  // all ResBlock emb_layers stacked into one [F, emb_ch] operand (K2 of SURVEY.md §2.3)
+  u->filmf = b.alloc(u->film_cols, u->emb_ch);
+  u->filmt = b.alloc(u->emb_ch, u->film_cols);
+  u->film_bias_off = b.f32_off;
+  b.f32_off += ceil_to(u->film_cols, 64);
+  for (ResLayer& r : u->res) {
+    b.pack_fwd(u->filmf, r.emb_w, 2 * r.cout, u->emb_ch, 1, r.film_off, 0);
+    b.pack_t(u->filmt, r.emb_w, 2 * r.cout, u->emb_ch, 1, 0, r.film_off);
+    b.entry(2, r.emb_b, -1, u->film_bias_off, 2 * r.cout, 1, 1, 0, 0, 0, 0, r.film_off);
+  }
+  // head conv
+  u->headf = b.alloc(c->out_channels, 9 * ceil_to(mc, 64));
+  b.pack_fwd(u->headf, u->hc_w, c->out_channels, mc, 9, 0, 0);
+  u->headt = b.alloc(mc, 9 * 64);
+  b.pack_t(u->headt, u->hc_w, c->out_channels, mc, 9, 0, 0);
+
+  u->table_bytes = static_cast<size_t>(ceil_to(static_cast<long long>(u->table.size() * sizeof(PackEntry)), 1024));
+  u->bf16_bytes = static_cast<size_t>(ceil_to(b.bf_off * 2, 1024));
+  u->f32_bytes = static_cast<size_t>(ceil_to(b.f32_off * 4, 1024));
+  return EDB_OK;
+}
+
+}  // namespace edb

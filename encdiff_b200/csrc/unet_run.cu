@@ -1,0 +1,449 @@
+// Workspace plan and the forward / backward launch sequences of the UNet (host only; every call enqueues kernels).
+#include <string.h>
+
+#include "host.cuh"
+#include "unet.cuh"
+
+namespace edb {
+
+// ---------------------------------------------------------------------------------------------------------------
+// workspace plan
+// ---------------------------------------------------------------------------------------------------------------
+struct Bump {
+  char* base;
+  size_t off = 0;
+  template <class X>
+  X* take(size_t n) {
+    off = (off + 1023) & ~size_t(1023);
+    X* p = reinterpret_cast<X*>(base + off);
+    off += n * sizeof(X);
+    return p;
+  }
+};
+
+static size_t res_scratch(const ResLayer& l, int B) {
+  const size_t m = static_cast<size_t>(B) * l.Hout * l.Wout;
+  return (m * l.cout * 2 + m * (l.c0 + l.c1)) * 2 + 8192;   // da2, dh1, da1
+}
+static size_t st_scratch(const StLayer& l, int B) {
+  const size_t m = static_cast<size_t>(B) * l.H * l.W;
+  return m * l.C * 27 * 2 + 32768;   // dt3 dl3 dt2 datt2 dq2 dl2 dt1 datt dl1 dt0 dn (11) + dqkv (3) + dgg (4) + dg (8)
+}
+
+int unet_plan(UNet* u, int B, char* ws, bool training) {
+  if (u->planB == B && u->plan_ws == ws && u->plan_training == training && ws != nullptr) return EDB_OK;
+  const encdiff_unet_config& c = u->cfg;
+  Bump a;
+  a.base = ws;
+  const int mc = c.model_channels, S = c.image_size;
+  const size_t M0 = static_cast<size_t>(B) * S * S;
+  u->temb = a.take<bf16>(static_cast<size_t>(B) * mc);
+  u->z1 = a.take<float>(static_cast<size_t>(B) * u->emb_ch);
+  u->a1e = a.take<bf16>(static_cast<size_t>(B) * u->emb_ch);
+  u->z2 = a.take<float>(static_cast<size_t>(B) * u->emb_ch);
+  u->a2e = a.take<bf16>(static_cast<size_t>(B) * u->emb_ch);
+  u->film = a.take<float>(static_cast<size_t>(B) * u->film_cols);
+  u->cols = a.take<bf16>(M0 * 64);
+  u->aH = a.take<bf16>(M0 * mc);
+  u->stH = a.take<float>(static_cast<size_t>(B) * 64);
+  u->yH = a.take<float>(M0 * c.out_channels);
+  if (training) {
+    u->dfilm = a.take<bf16>(static_cast<size_t>(B) * u->film_cols);
+    u->dyH = a.take<bf16>(M0 * 8);
+  }
+  // block-level tensors
+  u->tn.clear();
+  u->tn.reserve(1 + u->res.size() + u->st.size());
+  auto new_tn = [&](int C, int H) {
+    Tn t;
+    t.C = C;
+    t.H = t.W = H;
+    t.p = a.take<bf16>(static_cast<size_t>(B) * H * H * C);
+    if (training) t.g = a.take<bf16>(static_cast<size_t>(B) * H * H * C);
+    u->tn.push_back(t);
+    return &u->tn.back();
+  };
+  Tn* h = new_tn(mc, S);   // stem output
+  u->hs_of_in_block.clear();
+  std::vector<Tn*> hs;
+  auto plan_layers = [&](std::vector<Layer>& ls, Tn* skip) {
+    bool first = true;
+    for (Layer& ly : ls) {
+      if (ly.kind == 1) {
+        ResLayer& l = u->res[ly.idx];
+        const size_t mi = static_cast<size_t>(B) * l.Hin * l.Win, mo = static_cast<size_t>(B) * l.Hout * l.Wout;
+        (void)mi;
+        l.x0 = h;
+        l.x1 = (first && skip) ? skip : nullptr;
+        const int cin = l.c0 + l.c1;
+        l.a1 = a.take<bf16>(mo * cin);
+        l.xs = (l.up || l.down) ? a.take<bf16>(mo * cin) : nullptr;
+        l.st1 = a.take<float>(static_cast<size_t>(B) * 64);
+        l.h1 = a.take<bf16>(mo * l.cout);
+        l.st2 = a.take<float>(static_cast<size_t>(B) * 64);
+        l.a2 = a.take<bf16>(mo * l.cout);
+        l.y = new_tn(l.cout, l.Hout);
+        h = l.y;
+      } else if (ly.kind == 2) {
+        StLayer& l = u->st[ly.idx];
+        const size_t m = static_cast<size_t>(B) * l.H * l.W;
+        const int C = l.C;
+        l.x = h;
+        l.n = a.take<bf16>(m * C);
+        l.stn = a.take<float>(static_cast<size_t>(B) * 64);
+        l.t0 = a.take<bf16>(m * C);
+        l.l1 = a.take<bf16>(m * C);
+        l.ls1 = a.take<float>(m * 2);
+        l.qkv = a.take<bf16>(m * 3 * C);
+        l.att = a.take<bf16>(m * C);
+        l.lse = a.take<float>(m * l.heads);
+        l.t1 = a.take<bf16>(m * C);
+        l.l2 = a.take<bf16>(m * C);
+        l.ls2 = a.take<float>(m * 2);
+        l.q2 = a.take<bf16>(m * C);
+        l.att2 = a.take<bf16>(m * C);
+        l.t2 = a.take<bf16>(m * C);
+        l.l3 = a.take<bf16>(m * C);
+        l.ls3 = a.take<float>(m * 2);
+        l.g = a.take<bf16>(m * 8 * C);
+        l.gg = a.take<bf16>(m * 4 * C);
+        l.t3 = a.take<bf16>(m * C);
+        l.y = new_tn(C, l.H);
+        h = l.y;
+      }
+      first = false;
+    }
+  };
+  hs.push_back(h);
+  for (size_t i = 1; i < u->in_blocks.size(); ++i) {
+    plan_layers(u->in_blocks[i], nullptr);
+    hs.push_back(h);
+  }
+  plan_layers(u->mid, nullptr);
+  for (auto& blk : u->out_blocks) {
+    Tn* skip = hs.back();
+    hs.pop_back();
+    plan_layers(blk, skip);
+  }
+  u->ws_bytes_persist = (a.off + 1023) & ~size_t(1023);
+  size_t sc = static_cast<size_t>(B) * (u->emb_ch * 4) * 2 + M0 * (64 + mc) * 2 + 16384;   // emb MLP grads, dcols, daH
+  if (training) {
+    for (const ResLayer& l : u->res) sc = std::max(sc, res_scratch(l, B));
+    for (const StLayer& l : u->st) sc = std::max(sc, st_scratch(l, B));
+  } else {
+    sc = 0;
+  }
+  u->ws_bytes_scratch = sc;
+  u->scratch = ws ? ws + u->ws_bytes_persist : nullptr;
+  if (ws) {
+    u->planB = B;
+    u->plan_ws = ws;
+    u->plan_training = training;
+    u->act_maps.clear();
+  } else {
+    u->planB = -1;
+  }
+  return EDB_OK;
+}
+
+size_t unet_workspace_bytes(UNet* u, int B, bool training) {
+  unet_plan(u, B, nullptr, training);
+  return u->ws_bytes_persist + u->ws_bytes_scratch + 1024;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// launch helpers
+// ---------------------------------------------------------------------------------------------------------------
+struct Src {
+  const bf16* p;
+  int C;
+  int taps;
+};
+
+struct Exec {
+  UNet* u;
+  int B;
+  cudaStream_t s;
+  int err = 0;
+
+  // rc is a cudaError_t returned by a launcher
+  bool fail(int rc, const char* what) {
+    if (rc != 0 && err == 0) {
+      err = EDB_ERR_CUDA;
+      set_last_error(std::string(what) + ": " + cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    }
+    return err != 0;
+  }
+  void invalid(const char* what) {
+    if (err == 0) {
+      err = EDB_ERR_INVALID;
+      set_last_error(what);
+    }
+  }
+
+  const CUtensorMap* act_map(const bf16* p, int C, int H, int W, const TileGeom& g) {
+    auto key = std::make_tuple(static_cast<const void*>(p), C, H, W, B);
+    auto it = u->act_maps.find(key);
+    if (it != u->act_maps.end()) return &it->second;
+    CUtensorMap m;
+    int rc = make_act_tmap(&m, p, C, H, W, B, g);
+    if (rc) {
+      if (!err) err = rc;
+      return nullptr;
+    }
+    return &u->act_maps.emplace(key, m).first->second;
+  }
+  const CUtensorMap* w_map(const bf16* p, long long K, long long rows, int bn) {
+    auto key = std::make_tuple(static_cast<const void*>(p), K, rows, bn);
+    auto it = u->w_maps.find(key);
+    if (it != u->w_maps.end()) return &it->second;
+    CUtensorMap m;
+    int rc = make_w_tmap(&m, p, K, rows, bn);
+    if (rc) {
+      if (!err) err = rc;
+      return nullptr;
+    }
+    return &u->w_maps.emplace(key, m).first->second;
+  }
+
+  // out[M, N] = act(sum_s A_s * W^T + bias) + res ;  W = packed operand `pk` starting at row `row0`
+  void gemm(std::initializer_list<Src> srcs, int H, int W, const Packed& pk, long long row0, int N, int tap_sign,
+            const float* bias, const bf16* res, int ldres, int act, bool fp32, void* out, int ld) {
+    if (err) return;
+    SgemmParams p;
+    memset(&p, 0, sizeof(p));
+    if (!make_geom(H, W, &p.g)) {
+      invalid("gemm geometry: H*W must be a power of two, W <= 128");
+      return;
+    }
+    int i = 0;
+    long long K = 0;
+    for (const Src& sc : srcs) {
+      const CUtensorMap* m = act_map(sc.p, sc.C, H, W, p.g);
+      if (!m) return;
+      p.amap[i] = *m;
+      p.src_chunks[i] = (sc.C + 63) / 64;
+      p.src_taps[i] = sc.taps;
+      K += 64LL * p.src_chunks[i] * sc.taps;
+      ++i;
+    }
+    if (K != pk.K) {
+      invalid("internal: GEMM K mismatch with packed operand");
+      return;
+    }
+    p.nsrc = i;
+    const int bn = sgemm_pick_bn(N);
+    const CUtensorMap* wm = w_map(u->pbf() + pk.off + row0 * pk.K, pk.K, pk.rows - row0, bn);
+    if (!wm) return;
+    p.bmap = *wm;
+    p.tap_sign = tap_sign;
+    p.M = B * H * W;
+    p.N = N;
+    p.bias = bias;
+    p.res = res;
+    p.ldres = ldres;
+    p.act = act;
+    p.out_fp32 = fp32 ? 1 : 0;
+    p.out0 = out;
+    p.ld0 = ld;
+    p.split_col = 1 << 30;
+    fail(launch_sgemm(p, bn, s), "sgemm");
+  }
+
+  // grad[p, q(+q_off), tap] += sum_pix dy[pix, p_off + p] * x[pix, q]
+  void wgrad(const bf16* dy, int Cdy, int p_off, int Cp, const bf16* x, int Cx, int Cq, int H, int W, int taps,
+             float* out, long long stride_p, long long stride_q, long long stride_tap, int q_off) {
+    if (err || !out) return;
+    WgradParams p;
+    memset(&p, 0, sizeof(p));
+    if (!make_geom(H, W, &p.g)) {
+      invalid("wgrad geometry: H*W must be a power of two, W <= 128");
+      return;
+    }
+    const CUtensorMap* pm = act_map(dy, Cdy, H, W, p.g);
+    const CUtensorMap* qm = act_map(x, Cx, H, W, p.g);
+    if (!pm || !qm) return;
+    p.pmap = *pm;
+    p.qmap = *qm;
+    p.taps = taps;
+    p.m_tiles = (B * H * W + 127) / 128;
+    p.Cp = Cp;
+    p.Cq = Cq;
+    p.p_off = p_off;
+    p.out = out;
+    p.stride_p = stride_p;
+    p.stride_q = stride_q;
+    p.stride_tap = stride_tap;
+    p.q_off = q_off;
+    const int bn = Cq <= 64 ? 64 : 128;
+    const long long ctas = static_cast<long long>((Cp + 127) / 128) * taps * ((Cq + bn - 1) / bn);
+    // enough CTAs to fill the chip, but keep the number of fp32 atomics (weights x splits) bounded
+    long long splits = (2 * 148 + ctas - 1) / ctas;
+    const long long weights = static_cast<long long>(Cp) * Cq * taps;
+    const long long max_by_atomics = std::max(1LL, (8LL << 20) / std::max(1LL, weights));
+    splits = std::min(splits, max_by_atomics);
+    splits = std::max(1LL, std::min<long long>(splits, p.m_tiles));
+    fail(launch_wgrad(p, bn, static_cast<int>(splits), s), "wgrad");
+  }
+
+  void colsum(const bf16* x, long long M, int ld, int col0, int N, float* d0, float* d1 = nullptr) {
+    if (err || !d0) return;
+    fail(launch_colsum(x, M, ld, col0, N, d0, d1, s), "colsum");
+  }
+  const float* P(int idx) const { return u->pptr[idx]; }
+  float* G(int idx) const { return u->gptr.empty() ? nullptr : u->gptr[idx]; }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------------------------------
+static GnParams gn_res1(const ResLayer& l, Exec& e) {
+  GnParams p;
+  memset(&p, 0, sizeof(p));
+  p.x0 = l.x0->p;
+  p.C0 = l.c0;
+  p.x1 = l.x1 ? l.x1->p : nullptr;
+  p.C1 = l.c1;
+  p.H = l.Hin;
+  p.W = l.Win;
+  p.gamma = e.P(l.gn1_w);
+  p.beta = e.P(l.gn1_b);
+  p.eps = 1e-5f;
+  p.silu = 1;
+  p.resample = l.down ? RESAMPLE_DOWN : (l.up ? RESAMPLE_UP : RESAMPLE_NONE);
+  p.stats = l.st1;
+  p.act = l.a1;
+  p.xs = l.xs;
+  return p;
+}
+static GnParams gn_res2(const ResLayer& l, Exec& e) {
+  GnParams p;
+  memset(&p, 0, sizeof(p));
+  p.x0 = l.h1;
+  p.C0 = l.cout;
+  p.H = l.Hout;
+  p.W = l.Wout;
+  p.gamma = e.P(l.gn2_w);
+  p.beta = e.P(l.gn2_b);
+  p.film = e.u->film;
+  p.ldfilm = e.u->film_cols;
+  p.film_off = l.film_off;
+  p.eps = 1e-5f;
+  p.silu = 1;
+  p.resample = RESAMPLE_NONE;
+  p.stats = l.st2;
+  p.act = l.a2;
+  return p;
+}
+
+// ResBlock._forward (openaimodel_enc.py:255-275)
+static void res_forward(ResLayer& l, Exec& e) {
+  if (e.err) return;
+  const int cin = l.c0 + l.c1;
+  e.fail(launch_gn_fwd(gn_res1(l, e), e.B, e.s), "gn1");
+  e.gemm({{l.a1, cin, 9}}, l.Hout, l.Wout, l.w1f, 0, l.cout, 1, e.P(l.conv1_b), nullptr, 0, ACT_NONE, false, l.h1, l.cout);
+  e.fail(launch_gn_fwd(gn_res2(l, e), e.B, e.s), "gn2");
+  if (l.skipconv) {
+    const float* bias = e.u->pf32() + l.bias2_off;
+    if (l.x1)
+      e.gemm({{l.a2, l.cout, 9}, {l.x0->p, l.c0, 1}, {l.x1->p, l.c1, 1}}, l.Hout, l.Wout, l.w2f, 0, l.cout, 1, bias,
+             nullptr, 0, ACT_NONE, false, l.y->p, l.cout);
+    else
+      e.gemm({{l.a2, l.cout, 9}, {l.x0->p, l.c0, 1}}, l.Hout, l.Wout, l.w2f, 0, l.cout, 1, bias, nullptr, 0, ACT_NONE,
+             false, l.y->p, l.cout);
+  } else {
+    const bf16* skip = (l.up || l.down) ? l.xs : l.x0->p;
+    e.gemm({{l.a2, l.cout, 9}}, l.Hout, l.Wout, l.w2f, 0, l.cout, 1, e.P(l.conv2_b), skip, l.cout, ACT_NONE, false,
+           l.y->p, l.cout);
+  }
+}
+
+// SpatialTransformer.forward + BasicTransformerBlock._forward (attention.py:211-215,250-261)
+static void st_forward(StLayer& l, const float* ctx, Exec& e) {
+  if (e.err) return;
+  const int C = l.C, H = l.H, W = l.W, N = H * W;
+  const int M = e.B * N;
+  const encdiff_unet_config& c = e.u->cfg;
+  GnParams p;
+  memset(&p, 0, sizeof(p));
+  p.x0 = l.x->p;
+  p.C0 = C;
+  p.H = H;
+  p.W = W;
+  p.gamma = e.P(l.norm_w);
+  p.beta = e.P(l.norm_b);
+  p.eps = 1e-6f;
+  p.stats = l.stn;
+  p.act = l.n;
+  e.fail(launch_gn_fwd(p, e.B, e.s), "st.norm");
+  e.gemm({{l.n, C, 1}}, H, W, l.pinf, 0, C, 1, e.P(l.pin_b), nullptr, 0, ACT_NONE, false, l.t0, C);
+  // attn1 (self)
+  e.fail(launch_ln_fwd(l.t0, e.P(l.ln1_w), e.P(l.ln1_b), 1e-5f, l.l1, l.ls1, M, C, e.s), "ln1");
+  e.gemm({{l.l1, C, 1}}, H, W, l.qkvf, 0, 3 * C, 1, nullptr, nullptr, 0, ACT_NONE, false, l.qkv, 3 * C);
+  e.fail(launch_self_attn_fwd(l.qkv, l.att, l.lse, e.B, N, l.heads, l.D, e.s), "self_attn");
+  e.gemm({{l.att, C, 1}}, H, W, l.o1f, 0, C, 1, e.P(l.o1_b), l.t0, C, ACT_NONE, false, l.t1, C);
+  // attn2 (cross, concept tokens)
+  e.fail(launch_ln_fwd(l.t1, e.P(l.ln2_w), e.P(l.ln2_b), 1e-5f, l.l2, l.ls2, M, C, e.s), "ln2");
+  e.gemm({{l.l2, C, 1}}, H, W, l.q2f, 0, C, 1, nullptr, nullptr, 0, ACT_NONE, false, l.q2, C);
+  e.fail(launch_cross_attn_fwd(l.q2, ctx, e.P(l.k2_w), e.P(l.v2_w), l.att2, e.B, N, l.heads, l.D, c.latent_unit,
+                               c.context_dim, e.s),
+         "cross_attn");
+  e.gemm({{l.att2, C, 1}}, H, W, l.o2f, 0, C, 1, e.P(l.o2_b), l.t1, C, ACT_NONE, false, l.t2, C);
+  // GEGLU feed-forward
+  e.fail(launch_ln_fwd(l.t2, e.P(l.ln3_w), e.P(l.ln3_b), 1e-5f, l.l3, l.ls3, M, C, e.s), "ln3");
+  e.gemm({{l.l3, C, 1}}, H, W, l.ff1f, 0, 8 * C, 1, e.P(l.ff1_b), nullptr, 0, ACT_NONE, false, l.g, 8 * C);
+  e.fail(launch_geglu_fwd(l.g, l.gg, M, 4 * C, e.s), "geglu");
+  e.gemm({{l.gg, 4 * C, 1}}, H, W, l.ff2f, 0, C, 1, e.P(l.ff2_b), l.t2, C, ACT_NONE, false, l.t3, C);
+  e.gemm({{l.t3, C, 1}}, H, W, l.poutf, 0, C, 1, e.P(l.pout_b), l.x->p, C, ACT_NONE, false, l.y->p, C);
+}
+
+int unet_forward(UNet* u, int B, const float* x, const float* noise, const float* sa, const float* sb, const float* t,
+                 const float* ctx, float* out, float* xt, cudaStream_t s) {
+  EDB_REQUIRE(u->bound, "forward before bind");
+  EDB_REQUIRE(u->planB == B && u->plan_ws, "forward before plan");
+  const encdiff_unet_config& c = u->cfg;
+  Exec e{u, B, s};
+  const int mc = c.model_channels, S = c.image_size, E = u->emb_ch;
+  // timestep embedding MLP + all 28 FiLM projections (openaimodel_enc.py:726-727, 218-224, 264)
+  e.fail(launch_temb(t, u->temb, B, mc, s), "temb");
+  e.gemm({{u->temb, mc, 1}}, 1, 1, u->te0f, 0, E, 1, e.P(u->te0_b), nullptr, 0, ACT_NONE, true, u->z1, E);
+  e.fail(launch_silu_fwd(u->z1, u->a1e, static_cast<long long>(B) * E, s), "silu");
+  e.gemm({{u->a1e, E, 1}}, 1, 1, u->te2f, 0, E, 1, e.P(u->te2_b), nullptr, 0, ACT_NONE, true, u->z2, E);
+  e.fail(launch_silu_fwd(u->z2, u->a2e, static_cast<long long>(B) * E, s), "silu");
+  e.gemm({{u->a2e, E, 1}}, 1, 1, u->filmf, 0, u->film_cols, 1, u->pf32() + u->film_bias_off, nullptr, 0, ACT_NONE, true,
+         u->film, u->film_cols);
+  // stem conv as one K=64 GEMM over the im2col'd 3-channel input (q_sample fused when noise != null)
+  e.fail(launch_stem_im2col(x, noise, sa, sb, xt, u->cols, B, c.in_channels, S, S, s), "stem");
+  e.gemm({{u->cols, 64, 1}}, S, S, u->stemf, 0, mc, 1, e.P(u->stem_b), nullptr, 0, ACT_NONE, false, u->tn[0].p, mc);
+  auto run = [&](std::vector<Layer>& ls) {
+    for (Layer& ly : ls) {
+      if (ly.kind == 1) res_forward(u->res[ly.idx], e);
+      else if (ly.kind == 2) st_forward(u->st[ly.idx], ctx, e);
+    }
+  };
+  for (size_t i = 1; i < u->in_blocks.size(); ++i) run(u->in_blocks[i]);
+  run(u->mid);
+  for (auto& blk : u->out_blocks) run(blk);
+  // head: GN -> SiLU -> conv3x3 (openaimodel_enc.py:684-688,748)
+  Tn& last = u->tn.back();
+  GnParams p;
+  memset(&p, 0, sizeof(p));
+  p.x0 = last.p;
+  p.C0 = last.C;
+  p.H = p.W = S;
+  p.gamma = e.P(u->hn_w);
+  p.beta = e.P(u->hn_b);
+  p.eps = 1e-5f;
+  p.silu = 1;
+  p.stats = u->stH;
+  p.act = u->aH;
+  e.fail(launch_gn_fwd(p, B, s), "head.gn");
+  e.gemm({{u->aH, mc, 9}}, S, S, u->headf, 0, c.out_channels, 1, e.P(u->hc_b), nullptr, 0, ACT_NONE, true, u->yH,
+         c.out_channels);
+  e.fail(launch_nhwc_to_nchw(u->yH, out, B, c.out_channels, S, S, s), "head.out");
+  return e.err ? EDB_ERR_CUDA : EDB_OK;
+}
+
+}  // namespace edb
+
+#include "unet_bwd.inc"

@@ -48,6 +48,79 @@ int encdiff_op_wgrad(const void* dy, int Cp, const void* x, int Cq, int H, int W
                      long long stride_p, long long stride_q, long long stride_tap, int q_off, int bn, int splits,
                      void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Model level: the UNet denoiser.
+ *   Replaces UNetModel.__init__/forward (ldm/modules/diffusionmodules/openaimodel_enc.py:443-748) and everything
+ *   it calls: ResBlock (:179-275), Upsample/Downsample (:109-160), GroupNorm32 / timestep_embedding
+ *   (ldm/modules/diffusionmodules/util.py:179-244), SpatialTransformer / BasicTransformerBlock / CrossAttention /
+ *   FeedForward / GEGLU (ldm/modules/attention.py:37-64,152-261); the backward replaces what torch autograd
+ *   (+ CheckpointFunction, util.py:147-176) computes for them.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct encdiff_unet_config {   /* the `params` of unet_config, configs/latent-diffusion/shapes3d-vq-4-16-encdiff.yaml:35-48 */
+  int image_size, in_channels, model_channels, out_channels, num_res_blocks;
+  int n_attention_resolutions;
+  int attention_resolutions[8];
+  int n_channel_mult;
+  int channel_mult[8];
+  int num_heads, context_dim, latent_unit, transformer_depth;
+  int use_scale_shift_norm, resblock_updown;
+} encdiff_unet_config;
+
+typedef struct encdiff_unet encdiff_unet;
+
+/* Build the architecture (host only, no CUDA call).  Unsupported combinations fail with a message. */
+int encdiff_unet_create(const encdiff_unet_config* cfg /*host*/, encdiff_unet** out /*host*/);
+int encdiff_unet_destroy(encdiff_unet* h);
+
+/* Parameter inventory in the order of the reference UNetModel.named_parameters(); names are state_dict keys. */
+int encdiff_unet_num_params(const encdiff_unet* h);
+int encdiff_unet_param_info(const encdiff_unet* h, int i, char* name /*host*/, int name_cap, long long* shape4 /*host*/,
+                            int* ndim /*host*/);
+
+/* Sizes of the two caller-owned device buffers (bytes): the packed bf16 weight arena and the activation workspace
+ * for a batch (training != 0 keeps every activation and adds gradient buffers). */
+long long encdiff_unet_packed_bytes(const encdiff_unet* h);
+long long encdiff_unet_workspace_bytes(encdiff_unet* h, int batch, int training);
+
+/* Attach fp32 parameter tensors (reference layouts), optional fp32 gradient tensors (same shapes; gradients are
+ * ACCUMULATED into them) and the packed arena (1 KB aligned).  params/grads are host arrays of device pointers in
+ * inventory order.  Synchronises `stream` once (not a hot call). */
+int encdiff_unet_bind(encdiff_unet* h, const float* const* params /*host*/, float* const* grads /*host, may be NULL*/,
+                      void* packed, void* stream);
+/* Re-pack fp32 parameters into bf16 GEMM operands (forward and transposed layouts).  Call after every optimiser /
+ * EMA update of the parameters (the reference mutates them in place, ema.py:46-76). */
+int encdiff_unet_pack_weights(encdiff_unet* h, void* stream);
+/* Assign the workspace (1 KB aligned, >= workspace_bytes(batch, training)); cheap when unchanged. */
+int encdiff_unet_plan(encdiff_unet* h, int batch, void* workspace, int training);
+
+/* eps = UNet(x_t, t, context).  x [B,Cin,S,S] fp32 NCHW, t [B] fp32 (timesteps, may be fractional), ctx
+ * [B, latent_unit*context_dim] fp32, out [B,Cout,S,S] fp32.  When noise != NULL the q_sample of p_losses
+ * (ldm/models/diffusion/ddpm_enc.py:292-295) is fused in front: x_t = sqrt_acp[b]*x + sqrt_1macp[b]*noise (per-sample
+ * fp32 coefficients); x_t is also written to x_t_out when non-NULL. */
+int encdiff_unet_forward(encdiff_unet* h, int batch, const float* x, const float* noise, const float* sqrt_acp,
+                         const float* sqrt_1macp, const float* t, const float* ctx, float* out, float* x_t_out,
+                         void* stream);
+/* Backward of the last forward on this handle (training plan).  dout [B,Cout,S,S] fp32; writes dx (may be NULL) and
+ * dctx [B, latent_unit*context_dim] fp32 (overwritten); parameter gradients are accumulated into the bound tensors. */
+int encdiff_unet_backward(encdiff_unet* h, int batch, const float* dout, const float* ctx, float* dx, float* dctx,
+                          void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Diffusion glue around the UNet.
+ * ------------------------------------------------------------------------------------------------------------- */
+/* loss[0] = mean|eps_hat - noise| (loss_type l1, ddpm_enc.py:297-301,1198-1213); deps (may be NULL) = d loss / d eps_hat */
+int encdiff_l1_loss(const float* eps_hat, const float* noise, float* loss, float* deps, long long n, void* stream);
+/* One DDIM update (DDIMSampler.p_sample_ddim, ldm/models/diffusion/ddim.py:192-206), fp32, same operation order.
+ * coef4 = {a_t, a_prev, sigma_t, sqrt_one_minus_at} on the device; noise may be NULL (eta = 0). */
+int encdiff_ddim_update(const float* x, const float* e_t, const float* noise, const float* coef4, float temperature,
+                        float* x_prev, float* pred_x0, long long n, void* stream);
+/* timestep_embedding (ldm/modules/diffusionmodules/util.py:179-199): t [B] fp32 -> bf16 [B, dim], cosine half first */
+int encdiff_timestep_embedding(const float* t, void* out_bf16, int batch, int dim, void* stream);
+/* Fused AdamW (+EMA when ema != NULL) over flat fp32 buffers: torch.optim.AdamW as configured by
+ * LatentDiffusion.configure_optimizers (ddpm_enc.py:1598-1639) and LitEma.forward (ldm/modules/ema.py:25-44). */
+int encdiff_adamw_step(float* p, const float* g, float* m, float* v, float* ema, long long n, float lr, float beta1,
+                       float beta2, float eps, float weight_decay, int step, float ema_decay, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
