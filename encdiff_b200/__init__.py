@@ -7,3 +7,4 @@ __version__ = "0.1.0"
 
 from .modules import CrossAttention, SpatialTransformer  # noqa: F401
 from .unet import UNetModel  # noqa: F401
+from .sampler import DDIMSampler  # noqa: F401

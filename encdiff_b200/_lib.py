@@ -35,12 +35,21 @@ PROTOTYPES = {
     "encdiff_unet_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_void_p]),
     "encdiff_unet_backward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "encdiff_unet_profile": (c_int, [c_void_p, c_int]),
+    "encdiff_unet_profile_read": (c_ll, [c_void_p, C.c_char_p, c_ll]),
+    "encdiff_unet_debug_block": (c_int, [c_void_p, c_int, c_int, C.POINTER(c_void_p), C.POINTER(c_int),
+                                         C.POINTER(c_int), C.POINTER(c_int)]),
     "encdiff_l1_loss": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "encdiff_ddim_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, C.c_float, c_void_p, c_void_p, c_ll,
                                     c_void_p]),
+    "encdiff_ddim_select": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "encdiff_ddim_update_indexed": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, C.c_float, c_void_p,
+                                            c_void_p, c_ll, c_void_p]),
     "encdiff_timestep_embedding": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "encdiff_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, C.c_float, C.c_float,
                                    C.c_float, C.c_float, C.c_float, c_int, C.c_float, c_void_p]),
+    "encdiff_adamw_step_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p, C.c_float,
+                                       C.c_float, C.c_float, C.c_float, C.c_float, c_void_p]),
 }
 
 

@@ -111,6 +111,62 @@ extern "C" int encdiff_unet_backward(encdiff_unet* h, int batch, const float* do
   return unet_backward(&h->u, batch, dout, ctx, dx, dctx, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int encdiff_unet_profile(encdiff_unet* h, int enable) {
+  EDB_REQUIRE(h, "unet_profile: null handle");
+  h->u.prof = enable != 0;
+  h->u.prof_recs.clear();
+  h->u.prof_used = 0;
+  return EDB_OK;
+}
+
+extern "C" long long encdiff_unet_profile_read(encdiff_unet* h, char* buf, long long cap) {
+  if (!h || !buf || cap <= 0) return -1;
+  UNet& u = h->u;
+  if (!u.prof_recs.empty() && cudaEventSynchronize(u.prof_recs.back().ev) != cudaSuccess) return -1;
+  std::map<std::string, std::tuple<long long, double, double>> agg;   // launches, ms, flops
+  for (size_t i = 1; i < u.prof_recs.size(); ++i) {
+    const ProfRec& r = u.prof_recs[i];
+    if (r.name[0] == '(') continue;   // a "(begin)" marker: the gap before it is host time between calls
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, u.prof_recs[i - 1].ev, r.ev) != cudaSuccess) continue;
+    auto& a = agg[r.name];
+    std::get<0>(a) += 1;
+    std::get<1>(a) += ms;
+    std::get<2>(a) += r.flops;
+  }
+  std::string out;
+  char line[256];
+  for (auto& kv : agg) {
+    snprintf(line, sizeof(line), "%s,%lld,%.6f,%.6e\n", kv.first.c_str(), std::get<0>(kv.second),
+             std::get<1>(kv.second), std::get<2>(kv.second));
+    out += line;
+  }
+  u.prof_recs.clear();
+  u.prof_used = 0;
+  const long long n = static_cast<long long>(out.size());
+  if (n + 1 > cap) return -(n + 1);
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return n;
+}
+
+extern "C" int encdiff_unet_debug_block(encdiff_unet* h, int section, int index, void** ptr, int* C, int* H, int* W) {
+  EDB_REQUIRE(h && ptr && C && H && W, "debug_block: null argument");
+  UNet& u = h->u;
+  EDB_REQUIRE(u.planB > 0 && u.plan_ws, "debug_block before plan");
+  const std::vector<Layer>* ls = nullptr;
+  if (section == 0 && index >= 0 && index < static_cast<int>(u.in_blocks.size())) ls = &u.in_blocks[index];
+  else if (section == 1) ls = &u.mid;
+  else if (section == 2 && index >= 0 && index < static_cast<int>(u.out_blocks.size())) ls = &u.out_blocks[index];
+  EDB_REQUIRE(ls && !ls->empty(), "debug_block: bad section / index");
+  const Layer& l = ls->back();
+  const Tn* t = l.kind == 0 ? &u.tn[0] : (l.kind == 1 ? u.res[l.idx].y : u.st[l.idx].y);
+  *ptr = t->p;
+  *C = t->C;
+  *H = t->H;
+  *W = t->W;
+  return EDB_OK;
+}
+
 // ---- diffusion glue ---------------------------------------------------------------------------------------------
 extern "C" int encdiff_l1_loss(const float* eps_hat, const float* noise, float* loss, float* deps, long long n,
                                void* stream) {
@@ -129,6 +185,22 @@ extern "C" int encdiff_ddim_update(const float* x, const float* e_t, const float
   return EDB_OK;
 }
 
+extern "C" int encdiff_ddim_select(const float* t_table, int* cursor, float* ts, int* idx, int batch, void* stream) {
+  EDB_REQUIRE(t_table && cursor && ts && idx && batch > 0, "ddim_select: bad argument");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(
+      launch_ddim_select(t_table, cursor, ts, idx, batch, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_ddim_update_indexed(const float* x, const float* e_t, const float* noise_table,
+                                           const float* coef_table, const int* idx, float temperature, float* x_prev,
+                                           float* pred_x0, long long n, void* stream) {
+  EDB_REQUIRE(x && e_t && coef_table && idx && x_prev && n > 0, "ddim_update_indexed: bad argument");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_ddim_update_indexed(
+      x, e_t, noise_table, coef_table, idx, temperature, x_prev, pred_x0, n, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
 extern "C" int encdiff_timestep_embedding(const float* t, void* out_bf16, int batch, int dim, void* stream) {
   EDB_REQUIRE(t && out_bf16 && batch > 0 && dim > 1, "timestep_embedding: bad argument");
   EDB_CHECK_CUDA(static_cast<cudaError_t>(
@@ -144,5 +216,14 @@ extern "C" int encdiff_adamw_step(float* p, const float* g, float* m, float* v, 
   const float bc2 = 1.f - powf(beta2, static_cast<float>(step));
   EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_adamw(p, g, m, v, ema, n, lr, beta1, beta2, eps, weight_decay, bc1, bc2,
                                                        ema_decay, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_adamw_step_dev(float* p, const float* g, float* m, float* v, float* ema, long long n,
+                                      const float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                                      float grad_scale, void* stream) {
+  EDB_REQUIRE(p && g && m && v && hyper && n > 0, "adamw_step_dev: bad argument");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_adamw_dev(p, g, m, v, ema, n, hyper, beta1, beta2, eps, weight_decay,
+                                                           grad_scale, static_cast<cudaStream_t>(stream))));
   return EDB_OK;
 }

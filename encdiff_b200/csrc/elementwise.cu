@@ -272,6 +272,51 @@ int launch_ddim_update(const float* x, const float* e_t, const float* noise, con
   return static_cast<int>(cudaGetLastError());
 }
 
+// ---- DDIM loop state on the device, so that ONE captured step graph can be replayed S times (ddim.py:141-166) ----------
+// cursor[0] = loop iteration i; writes ts[b] = t_table[i] (ddim.py:143), idx[0] = i, then advances the cursor.
+__global__ void ddim_select_kernel(const float* __restrict__ t_table, int* __restrict__ cursor, float* __restrict__ ts,
+                                   int* __restrict__ idx, int B) {
+  const int i = *cursor;
+  __syncthreads();
+  const float t = t_table[i];
+  for (int b = threadIdx.x; b < B; b += blockDim.x) ts[b] = t;
+  if (threadIdx.x == 0) {
+    *idx = i;
+    *cursor = i + 1;
+  }
+}
+int launch_ddim_select(const float* t_table, int* cursor, float* ts, int* idx, int B, cudaStream_t s) {
+  ddim_select_kernel<<<1, 256, 0, s>>>(t_table, cursor, ts, idx, B);
+  return static_cast<int>(cudaGetLastError());
+}
+__global__ void ddim_update_indexed_kernel(const float* __restrict__ x, const float* __restrict__ e,
+                                           const float* __restrict__ noise_table, const float* __restrict__ coef_table,
+                                           const int* __restrict__ idx, float temperature, float* __restrict__ x_prev,
+                                           float* __restrict__ pred_x0, long long n) {
+  const int it = *idx;
+  const float* coef = coef_table + 4 * it;
+  const float* nz = noise_table ? noise_table + static_cast<long long>(it) * n : nullptr;
+  const float a_t = coef[0], a_prev = coef[1], sigma = coef[2], somat = coef[3];
+  const float sqrt_at = sqrtf(a_t), sqrt_ap = sqrtf(a_prev);
+  const float dir = sqrtf(__fsub_rn(__fsub_rn(1.f, a_prev), __fmul_rn(sigma, sigma)));
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float et = e[i];
+    const float p0 = __fdiv_rn(x[i] - __fmul_rn(somat, et), sqrt_at);
+    const float d = __fmul_rn(dir, et);
+    const float noise = nz ? __fmul_rn(__fmul_rn(sigma, nz[i]), temperature) : 0.f;
+    x_prev[i] = __fadd_rn(__fadd_rn(__fmul_rn(sqrt_ap, p0), d), noise);
+    if (pred_x0) pred_x0[i] = p0;
+  }
+}
+int launch_ddim_update_indexed(const float* x, const float* e_t, const float* noise_table, const float* coef_table,
+                               const int* idx, float temperature, float* x_prev, float* pred_x0, long long n,
+                               cudaStream_t s) {
+  ddim_update_indexed_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, e_t, noise_table, coef_table, idx, temperature, x_prev,
+                                                             pred_x0, n);
+  return static_cast<int>(cudaGetLastError());
+}
+
 // ---- weight packing: fp32 reference-layout parameters -> bf16 GEMM operands (and fused fp32 biases) -------------------
 __global__ void pack_kernel(const PackEntry* __restrict__ tab, int n_entries, long long total, bf16* __restrict__ abf,
                             float* __restrict__ af32) {
@@ -334,6 +379,34 @@ int launch_adamw(float* p, const float* g, float* m, float* v, float* ema, long 
                  float beta2, float eps, float wd, float bc1, float bc2, float ema_decay, cudaStream_t s) {
   adamw_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, s>>>(p, g, m, v, ema, n, lr, beta1, beta2, eps, wd, bc1, bc2,
                                                           ema_decay);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// same update with the step-dependent scalars read from device memory, so a captured graph of the optimiser step can be
+// replayed: hyper = {lr, 1-beta1^t, 1-beta2^t, ema_decay}
+__global__ void adamw_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                 float* __restrict__ v, float* __restrict__ ema, long long n,
+                                 const float* __restrict__ hyper, float b1, float b2, float eps, float wd,
+                                 float grad_scale) {
+  const float lr = hyper[0], bc1 = hyper[1], bc2 = hyper[2], ema_decay = hyper[3];
+  const float rs = rsqrtf(bc2), step = lr / bc1, keep = 1.f - lr * wd, om = 1.f - ema_decay;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float w = p[i] * keep;
+    const float gi = g[i] * grad_scale;
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    w -= step * (mi / (sqrtf(vi) * rs + eps));
+    p[i] = w;
+    if (ema) ema[i] -= om * (ema[i] - w);
+  }
+}
+int launch_adamw_dev(float* p, const float* g, float* m, float* v, float* ema, long long n, const float* hyper,
+                     float beta1, float beta2, float eps, float wd, float grad_scale, cudaStream_t s) {
+  adamw_dev_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, s>>>(p, g, m, v, ema, n, hyper, beta1, beta2, eps, wd,
+                                                              grad_scale);
   return static_cast<int>(cudaGetLastError());
 }
 

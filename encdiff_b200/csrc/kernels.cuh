@@ -84,6 +84,13 @@ int launch_l1_loss(const float* eps_hat, const float* noise, float* loss, float*
 int launch_ddim_update(const float* x, const float* e_t, const float* noise, const float* coef, float temperature,
                        float* x_prev, float* pred_x0, long long n, cudaStream_t s);
 
+// device-resident DDIM loop state (one captured step graph replayed S times): tables are in loop order (i = 0 is the
+// first, noisiest step); cursor/idx are device ints
+int launch_ddim_select(const float* t_table, int* cursor, float* ts, int* idx, int B, cudaStream_t s);
+int launch_ddim_update_indexed(const float* x, const float* e_t, const float* noise_table, const float* coef_table,
+                               const int* idx, float temperature, float* x_prev, float* pred_x0, long long n,
+                               cudaStream_t s);
+
 // ---- weight packing ---------------------------------------------------------------------------------------------
 struct PackEntry {
   const float* src;      // fp32 parameter, reference layout [rows, cin, taps]
@@ -106,5 +113,10 @@ int launch_pack(const PackEntry* table_dev, int n_entries, long long total, bf16
 // fused AdamW (+ optional EMA) over a flat fp32 parameter buffer (ddpm_enc.py:1598-1639, ema.py:25-44)
 int launch_adamw(float* p, const float* g, float* m, float* v, float* ema, long long n, float lr, float beta1,
                  float beta2, float eps, float wd, float bc1, float bc2, float ema_decay, cudaStream_t s);
+
+// hyper (device) = {lr, 1-beta1^t, 1-beta2^t, ema_decay}; g is multiplied by grad_scale (1/world_size after a sum
+// all-reduce) before use
+int launch_adamw_dev(float* p, const float* g, float* m, float* v, float* ema, long long n, const float* hyper,
+                     float beta1, float beta2, float eps, float wd, float grad_scale, cudaStream_t s);
 
 }  // namespace edb

@@ -71,8 +71,20 @@ struct Layer {
   int idx;    // index into res / st vectors
 };
 
+// live per-launch timing (bench / tuning): one CUDA event after every launch of a step, on the launching stream;
+// a launch's duration is the difference to the previous event (launches of one stream are serialised)
+struct ProfRec {
+  const char* name;
+  double flops;
+  cudaEvent_t ev;
+};
+
 struct UNet {
   encdiff_unet_config cfg;
+  bool prof = false;
+  std::vector<ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
+  size_t prof_used = 0;
   std::vector<ParamInfo> params;
   std::vector<ResLayer> res;
   std::vector<StLayer> st;

@@ -166,8 +166,24 @@ struct Exec {
   cudaStream_t s;
   int err = 0;
 
+  double next_flops = 0;   // algorithmic FLOPs of the launch about to be reported through fail()
+
+  void mark(const char* what) {
+    if (!u->prof) return;
+    if (u->prof_used == u->prof_pool.size()) {
+      cudaEvent_t ev;
+      if (cudaEventCreate(&ev) != cudaSuccess) return;
+      u->prof_pool.push_back(ev);
+    }
+    cudaEvent_t ev = u->prof_pool[u->prof_used++];
+    cudaEventRecord(ev, s);
+    u->prof_recs.push_back(ProfRec{what, next_flops, ev});
+    next_flops = 0;
+  }
+
   // rc is a cudaError_t returned by a launcher
   bool fail(int rc, const char* what) {
+    mark(what);
     if (rc != 0 && err == 0) {
       err = EDB_ERR_CUDA;
       set_last_error(std::string(what) + ": " + cudaGetErrorString(static_cast<cudaError_t>(rc)));
@@ -247,6 +263,7 @@ struct Exec {
     p.out0 = out;
     p.ld0 = ld;
     p.split_col = 1 << 30;
+    next_flops = 2.0 * p.M * static_cast<double>(N) * static_cast<double>(K);
     fail(launch_sgemm(p, bn, s), "sgemm");
   }
 
@@ -283,6 +300,7 @@ struct Exec {
     const long long max_by_atomics = std::max(1LL, (8LL << 20) / std::max(1LL, weights));
     splits = std::min(splits, max_by_atomics);
     splits = std::max(1LL, std::min<long long>(splits, p.m_tiles));
+    next_flops = 2.0 * B * H * W * static_cast<double>(Cp) * Cq * taps;
     fail(launch_wgrad(p, bn, static_cast<int>(splits), s), "wgrad");
   }
 
@@ -403,6 +421,7 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
   EDB_REQUIRE(u->planB == B && u->plan_ws, "forward before plan");
   const encdiff_unet_config& c = u->cfg;
   Exec e{u, B, s};
+  e.mark("(begin)");
   const int mc = c.model_channels, S = c.image_size, E = u->emb_ch;
   // timestep embedding MLP + all 28 FiLM projections (openaimodel_enc.py:726-727, 218-224, 264)
   e.fail(launch_temb(t, u->temb, B, mc, s), "temb");

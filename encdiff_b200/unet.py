@@ -246,6 +246,10 @@ class UNetModel(nn.Module):
             self._ws = {key: ws}     # one live workspace: batch-size changes free the old one
         return ws
 
+    def plan_key(self):
+        """Identity of everything a captured graph of forward() bakes in: workspace plan and parameter binding."""
+        return (self._planned, self._bound_key, None if self._packed is None else self._packed.data_ptr())
+
     def _prepare_grads(self):
         """param.grad must be the views of the flat bucket the library accumulates into (zeroed when re-attached)."""
         params = self._params()
@@ -290,6 +294,34 @@ class UNetModel(nn.Module):
         _lib.check(self._lib.encdiff_unet_backward(self._h, B, dout.data_ptr(), cond.data_ptr(), _lib.ptr(dx),
                                                    dctx.data_ptr(), _lib.current_stream()), "unet_backward")
         return dx, dctx
+
+    def profile(self, enable: bool):
+        """Switch the library's per-launch event timing on/off (bench.py roofline figures)."""
+        _lib.check(self._lib.encdiff_unet_profile(self._h, int(enable)), "unet_profile")
+
+    def profile_read(self):
+        """{family: (launches, total_ms, total_flops)} since the last read."""
+        buf = C.create_string_buffer(1 << 16)
+        n = self._lib.encdiff_unet_profile_read(self._h, buf, len(buf))
+        if n < 0:
+            raise RuntimeError("encdiff_b200: profile_read failed")
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, k, ms, fl = line.split(",")
+            out[name] = (int(k), float(ms), float(fl))
+        return out
+
+    def debug_block(self, section: int, index: int = 0) -> torch.Tensor:
+        """Output of input_blocks[index] (section 0) / middle_block (1) / output_blocks[index] (2) of the last forward,
+        as a (B, C, H, W) fp32 copy — what a forward hook on the reference module would see (parity tests only)."""
+        ptr, c, h, w = C.c_void_p(), C.c_int(), C.c_int(), C.c_int()
+        _lib.check(self._lib.encdiff_unet_debug_block(self._h, section, index, C.byref(ptr), C.byref(c), C.byref(h),
+                                                      C.byref(w)), "debug_block")
+        (B, _training), ws = next(iter(self._ws.items()))
+        off = ptr.value - ws.data_ptr()
+        n = B * h.value * w.value * c.value
+        t = ws[off:off + 2 * n].view(torch.bfloat16).view(B, h.value, w.value, c.value)
+        return t.float().permute(0, 3, 1, 2).contiguous()
 
     # ------------------------------------------------------------------------------------------------------------
     def forward(self, x, timesteps=None, context=None, y=None, **kwargs):

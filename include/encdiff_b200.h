@@ -105,6 +105,19 @@ int encdiff_unet_forward(encdiff_unet* h, int batch, const float* x, const float
 int encdiff_unet_backward(encdiff_unet* h, int batch, const float* dout, const float* ctx, float* dx, float* dctx,
                           void* stream);
 
+/* Live per-launch timing for bench.py's roofline figure: while enabled, forward/backward record one CUDA event after
+ * every kernel launch on the launching stream.  profile_read synchronises on the last event, writes one text line
+ * "family,launches,total_ms,total_flops" per kernel family into buf and clears the records; returns the byte count,
+ * or -(needed) when cap is too small, or -1 on error. */
+int encdiff_unet_profile(encdiff_unet* h, int enable);
+long long encdiff_unet_profile_read(encdiff_unet* h, char* buf /*host*/, long long cap);
+
+/* Debug / parity-test hook: device pointer and shape of the NHWC bf16 output of one block of the LAST forward.
+ * section 0 = input_blocks[index], 1 = middle_block, 2 = output_blocks[index]; the tensor is [B, H, W, C].  The
+ * reference exposes the same tensors through forward hooks on input_blocks / middle_block / output_blocks. */
+int encdiff_unet_debug_block(encdiff_unet* h, int section, int index, void** ptr /*host*/, int* C /*host*/,
+                             int* H /*host*/, int* W /*host*/);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Diffusion glue around the UNet.
  * ------------------------------------------------------------------------------------------------------------- */
@@ -114,12 +127,26 @@ int encdiff_l1_loss(const float* eps_hat, const float* noise, float* loss, float
  * coef4 = {a_t, a_prev, sigma_t, sqrt_one_minus_at} on the device; noise may be NULL (eta = 0). */
 int encdiff_ddim_update(const float* x, const float* e_t, const float* noise, const float* coef4, float temperature,
                         float* x_prev, float* pred_x0, long long n, void* stream);
+/* Device-resident loop state of DDIMSampler.ddim_sampling (ddim.py:141-166) so that one captured step graph can be
+ * replayed S times without host updates.  Tables are in loop order (row 0 = first, noisiest step): t_table [S] fp32,
+ * coef_table [S,4] = {a_t, a_prev, sigma_t, sqrt_one_minus_at}, noise_table [S,n] or NULL.
+ * ddim_select: i = cursor[0]; ts[0..batch) = t_table[i] (the `ts = torch.full((b,), step)` of ddim.py:143); idx[0] = i;
+ * cursor[0] = i + 1.  ddim_update_indexed: encdiff_ddim_update with row idx[0] of the tables. */
+int encdiff_ddim_select(const float* t_table, int* cursor, float* ts, int* idx, int batch, void* stream);
+int encdiff_ddim_update_indexed(const float* x, const float* e_t, const float* noise_table, const float* coef_table,
+                                const int* idx, float temperature, float* x_prev, float* pred_x0, long long n,
+                                void* stream);
 /* timestep_embedding (ldm/modules/diffusionmodules/util.py:179-199): t [B] fp32 -> bf16 [B, dim], cosine half first */
 int encdiff_timestep_embedding(const float* t, void* out_bf16, int batch, int dim, void* stream);
 /* Fused AdamW (+EMA when ema != NULL) over flat fp32 buffers: torch.optim.AdamW as configured by
  * LatentDiffusion.configure_optimizers (ddpm_enc.py:1598-1639) and LitEma.forward (ldm/modules/ema.py:25-44). */
 int encdiff_adamw_step(float* p, const float* g, float* m, float* v, float* ema, long long n, float lr, float beta1,
                        float beta2, float eps, float weight_decay, int step, float ema_decay, void* stream);
+
+/* Graph-replayable form: the step-dependent scalars come from device memory, hyper = {lr, 1-beta1^t, 1-beta2^t,
+ * ema_decay}; g is multiplied by grad_scale first (1/world_size after a sum all-reduce). */
+int encdiff_adamw_step_dev(float* p, const float* g, float* m, float* v, float* ema, long long n, const float* hyper,
+                           float beta1, float beta2, float eps, float weight_decay, float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }
