@@ -18,6 +18,7 @@ c_void_p, c_int, c_ll, c_float_p = C.c_void_p, C.c_int, C.c_longlong, C.c_void_p
 # symbol the header declares is exported and listed here.
 PROTOTYPES = {
     "encdiff_last_error": (C.c_char_p, []),
+    "encdiff_act_format": (c_int, []),
     "encdiff_op_sgemm": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int), c_int, c_int, c_int,
                                  c_void_p, c_ll, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
                                  c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
@@ -89,6 +90,12 @@ def load(build_if_missing: bool = True):
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def act_dtype():
+    """torch dtype of the library's 16-bit storage type (fp16 by default, bf16 in the -DEDB_ACT_BF16 build)."""
+    import torch
+    return torch.bfloat16 if load().encdiff_act_format() == 1 else torch.float16
 
 
 def check(status: int, what: str = "") -> None:

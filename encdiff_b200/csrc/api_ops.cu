@@ -3,6 +3,7 @@
 #include "../../include/encdiff_b200.h"
 #include <string.h>
 
+#include "common.cuh"
 #include "gemm.cuh"
 #include "host.cuh"
 
@@ -75,3 +76,6 @@ extern "C" int encdiff_op_wgrad(const void* dy, int Cp, const void* x, int Cq, i
   EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_wgrad(p, bn, splits, static_cast<cudaStream_t>(stream))));
   return EDB_OK;
 }
+
+// 0 = fp16, 1 = bf16: the 16-bit storage / operand type this library was built with (types.cuh)
+extern "C" int encdiff_act_format(void) { return EDB_FMT; }

@@ -47,7 +47,7 @@ extern "C" int encdiff_unet_param_info(const encdiff_unet* h, int i, char* name,
 }
 
 extern "C" long long encdiff_unet_packed_bytes(const encdiff_unet* h) {
-  return h ? static_cast<long long>(h->u.table_bytes + h->u.bf16_bytes + h->u.f32_bytes) : -1;
+  return h ? static_cast<long long>(h->u.table_bytes + h->u.h16_bytes + h->u.f32_bytes) : -1;
 }
 
 extern "C" long long encdiff_unet_workspace_bytes(encdiff_unet* h, int batch, int training) {
@@ -74,7 +74,7 @@ extern "C" int encdiff_unet_bind(encdiff_unet* h, const float* const* params, fl
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   u.packed = static_cast<char*>(packed);
-  EDB_CHECK_CUDA(cudaMemsetAsync(packed, 0, u.table_bytes + u.bf16_bytes + u.f32_bytes, s));
+  EDB_CHECK_CUDA(cudaMemsetAsync(packed, 0, u.table_bytes + u.h16_bytes + u.f32_bytes, s));
   EDB_CHECK_CUDA(cudaMemcpyAsync(packed, u.table.data(), u.table.size() * sizeof(PackEntry), cudaMemcpyHostToDevice, s));
   EDB_CHECK_CUDA(cudaStreamSynchronize(s));   // the host table may be re-bound later; bind is not a hot call
   u.w_maps.clear();
@@ -201,10 +201,10 @@ extern "C" int encdiff_ddim_update_indexed(const float* x, const float* e_t, con
   return EDB_OK;
 }
 
-extern "C" int encdiff_timestep_embedding(const float* t, void* out_bf16, int batch, int dim, void* stream) {
-  EDB_REQUIRE(t && out_bf16 && batch > 0 && dim > 1, "timestep_embedding: bad argument");
+extern "C" int encdiff_timestep_embedding(const float* t, void* out_h16, int batch, int dim, void* stream) {
+  EDB_REQUIRE(t && out_h16 && batch > 0 && dim > 1, "timestep_embedding: bad argument");
   EDB_CHECK_CUDA(static_cast<cudaError_t>(
-      launch_temb(t, static_cast<bf16*>(out_bf16), batch, dim, static_cast<cudaStream_t>(stream))));
+      launch_temb(t, static_cast<h16*>(out_h16), batch, dim, static_cast<cudaStream_t>(stream))));
   return EDB_OK;
 }
 

@@ -13,7 +13,7 @@ static constexpr float kLog2e = 1.4426950408889634f;
 // self-attention forward
 // ---------------------------------------------------------------------------------------------------------------
 template <int D>
-__global__ void __launch_bounds__(256) self_attn_fwd_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out,
+__global__ void __launch_bounds__(256) self_attn_fwd_kernel(const h16* __restrict__ qkv, h16* __restrict__ out,
                                                             float* __restrict__ lse, int N, int heads, int TN, int G,
                                                             int total_pairs, float scale_log2) {
   extern __shared__ float sm[];
@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(256) self_attn_fwd_kernel(const bf16* __restri
     const int pair = pair0 + g;
     if (pair < total_pairs) {
       const int b = pair / heads, h = pair - b * heads;
-      const bf16* base = qkv + (static_cast<long long>(b) * N + j) * 3 * C + h * D + dc * 8;
+      const h16* base = qkv + (static_cast<long long>(b) * N + j) * 3 * C + h * D + dc * 8;
       unpack8(*reinterpret_cast<const uint4*>(base + C), Ks + (static_cast<size_t>(g) * N + j) * D + dc * 8);
       unpack8(*reinterpret_cast<const uint4*>(base + 2 * C), Vs + (static_cast<size_t>(g) * N + j) * D + dc * 8);
     }
@@ -103,9 +103,9 @@ __global__ void __launch_bounds__(256) self_attn_fwd_kernel(const bf16* __restri
 // recomputed from the saved log-sum-exp.
 // ---------------------------------------------------------------------------------------------------------------
 template <int D>
-__global__ void __launch_bounds__(256) self_attn_bwd_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ out,
-                                                            const bf16* __restrict__ dout, const float* __restrict__ lse,
-                                                            bf16* __restrict__ dqkv, int N, int heads, int TN, int G,
+__global__ void __launch_bounds__(256) self_attn_bwd_kernel(const h16* __restrict__ qkv, const h16* __restrict__ out,
+                                                            const h16* __restrict__ dout, const float* __restrict__ lse,
+                                                            h16* __restrict__ dqkv, int N, int heads, int TN, int G,
                                                             int total_pairs, float scale) {
   extern __shared__ float sm[];
   const size_t sz = static_cast<size_t>(G) * N * D;
@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256) self_attn_bwd_kernel(const bf16* __restri
     if (pair < total_pairs) {
       const int b = pair / heads, h = pair - b * heads;
       const long long row = static_cast<long long>(b) * N + j;
-      const bf16* base = qkv + row * 3 * C + h * D + dc * 8;
+      const h16* base = qkv + row * 3 * C + h * D + dc * 8;
       const size_t o = (static_cast<size_t>(g) * N + j) * D + dc * 8;
       unpack8(*reinterpret_cast<const uint4*>(base), Qs + o);
       unpack8(*reinterpret_cast<const uint4*>(base + C), Ks + o);
@@ -234,7 +234,7 @@ static SelfAttnShape self_attn_shape(int N) {
 }
 
 template <int D>
-static int self_attn_fwd_t(const bf16* qkv, bf16* out, float* lse, int B, int N, int heads, cudaStream_t st) {
+static int self_attn_fwd_t(const h16* qkv, h16* out, float* lse, int B, int N, int heads, cudaStream_t st) {
   const SelfAttnShape s = self_attn_shape(N);
   const int total = B * heads;
   const size_t smem = 2ull * s.G * N * D * sizeof(float);
@@ -251,7 +251,7 @@ static int self_attn_fwd_t(const bf16* qkv, bf16* out, float* lse, int B, int N,
 }
 
 template <int D>
-static int self_attn_bwd_t(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int B, int N,
+static int self_attn_bwd_t(const h16* qkv, const h16* out, const h16* dout, const float* lse, h16* dqkv, int B, int N,
                            int heads, cudaStream_t st) {
   const SelfAttnShape s = self_attn_shape(N);
   const int total = B * heads;
@@ -268,7 +268,7 @@ static int self_attn_bwd_t(const bf16* qkv, const bf16* out, const bf16* dout, c
   return static_cast<int>(cudaGetLastError());
 }
 
-int launch_self_attn_fwd(const bf16* qkv, bf16* out, float* lse, int B, int N, int heads, int D, cudaStream_t s) {
+int launch_self_attn_fwd(const h16* qkv, h16* out, float* lse, int B, int N, int heads, int D, cudaStream_t s) {
   if (N < 4 || (N & 3)) return static_cast<int>(cudaErrorInvalidValue);
   switch (D) {
     case 8: return self_attn_fwd_t<8>(qkv, out, lse, B, N, heads, s);
@@ -279,7 +279,7 @@ int launch_self_attn_fwd(const bf16* qkv, bf16* out, float* lse, int B, int N, i
   }
 }
 
-int launch_self_attn_bwd(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int B, int N,
+int launch_self_attn_bwd(const h16* qkv, const h16* out, const h16* dout, const float* lse, h16* dqkv, int B, int N,
                          int heads, int D, cudaStream_t s) {
   if (N < 4 || (N & 3)) return static_cast<int>(cudaErrorInvalidValue);
   switch (D) {
@@ -313,9 +313,9 @@ __device__ __forceinline__ void project_ctx(const float* __restrict__ ctx_s, con
 }
 
 template <int D>
-__global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const bf16* __restrict__ q, const float* __restrict__ ctx,
+__global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restrict__ q, const float* __restrict__ ctx,
                                                              const float* __restrict__ wk, const float* __restrict__ wv,
-                                                             bf16* __restrict__ out, int N, int heads, int T, int Dc,
+                                                             h16* __restrict__ out, int N, int heads, int T, int Dc,
                                                              float scale_log2) {
   extern __shared__ float sm[];
   const int C = heads * D;
@@ -372,12 +372,14 @@ __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const bf16* __restr
 }
 
 template <int D>
-__global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const bf16* __restrict__ q, const float* __restrict__ ctx,
+__global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const h16* __restrict__ q, const float* __restrict__ ctx,
                                                              const float* __restrict__ wk, const float* __restrict__ wv,
-                                                             const bf16* __restrict__ dout, bf16* __restrict__ dq,
+                                                             const h16* __restrict__ dout, h16* __restrict__ dq,
                                                              float* __restrict__ dwk, float* __restrict__ dwv,
-                                                             float* __restrict__ dctx, int N, int heads, int T, int Dc,
-                                                             float scale) {
+                                                             float* __restrict__ dctx,
+                                                             const float* __restrict__ gscale, int N, int heads, int T,
+                                                             int Dc, float scale) {
+  const float ginv = gscale ? gscale[1] : 1.f;
   extern __shared__ float sm[];
   const int C = heads * D;
   float* Ks = sm;                   // [T][C]
@@ -462,11 +464,11 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const bf16* __restr
     for (int e = threadIdx.x; e < T * D; e += blockDim.x) {
       const int j = e / D, d = e - j * D;
       float ak = 0.f, av = 0.f;
-      const bf16* qc = q + static_cast<long long>(b) * N * C + h * D + d;
-      const bf16* oc = dout + static_cast<long long>(b) * N * C + h * D + d;
+      const h16* qc = q + static_cast<long long>(b) * N * C + h * D + d;
+      const h16* oc = dout + static_cast<long long>(b) * N * C + h * D + d;
       for (int i = 0; i < N; ++i) {
-        ak += dSs[i * T + j] * __bfloat162float(qc[static_cast<long long>(i) * C]);
-        av += Ps[i * T + j] * __bfloat162float(oc[static_cast<long long>(i) * C]);
+        ak += dSs[i * T + j] * h2f(qc[static_cast<long long>(i) * C]);
+        av += Ps[i * T + j] * h2f(oc[static_cast<long long>(i) * C]);
       }
       dKh[e] = ak;
       dVh[e] = av;
@@ -480,8 +482,8 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const bf16* __restr
         ak += dKh[j * D + d] * ctx_s[j * Dc + x];
         av += dVh[j * D + d] * ctx_s[j * Dc + x];
       }
-      atomicAdd(dwk + (h * D + d) * Dc + x, ak);
-      atomicAdd(dwv + (h * D + d) * Dc + x, av);
+      atomicAdd(dwk + (h * D + d) * Dc + x, ak * ginv);
+      atomicAdd(dwv + (h * D + d) * Dc + x, av * ginv);
     }
     for (int e = threadIdx.x; e < T * Dc; e += blockDim.x) {
       const int j = e / Dc, x = e - j * Dc;
@@ -492,11 +494,11 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const bf16* __restr
     }
     __syncthreads();
   }
-  for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) dctx[static_cast<long long>(b) * T * Dc + i] += dctx_s[i];
+  for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) dctx[static_cast<long long>(b) * T * Dc + i] += dctx_s[i] * ginv;
 }
 
 template <int D>
-static int cross_fwd_t(const bf16* q, const float* ctx, const float* wk, const float* wv, bf16* out, int B, int N,
+static int cross_fwd_t(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
                        int heads, int T, int Dc, cudaStream_t st) {
   const int C = heads * D;
   const size_t smem = (2ull * T * C + T * Dc) * sizeof(float);
@@ -512,8 +514,9 @@ static int cross_fwd_t(const bf16* q, const float* ctx, const float* wk, const f
 }
 
 template <int D>
-static int cross_bwd_t(const bf16* q, const float* ctx, const float* wk, const float* wv, const bf16* dout, bf16* dq,
-                       float* dwk, float* dwv, float* dctx, int B, int N, int heads, int T, int Dc, cudaStream_t st) {
+static int cross_bwd_t(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
+                       float* dwk, float* dwv, float* dctx, const float* gscale, int B, int N, int heads, int T, int Dc,
+                       cudaStream_t st) {
   const int C = heads * D;
   const size_t smem = (2ull * T * C + 2ull * T * Dc + 2ull * N * T + 2ull * T * D) * sizeof(float);
   static size_t configured = 48 * 1024;
@@ -522,12 +525,12 @@ static int cross_bwd_t(const bf16* q, const float* ctx, const float* wk, const f
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = smem;
   }
-  cross_attn_bwd_kernel<D><<<B, 256, smem, st>>>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, N, heads, T, Dc,
+  cross_attn_bwd_kernel<D><<<B, 256, smem, st>>>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, N, heads, T, Dc,
                                                  rsqrtf(static_cast<float>(D)));
   return static_cast<int>(cudaGetLastError());
 }
 
-int launch_cross_attn_fwd(const bf16* q, const float* ctx, const float* wk, const float* wv, bf16* out, int B, int N,
+int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
                           int heads, int D, int T, int Dc, cudaStream_t s) {
   if (T < 1 || T > kMaxT) return static_cast<int>(cudaErrorInvalidValue);
   switch (D) {
@@ -539,15 +542,15 @@ int launch_cross_attn_fwd(const bf16* q, const float* ctx, const float* wk, cons
   }
 }
 
-int launch_cross_attn_bwd(const bf16* q, const float* ctx, const float* wk, const float* wv, const bf16* dout, bf16* dq,
-                          float* dwk, float* dwv, float* dctx, int B, int N, int heads, int D, int T, int Dc,
-                          cudaStream_t s) {
+int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
+                          float* dwk, float* dwv, float* dctx, const float* gscale, int B, int N, int heads, int D, int T,
+                          int Dc, cudaStream_t s) {
   if (T < 1 || T > kMaxT) return static_cast<int>(cudaErrorInvalidValue);
   switch (D) {
-    case 8: return cross_bwd_t<8>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, B, N, heads, T, Dc, s);
-    case 16: return cross_bwd_t<16>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, B, N, heads, T, Dc, s);
-    case 32: return cross_bwd_t<32>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, B, N, heads, T, Dc, s);
-    case 64: return cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, B, N, heads, T, Dc, s);
+    case 8: return cross_bwd_t<8>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
+    case 16: return cross_bwd_t<16>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
+    case 32: return cross_bwd_t<32>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
+    case 64: return cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
 }

@@ -2,14 +2,13 @@
 // PTX wrappers for mbarrier, TMA (cp.async.bulk.tensor), tcgen05 (MMA/TMEM).
 #pragma once
 #include <cuda.h>
-#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
 
-namespace edb {
+#include "types.cuh"
 
-typedef __nv_bfloat16 bf16;
+namespace edb {
 
 // ---------------------------------------------------------------------------------------------
 // generic helpers
@@ -57,24 +56,21 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
-// 8 x bf16 <-> 8 x float through one 16-byte vector
-struct __align__(16) bf16x8 {
-  __nv_bfloat162 v[4];
-};
+// 8 x h16 <-> 8 x float through one 16-byte vector
 __device__ __forceinline__ void unpack8(const uint4& u, float* f) {
-  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+  const h162* h = reinterpret_cast<const h162*>(&u);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    float2 t = __bfloat1622float2(h[i]);
+    float2 t = h22f2(h[i]);
     f[2 * i] = t.x;
     f[2 * i + 1] = t.y;
   }
 }
 __device__ __forceinline__ uint4 pack8(const float* f) {
   uint4 u;
-  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+  h162* h = reinterpret_cast<h162*>(&u);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  for (int i = 0; i < 4; ++i) h[i] = f22h2(f[2 * i], f[2 * i + 1]);
   return u;
 }
 
@@ -160,8 +156,8 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {  // whole warp
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
 }
 
-// D[tmem] (+)= A[smem desc] * B[smem desc], bf16 inputs, fp32 accumulate. One thread issues.
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+// D[tmem] (+)= A[smem desc] * B[smem desc], h16 inputs, fp32 accumulate. One thread issues.
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                           uint32_t accumulate) {
   asm volatile(
       "{\n"
@@ -195,8 +191,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* r) {
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // Shared-memory matrix descriptor (sm_100 "version 1"), 128-byte swizzle.
-//   K-major operand  : rows of 128 B (64 bf16 of K), 8-row groups 1024 B apart (SBO); LBO unused (=1)
-//   MN-major operand : rows of 128 B (64 bf16 of M/N) indexed by k, 8-k groups 1024 B apart (SBO),
+//   K-major operand  : rows of 128 B (64 h16 of K), 8-row groups 1024 B apart (SBO); LBO unused (=1)
+//   MN-major operand : rows of 128 B (64 h16 of M/N) indexed by k, 8-k groups 1024 B apart (SBO),
 //                      next 64-wide M/N block LBO bytes away
 __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = 0;
@@ -207,10 +203,15 @@ __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_byte
   d |= 2ull << 61;  // SWIZZLE_128B
   return d;
 }
-// Instruction descriptor, kind::f16: D=f32, A=B=bf16, M=128.
+// Instruction descriptor, kind::f16 with explicit operand formats (FMT_F16 / FMT_BF16): D=f32, M=128.
+__host__ __device__ constexpr uint32_t make_idesc_fmt(int n, bool a_mn_major, bool b_mn_major, int a_fmt, int b_fmt) {
+  return (1u << 4) | (static_cast<uint32_t>(a_fmt) << 7) | (static_cast<uint32_t>(b_fmt) << 10) |
+         ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
+         (static_cast<uint32_t>(128 >> 4) << 24);
+}
+// Instruction descriptor for the plan's 16-bit type on both operands.
 __host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn_major, bool b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
-         (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(128 >> 4) << 24);
+  return make_idesc_fmt(n, a_mn_major, b_mn_major, EDB_FMT, EDB_FMT);
 }
 
 }  // namespace edb

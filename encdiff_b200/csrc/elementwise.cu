@@ -12,45 +12,45 @@ static inline int grid_for(long long n, int block, int cap = 148 * 16) {
 }
 
 // ---- timestep embedding (util.py:179-199): [cos(t f_i) | sin(t f_i)], f_i = exp(-ln(1e4) i / half) ---------------
-__global__ void temb_kernel(const float* __restrict__ t, bf16* __restrict__ out, int B, int dim) {
+__global__ void temb_kernel(const float* __restrict__ t, h16* __restrict__ out, int B, int dim) {
   const int half = dim / 2;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < B * half; idx += gridDim.x * blockDim.x) {
     const int b = idx / half, i = idx - b * half;
     const float freq = expf(-9.210340371976184f * static_cast<float>(i) / static_cast<float>(half));
     const float a = t[b] * freq;
-    out[b * dim + i] = __float2bfloat16(cosf(a));
-    out[b * dim + half + i] = __float2bfloat16(sinf(a));
-    if ((dim & 1) && i == 0) out[b * dim + dim - 1] = __float2bfloat16(0.f);
+    out[b * dim + i] = f2h(cosf(a));
+    out[b * dim + half + i] = f2h(sinf(a));
+    if ((dim & 1) && i == 0) out[b * dim + dim - 1] = f2h(0.f);
   }
 }
-int launch_temb(const float* t, bf16* out, int B, int dim, cudaStream_t s) {
+int launch_temb(const float* t, h16* out, int B, int dim, cudaStream_t s) {
   temb_kernel<<<grid_for(static_cast<long long>(B) * (dim / 2), 256), 256, 0, s>>>(t, out, B, dim);
   return static_cast<int>(cudaGetLastError());
 }
 
 // ---- SiLU on the (tiny) embedding MLP ------------------------------------------------------------------------------
-__global__ void silu_fwd_kernel(const float* __restrict__ x, bf16* __restrict__ y, long long n) {
+__global__ void silu_fwd_kernel(const float* __restrict__ x, h16* __restrict__ y, long long n) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
-    y[i] = __float2bfloat16(silu_f(x[i]));
+    y[i] = f2h(silu_f(x[i]));
 }
-__global__ void silu_bwd_kernel(const float* __restrict__ x, const bf16* __restrict__ dy, bf16* __restrict__ dx,
+__global__ void silu_bwd_kernel(const float* __restrict__ x, const h16* __restrict__ dy, h16* __restrict__ dx,
                                 long long n) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
-    dx[i] = __float2bfloat16(__bfloat162float(dy[i]) * silu_grad_f(x[i]));
+    dx[i] = f2h(h2f(dy[i]) * silu_grad_f(x[i]));
 }
-int launch_silu_fwd(const float* x, bf16* y, long long n, cudaStream_t s) {
+int launch_silu_fwd(const float* x, h16* y, long long n, cudaStream_t s) {
   silu_fwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, y, n);
   return static_cast<int>(cudaGetLastError());
 }
-int launch_silu_bwd(const float* x, const bf16* dy, bf16* dx, long long n, cudaStream_t s) {
+int launch_silu_bwd(const float* x, const h16* dy, h16* dx, long long n, cudaStream_t s) {
   silu_bwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, dy, dx, n);
   return static_cast<int>(cudaGetLastError());
 }
 
 // ---- GEGLU (attention.py:37-45) -------------------------------------------------------------------------------------
-__global__ void geglu_fwd_kernel(const bf16* __restrict__ g, bf16* __restrict__ out, long long M, int inner) {
+__global__ void geglu_fwd_kernel(const h16* __restrict__ g, h16* __restrict__ out, long long M, int inner) {
   const int nv = inner >> 3;
   const long long total = M * nv;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -65,7 +65,7 @@ __global__ void geglu_fwd_kernel(const bf16* __restrict__ g, bf16* __restrict__ 
     *reinterpret_cast<uint4*>(out + row * inner + c) = pack8(v);
   }
 }
-__global__ void geglu_bwd_kernel(const bf16* __restrict__ g, const bf16* __restrict__ dout, bf16* __restrict__ dg,
+__global__ void geglu_bwd_kernel(const h16* __restrict__ g, const h16* __restrict__ dout, h16* __restrict__ dg,
                                  long long M, int inner) {
   const int nv = inner >> 3;
   const long long total = M * nv;
@@ -86,12 +86,12 @@ __global__ void geglu_bwd_kernel(const bf16* __restrict__ g, const bf16* __restr
     *reinterpret_cast<uint4*>(dg + row * 2 * inner + inner + c) = pack8(dgt);
   }
 }
-int launch_geglu_fwd(const bf16* g, bf16* out, long long M, int inner, cudaStream_t s) {
+int launch_geglu_fwd(const h16* g, h16* out, long long M, int inner, cudaStream_t s) {
   if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
   geglu_fwd_kernel<<<grid_for(M * (inner / 8), 256), 256, 0, s>>>(g, out, M, inner);
   return static_cast<int>(cudaGetLastError());
 }
-int launch_geglu_bwd(const bf16* g, const bf16* dout, bf16* dg, long long M, int inner, cudaStream_t s) {
+int launch_geglu_bwd(const h16* g, const h16* dout, h16* dg, long long M, int inner, cudaStream_t s) {
   if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
   geglu_bwd_kernel<<<grid_for(M * (inner / 8), 256), 256, 0, s>>>(g, dout, dg, M, inner);
   return static_cast<int>(cudaGetLastError());
@@ -99,15 +99,16 @@ int launch_geglu_bwd(const bf16* g, const bf16* dout, bf16* dg, long long M, int
 
 // ---- bias gradient: column sums -------------------------------------------------------------------------------------
 // block = (32 column-lanes) x (8 row-lanes); grid.x tiles columns by 32, grid.y splits rows
-__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, long long M, int ld, int col0, int N,
-                                                     float* __restrict__ dst0, float* __restrict__ dst1) {
+__global__ void __launch_bounds__(256) colsum_kernel(const h16* __restrict__ x, long long M, int ld, int col0, int N,
+                                                     float* __restrict__ dst0, float* __restrict__ dst1,
+                                                     const float* __restrict__ gscale) {
   __shared__ float red[8][33];
   const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + cl;
   float a = 0.f;
   if (col < N) {
     for (long long r = blockIdx.y * 8 + rl; r < M; r += static_cast<long long>(gridDim.y) * 8)
-      a += __bfloat162float(x[r * ld + col0 + col]);
+      a += h2f(x[r * ld + col0 + col]);
   }
   red[rl][cl] = a;
   __syncthreads();
@@ -115,33 +116,35 @@ __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x,
     float t = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) t += red[i][cl];
+    if (gscale) t *= gscale[1];
     atomicAdd(dst0 + col, t);
     if (dst1) atomicAdd(dst1 + col, t);
   }
 }
-int launch_colsum(const bf16* x, long long M, int ld, int col0, int N, float* dst0, float* dst1, cudaStream_t s) {
+int launch_colsum(const h16* x, long long M, int ld, int col0, int N, float* dst0, float* dst1, const float* gscale,
+                  cudaStream_t s) {
   const int gx = (N + 31) / 32;
   long long gy = (M + 8 * 32 - 1) / (8 * 32);   // >= 32 rows per thread
   const long long cap = (148 * 8 + gx - 1) / gx;
   if (gy > cap) gy = cap;
   if (gy < 1) gy = 1;
-  colsum_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, 0, s>>>(x, M, ld, col0, N, dst0, dst1);
+  colsum_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, 0, s>>>(x, M, ld, col0, N, dst0, dst1, gscale);
   return static_cast<int>(cudaGetLastError());
 }
 
-// ---- input stem: (optional q_sample) + NCHW fp32 -> im2col bf16 [B*H*W, 64], column ci*9 + tap ----------------------
+// ---- input stem: (optional q_sample) + NCHW fp32 -> im2col h16 [B*H*W, 64], column ci*9 + tap ----------------------
 __global__ void stem_im2col_kernel(const float* __restrict__ x, const float* __restrict__ noise,
                                    const float* __restrict__ sa, const float* __restrict__ sb, float* __restrict__ xt,
-                                   bf16* __restrict__ cols, int B, int Cin, int H, int W) {
+                                   h16* __restrict__ cols, int B, int Cin, int H, int W) {
   const long long total = static_cast<long long>(B) * H * W;
   for (long long pix = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; pix < total;
        pix += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int b = static_cast<int>(pix / (H * W));
     const int rem = static_cast<int>(pix - static_cast<long long>(b) * H * W);
     const int y = rem / W, xx = rem - y * W;
-    bf16 row[64];
+    h16 row[64];
 #pragma unroll
-    for (int i = 0; i < 64; ++i) row[i] = __float2bfloat16(0.f);
+    for (int i = 0; i < 64; ++i) row[i] = f2h(0.f);
     for (int ci = 0; ci < Cin; ++ci) {
       const long long plane = (static_cast<long long>(b) * Cin + ci) * H * W;
       for (int t = 0; t < 9; ++t) {
@@ -151,7 +154,7 @@ __global__ void stem_im2col_kernel(const float* __restrict__ x, const float* __r
           v = x[plane + yy * W + xs];
           if (noise) v = sa[b] * v + sb[b] * noise[plane + yy * W + xs];
         }
-        if (ci * 9 + t < 64) row[ci * 9 + t] = __float2bfloat16(v);
+        if (ci * 9 + t < 64) row[ci * 9 + t] = f2h(v);
         if (t == 4 && xt) xt[plane + y * W + xx] = v;
       }
     }
@@ -161,7 +164,7 @@ __global__ void stem_im2col_kernel(const float* __restrict__ x, const float* __r
     for (int i = 0; i < 8; ++i) dst[i] = src[i];
   }
 }
-int launch_stem_im2col(const float* x, const float* noise, const float* sa, const float* sb, float* xt, bf16* cols,
+int launch_stem_im2col(const float* x, const float* noise, const float* sa, const float* sb, float* xt, h16* cols,
                        int B, int Cin, int H, int W, cudaStream_t s) {
   if (Cin * 9 > 64) return static_cast<int>(cudaErrorInvalidValue);
   stem_im2col_kernel<<<grid_for(static_cast<long long>(B) * H * W, 128), 128, 0, s>>>(x, noise, sa, sb, xt, cols, B,
@@ -169,7 +172,9 @@ int launch_stem_im2col(const float* x, const float* noise, const float* sa, cons
   return static_cast<int>(cudaGetLastError());
 }
 
-__global__ void stem_col2im_kernel(const bf16* __restrict__ dcols, float* __restrict__ dx, int B, int Cin, int H, int W) {
+__global__ void stem_col2im_kernel(const h16* __restrict__ dcols, float* __restrict__ dx,
+                                   const float* __restrict__ gscale, int B, int Cin, int H, int W) {
+  const float ginv = gscale ? gscale[1] : 1.f;
   const long long total = static_cast<long long>(B) * Cin * H * W;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -182,13 +187,13 @@ __global__ void stem_col2im_kernel(const bf16* __restrict__ dcols, float* __rest
     for (int t = 0; t < 9; ++t) {
       const int oy = y - (t / 3 - 1), ox = xx - (t % 3 - 1);
       if (oy >= 0 && oy < H && ox >= 0 && ox < W)
-        a += __bfloat162float(dcols[((static_cast<long long>(b) * H + oy) * W + ox) * 64 + ci * 9 + t]);
+        a += h2f(dcols[((static_cast<long long>(b) * H + oy) * W + ox) * 64 + ci * 9 + t]);
     }
-    dx[idx] = a;
+    dx[idx] = a * ginv;
   }
 }
-int launch_stem_col2im(const bf16* dcols, float* dx, int B, int Cin, int H, int W, cudaStream_t s) {
-  stem_col2im_kernel<<<grid_for(static_cast<long long>(B) * Cin * H * W, 256), 256, 0, s>>>(dcols, dx, B, Cin, H, W);
+int launch_stem_col2im(const h16* dcols, float* dx, const float* gscale, int B, int Cin, int H, int W, cudaStream_t s) {
+  stem_col2im_kernel<<<grid_for(static_cast<long long>(B) * Cin * H * W, 256), 256, 0, s>>>(dcols, dx, gscale, B, Cin, H, W);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -207,20 +212,50 @@ int launch_nhwc_to_nchw(const float* y, float* out, int B, int C, int H, int W, 
   nhwc_to_nchw_kernel<<<grid_for(static_cast<long long>(B) * C * H * W, 256), 256, 0, s>>>(y, out, B, C, H * W);
   return static_cast<int>(cudaGetLastError());
 }
-__global__ void nchw_to_nhwc_bf16_kernel(const float* __restrict__ x, bf16* __restrict__ out, int B, int C, int HW,
-                                         int Cpad) {
+__global__ void grad_scale_kernel(const float* __restrict__ x, long long n, float* __restrict__ gscale) {
+  float m = 0.f;
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, fabsf(x[i]));
+  m = warp_max(m);
+  __shared__ float red[32];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    t = warp_max(t);
+    if (threadIdx.x == 0) {
+      float sc = 1.f;
+#ifndef EDB_ACT_BF16
+      if (t > 0.f && isfinite(t)) {
+        int e;
+        frexpf(t, &e);                          // t = f * 2^e, f in [0.5, 1)
+        sc = ldexpf(1.f, -3 - e);               // sc * t in [2^-4, 2^-3)
+      }
+#endif
+      gscale[0] = sc;
+      gscale[1] = 1.f / sc;
+    }
+  }
+}
+int launch_grad_scale(const float* x, long long n, float* gscale, cudaStream_t s) {
+  grad_scale_kernel<<<1, 1024, 0, s>>>(x, n, gscale);
+  return static_cast<int>(cudaGetLastError());
+}
+__global__ void nchw_to_nhwc_h16_kernel(const float* __restrict__ x, h16* __restrict__ out,
+                                         const float* __restrict__ gscale, int B, int C, int HW, int Cpad) {
+  const float gsc = gscale ? gscale[0] : 1.f;
   const long long total = static_cast<long long>(B) * HW * Cpad;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c = static_cast<int>(idx % Cpad);
     const int p = static_cast<int>((idx / Cpad) % HW);
     const long long b = idx / (static_cast<long long>(Cpad) * HW);
-    out[idx] = __float2bfloat16(c < C ? x[(b * C + c) * HW + p] : 0.f);
+    out[idx] = f2h(c < C ? x[(b * C + c) * HW + p] * gsc : 0.f);
   }
 }
-int launch_nchw_to_nhwc_bf16(const float* x, bf16* out, int B, int C, int H, int W, int Cpad, cudaStream_t s) {
-  nchw_to_nhwc_bf16_kernel<<<grid_for(static_cast<long long>(B) * H * W * Cpad, 256), 256, 0, s>>>(x, out, B, C, H * W,
-                                                                                                  Cpad);
+int launch_nchw_to_nhwc_h16(const float* x, h16* out, const float* gscale, int B, int C, int H, int W, int Cpad,
+                            cudaStream_t s) {
+  nchw_to_nhwc_h16_kernel<<<grid_for(static_cast<long long>(B) * H * W * Cpad, 256), 256, 0, s>>>(x, out, gscale, B, C,
+                                                                                                  H * W, Cpad);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -317,8 +352,8 @@ int launch_ddim_update_indexed(const float* x, const float* e_t, const float* no
   return static_cast<int>(cudaGetLastError());
 }
 
-// ---- weight packing: fp32 reference-layout parameters -> bf16 GEMM operands (and fused fp32 biases) -------------------
-__global__ void pack_kernel(const PackEntry* __restrict__ tab, int n_entries, long long total, bf16* __restrict__ abf,
+// ---- weight packing: fp32 reference-layout parameters -> h16 GEMM operands (and fused fp32 biases) -------------------
+__global__ void pack_kernel(const PackEntry* __restrict__ tab, int n_entries, long long total, h16* __restrict__ abf,
                             float* __restrict__ af32) {
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -346,13 +381,13 @@ __global__ void pack_kernel(const PackEntry* __restrict__ tab, int n_entries, lo
         case 4: row = en.row0 + r; col = en.col0 + rem; break;
         default: row = en.row0 + rem; col = en.col0 + r; break;   // 5
       }
-      abf[en.dst_off + row * en.dst_ld + col] = __float2bfloat16(v);
+      abf[en.dst_off + row * en.dst_ld + col] = f2h(v);
     }
   }
 }
-int launch_pack(const PackEntry* table_dev, int n_entries, long long total, bf16* arena_bf16, float* arena_f32,
+int launch_pack(const PackEntry* table_dev, int n_entries, long long total, h16* arena_h16, float* arena_f32,
                 cudaStream_t s) {
-  pack_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, s>>>(table_dev, n_entries, total, arena_bf16, arena_f32);
+  pack_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, s>>>(table_dev, n_entries, total, arena_h16, arena_f32);
   return static_cast<int>(cudaGetLastError());
 }
 

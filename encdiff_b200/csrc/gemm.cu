@@ -8,8 +8,8 @@
 namespace edb {
 
 static constexpr int kTileM = 128;   // pixels per tile (UMMA M)
-static constexpr int kChunk = 64;    // bf16 elements per 128-byte swizzle row
-static constexpr int kABytes = kTileM * kChunk * 2;  // 16 KB: one [128 x 64] bf16 box
+static constexpr int kChunk = 64;    // h16 elements per 128-byte swizzle row
+static constexpr int kABytes = kTileM * kChunk * 2;  // 16 KB: one [128 x 64] h16 box
 
 __device__ __forceinline__ void tile_origin(const TileGeom& g, int tile, int& b0, int& y0) {
   if (g.tiles_per_img > 1) {
@@ -100,8 +100,8 @@ __global__ void __launch_bounds__(192) sgemm_kernel(const __grid_constant__ Sgem
         const uint64_t db = make_sdesc(sa + kABytes, 16, 1024);
 #pragma unroll
         for (int k = 0; k < kChunk / 16; ++k) {
-          // advance 16 bf16 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-          umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          // advance 16 h16 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
+          umma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
         }
         umma_commit(&empty_bar[st]);
       }
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(192) sgemm_kernel(const __grid_constant__ Sgem
         for (int i = 0; i < 32; ++i) v[i] = silu_f(v[i]);
       }
       if (p.res) {
-        const bf16* r = reinterpret_cast<const bf16*>(p.res) + row * p.ldres + n0;
+        const h16* r = reinterpret_cast<const h16*>(p.res) + row * p.ldres + n0;
         if (nv == 32 && (p.ldres & 7) == 0) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(192) sgemm_kernel(const __grid_constant__ Sgem
             for (int i = 0; i < 8; ++i) v[8 * j + i] += f[i];
           }
         } else {
-          for (int i = 0; i < nv; ++i) v[i] += __bfloat162float(r[i]);
+          for (int i = 0; i < nv; ++i) v[i] += h2f(r[i]);
         }
       }
       void* dst = p.out0;
@@ -162,12 +162,12 @@ __global__ void __launch_bounds__(192) sgemm_kernel(const __grid_constant__ Sgem
           for (int i = 0; i < nv; ++i) o[i] = v[i];
         }
       } else {
-        bf16* o = reinterpret_cast<bf16*>(dst) + row * ld + col;
+        h16* o = reinterpret_cast<h16*>(dst) + row * ld + col;
         if (nv == 32 && (ld & 7) == 0) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(o + 8 * j) = pack8(v + 8 * j);
         } else {
-          for (int i = 0; i < nv; ++i) o[i] = __float2bfloat16(v[i]);
+          for (int i = 0; i < nv; ++i) o[i] = f2h(v[i]);
         }
       }
     }
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ Wgra
           // 16 pixels (the reduction) = 16 rows of 128 B = 2048 B per MMA step
           const uint64_t da = make_sdesc(sp + k * 2048, kABytes, 1024);
           const uint64_t db = make_sdesc(sp + P_BYTES + k * 2048, kABytes, 1024);
-          umma_bf16(tmem_base, da, db, idesc, (i | k) ? 1u : 0u);
+          umma_f16(tmem_base, da, db, idesc, (i | k) ? 1u : 0u);
         }
         umma_commit(&empty_bar[st]);
       }
@@ -296,6 +296,7 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ Wgra
     const int q = warp & 3;
     const int pc = p_tile * 128 + q * 32 + lane;  // channel on the dY side
     const bool row_ok = pc < p.Cp;
+    const float ginv = p.gscale ? __ldg(p.gscale + 1) : 1.f;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
 #pragma unroll 1
@@ -310,7 +311,7 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ Wgra
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         const int qc = qc0 + i;
-        if (qc < p.Cq) atomicAdd(o + static_cast<long long>(qc + p.q_off) * p.stride_q, v[i]);
+        if (qc < p.Cq) atomicAdd(o + static_cast<long long>(qc + p.q_off) * p.stride_q, v[i] * ginv);
       }
     }
   }

@@ -1,7 +1,7 @@
 // Parameter blocks + launchers of the two tcgen05 GEMM kernels.
 //
 //  sgemm  : "segmented implicit GEMM".  D[M, N] = sum_s sum_tap sum_chunk  A_s(shifted by tap)[M, 64] * Wt[N, 64]^T
-//           M = pixels (b, y, x) of an NHWC bf16 tensor, N = output channels, K = concatenation of up to three
+//           M = pixels (b, y, x) of an NHWC h16 tensor, N = output channels, K = concatenation of up to three
 //           sources, each either 1 tap (1x1 conv / linear) or 9 taps (3x3 conv, pad 1, realised by shifting the
 //           TMA box and letting TMA zero-fill out-of-bounds pixels).  Covers reference call sites
 //           nn.Conv2d 3x3 / 1x1 and nn.Linear (openaimodel_enc.py:201-241, attention.py:37-64,152-193,231-247)
@@ -26,8 +26,8 @@ struct TileGeom {
 };
 
 struct SgemmParams {
-  CUtensorMap amap[3];  // 4D (C, W, H, B) bf16 maps of the A sources, box (64, box_w, box_h, box_b), SWIZZLE_128B
-  CUtensorMap bmap;     // 2D (Ktot, Nrows) bf16 map of the packed weights, box (64, BN)
+  CUtensorMap amap[3];  // 4D (C, W, H, B) h16 maps of the A sources, box (64, box_w, box_h, box_b), SWIZZLE_128B
+  CUtensorMap bmap;     // 2D (Ktot, Nrows) h16 map of the packed weights, box (64, BN)
   int nsrc;
   int src_chunks[3];    // 64-channel chunks per source
   int src_taps[3];      // 1 or 9
@@ -35,10 +35,10 @@ struct SgemmParams {
   TileGeom g;
   int M, N;             // valid rows / columns
   const float* bias;    // [N] fp32 or null
-  const void* res;      // bf16 [M, ldres] added in the epilogue, or null
+  const void* res;      // h16 [M, ldres] added in the epilogue, or null
   int ldres;
   int act;              // ACT_*
-  int out_fp32;         // 0: bf16 out, 1: fp32 out
+  int out_fp32;         // 0: 16-bit out, 1: fp32 out
   void* out0;           // columns [0, split_col)
   int ld0;
   int split_col;        // >= N when there is a single destination; multiple of 32 otherwise
@@ -58,6 +58,7 @@ struct WgradParams {
   float* out;           // fp32 gradient, element (p, q, tap) at out[p*stride_p + (q+q_off)*stride_q + tap*stride_tap]
   long long stride_p, stride_q, stride_tap;
   int q_off;
+  const float* gscale;  // device {scale, 1/scale} of dY (null = 1): the fp32 result is multiplied by gscale[1]
 };
 
 // BN in {32(padded small N), 64, 128, 256}; returns cudaError_t as int

@@ -1,10 +1,17 @@
 #include "host.cuh"
+#include "types.cuh"
 
 #include <cudaTypedefs.h>
 
 #include <mutex>
 
 namespace edb {
+
+#ifdef EDB_ACT_BF16
+static const CUtensorMapDataType kMapType = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+#else
+static const CUtensorMapDataType kMapType = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+#endif
 
 static thread_local std::string g_last_error;
 void set_last_error(const std::string& msg) { g_last_error = msg; }
@@ -57,7 +64,7 @@ int make_act_tmap(CUtensorMap* m, const void* base, int C, int H, int W, int B, 
   cuuint32_t box[4] = {64, static_cast<cuuint32_t>(W), static_cast<cuuint32_t>(g.box_h),
                        static_cast<cuuint32_t>(g.box_b)};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(m, kMapType, 4, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -81,7 +88,7 @@ int make_w_tmap(CUtensorMap* m, const void* base, long long K, long long rows, i
   cuuint64_t strides[1] = {static_cast<cuuint64_t>(K) * 2};
   cuuint32_t box[2] = {64, static_cast<cuuint32_t>(bn)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(m, kMapType, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {

@@ -41,9 +41,9 @@ const char* last_error();
 // (H*W must be a power of two; W <= 128).
 bool make_geom(int H, int W, TileGeom* g);
 
-// 4D (C, W, H, B) bf16 NHWC activation map, box (64, W, box_h, box_b), SWIZZLE_128B, zero OOB fill.
+// 4D (C, W, H, B) h16 NHWC activation map, box (64, W, box_h, box_b), SWIZZLE_128B, zero OOB fill.
 int make_act_tmap(CUtensorMap* m, const void* base, int C, int H, int W, int B, const TileGeom& g);
-// 2D (K, rows) bf16 packed-weight map, box (64, bn), SWIZZLE_128B.
+// 2D (K, rows) h16 packed-weight map, box (64, bn), SWIZZLE_128B.
 int make_w_tmap(CUtensorMap* m, const void* base, long long K, long long rows, int bn);
 
 }  // namespace edb

@@ -1,13 +1,13 @@
-// Launchers of the non-GEMM kernels (HBM-bound: norms, attention, elementwise glue).  All tensors NHWC bf16
+// Launchers of the non-GEMM kernels (HBM-bound: norms, attention, elementwise glue).  All tensors NHWC h16
 // unless stated.  Every launcher returns a cudaError_t as int and only enqueues work on `stream`.
 #pragma once
-#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "types.cuh"
+
 namespace edb {
 
-typedef __nv_bfloat16 bf16;
 
 enum { RESAMPLE_NONE = 0, RESAMPLE_DOWN = 1, RESAMPLE_UP = 2 };
 
@@ -15,69 +15,76 @@ enum { RESAMPLE_NONE = 0, RESAMPLE_DOWN = 1, RESAMPLE_UP = 2 };
 // (y*(1+scale)+shift), SiLU and 2x average-pool / nearest-upsample.
 // Reference: GroupNorm32 util.py:227-244; ResBlock._forward openaimodel_enc.py:255-271; Normalize attention.py:76-77.
 struct GnParams {
-  const bf16* x0; int C0;      // [B, H*W, C0]
-  const bf16* x1; int C1;      // [B, H*W, C1] or null/0
+  const h16* x0; int C0;      // [B, H*W, C0]
+  const h16* x1; int C1;      // [B, H*W, C1] or null/0
   int H, W;                    // input spatial size
   const float* gamma; const float* beta;   // [C0+C1]
   const float* film; int ldfilm; int film_off;  // scale at film[b*ldfilm+film_off+c], shift at +C; null = no FiLM
   float eps; int silu; int resample;
   float* stats;                // [B, 32, 2] (mean, rstd): written by fwd, read by bwd
   // forward outputs
-  bf16* act;                   // [B, H'*W', C]
-  bf16* xs;                    // resampled raw input [B, H'*W', C] (only when resample != NONE), may be null
+  h16* act;                   // [B, H'*W', C]
+  h16* xs;                    // resampled raw input [B, H'*W', C] (only when resample != NONE), may be null
   // backward inputs/outputs
-  const bf16* dact;            // grad of act
-  const bf16* dxs;             // grad arriving on the (resampled) raw-input path or null; same resolution as act
-  bf16* dx0; int acc0;         // grad of x0 (acc: add to existing content)
-  bf16* dx1; int acc1;
+  const h16* dact;            // grad of act
+  const h16* dxs;             // grad arriving on the (resampled) raw-input path or null; same resolution as act
+  h16* dx0; int acc0;         // grad of x0 (acc: add to existing content)
+  h16* dx1; int acc1;
   float* dgamma; float* dbeta; // fp32 atomics
-  bf16* dfilm; int lddfilm;    // grad of film (same column layout), plain store
+  h16* dfilm; int lddfilm;    // grad of film (same column layout), plain store
+  const float* gscale;         // device {scale, 1/scale} of the activation gradients (null = 1): fp32 outputs are unscaled
 };
 int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s);
 int launch_gn_bwd(const GnParams& p, int B, cudaStream_t s);
 
 // LayerNorm over the last dim (attention.py:203-205, eps 1e-5).  stats [M,2] = (mean, rstd).
-int launch_ln_fwd(const bf16* x, const float* gamma, const float* beta, float eps, bf16* y, float* stats, int M, int C,
+int launch_ln_fwd(const h16* x, const float* gamma, const float* beta, float eps, h16* y, float* stats, int M, int C,
                   cudaStream_t s);
 // dx = dres + LN-backward(dy)   (dres = gradient of the residual branch that shares x, may be null)
-int launch_ln_bwd(const bf16* x, const float* stats, const float* gamma, const bf16* dy, const bf16* dres, bf16* dx,
-                  float* dgamma, float* dbeta, int M, int C, cudaStream_t s);
+int launch_ln_bwd(const h16* x, const float* stats, const float* gamma, const h16* dy, const h16* dres, h16* dx,
+                  float* dgamma, float* dbeta, const float* gscale, int M, int C, cudaStream_t s);
 
 // Self-attention over N tokens per sample (CrossAttention.forward with context=None, attention.py:170-193).
 // qkv [B*N, 3C] (q | k | v, head h at columns h*D), out [B*N, C], lse [B*heads*N] (log2 domain).
-int launch_self_attn_fwd(const bf16* qkv, bf16* out, float* lse, int B, int N, int heads, int D, cudaStream_t s);
-int launch_self_attn_bwd(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int B, int N,
+int launch_self_attn_fwd(const h16* qkv, h16* out, float* lse, int B, int N, int heads, int D, cudaStream_t s);
+int launch_self_attn_bwd(const h16* qkv, const h16* out, const h16* dout, const float* lse, h16* dqkv, int B, int N,
                          int heads, int D, cudaStream_t s);
 
 // Cross-attention against T concept tokens of width Dc (attention.py:170-193 with context; openaimodel_enc.py:729).
-// q [B*N, C] bf16, ctx [B, T, Dc] fp32, wk/wv [C, Dc] fp32 (reference to_k/to_v weights), out [B*N, C].
-int launch_cross_attn_fwd(const bf16* q, const float* ctx, const float* wk, const float* wv, bf16* out, int B, int N,
+// q [B*N, C] h16, ctx [B, T, Dc] fp32, wk/wv [C, Dc] fp32 (reference to_k/to_v weights), out [B*N, C].
+int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
                           int heads, int D, int T, int Dc, cudaStream_t s);
-int launch_cross_attn_bwd(const bf16* q, const float* ctx, const float* wk, const float* wv, const bf16* dout, bf16* dq,
-                          float* dwk, float* dwv, float* dctx, int B, int N, int heads, int D, int T, int Dc,
-                          cudaStream_t s);
+int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
+                          float* dwk, float* dwv, float* dctx, const float* gscale, int B, int N, int heads, int D, int T,
+                          int Dc, cudaStream_t s);
 
 // ---- elementwise glue -------------------------------------------------------------------------------------------
-// sinusoidal timestep embedding, cos half first (util.py:179-199): t [B] fp32 -> bf16 [B, dim]
-int launch_temb(const float* t, bf16* out, int B, int dim, cudaStream_t s);
-// y = silu(x): x fp32 [n] -> bf16;  dx = dy * silu'(x): dy bf16, x fp32 -> dx bf16
-int launch_silu_fwd(const float* x, bf16* y, long long n, cudaStream_t s);
-int launch_silu_bwd(const float* x, const bf16* dy, bf16* dx, long long n, cudaStream_t s);
+// sinusoidal timestep embedding, cos half first (util.py:179-199): t [B] fp32 -> h16 [B, dim]
+int launch_temb(const float* t, h16* out, int B, int dim, cudaStream_t s);
+// y = silu(x): x fp32 [n] -> h16;  dx = dy * silu'(x): dy h16, x fp32 -> dx h16
+int launch_silu_fwd(const float* x, h16* y, long long n, cudaStream_t s);
+int launch_silu_bwd(const float* x, const h16* dy, h16* dx, long long n, cudaStream_t s);
 // GEGLU (attention.py:37-45): g [M, 2*inner] (value | gate) -> out [M, inner] = value * gelu_erf(gate)
-int launch_geglu_fwd(const bf16* g, bf16* out, long long M, int inner, cudaStream_t s);
-int launch_geglu_bwd(const bf16* g, const bf16* dout, bf16* dg, long long M, int inner, cudaStream_t s);
-// bias gradient: dst0[n] (+= and dst1[n] +=) sum_m x[m, n]; x bf16 [M, ld] columns [col0, col0+N)
-int launch_colsum(const bf16* x, long long M, int ld, int col0, int N, float* dst0, float* dst1, cudaStream_t s);
-// input stem: x NCHW fp32 [B,Cin,H,W] (optionally q_sample'd: sa[b]*x + sb[b]*noise) -> im2col bf16 [B*H*W, 64],
+int launch_geglu_fwd(const h16* g, h16* out, long long M, int inner, cudaStream_t s);
+int launch_geglu_bwd(const h16* g, const h16* dout, h16* dg, long long M, int inner, cudaStream_t s);
+// bias gradient: dst0[n] (+= and dst1[n] +=) sum_m x[m, n]; x h16 [M, ld] columns [col0, col0+N)
+int launch_colsum(const h16* x, long long M, int ld, int col0, int N, float* dst0, float* dst1, const float* gscale,
+                  cudaStream_t s);
+// input stem: x NCHW fp32 [B,Cin,H,W] (optionally q_sample'd: sa[b]*x + sb[b]*noise) -> im2col h16 [B*H*W, 64],
 // column ci*9 + (ky*3+kx), zero padded; also writes x_t (NCHW fp32) when xt != null
-int launch_stem_im2col(const float* x, const float* noise, const float* sa, const float* sb, float* xt, bf16* cols,
+int launch_stem_im2col(const float* x, const float* noise, const float* sa, const float* sb, float* xt, h16* cols,
                        int B, int Cin, int H, int W, cudaStream_t s);
-// transpose of the above for the input gradient: dcols bf16 [B*H*W, 64] -> dx NCHW fp32 (overwrite)
-int launch_stem_col2im(const bf16* dcols, float* dx, int B, int Cin, int H, int W, cudaStream_t s);
+// transpose of the above for the input gradient: dcols h16 [B*H*W, 64] -> dx NCHW fp32 (overwrite)
+int launch_stem_col2im(const h16* dcols, float* dx, const float* gscale, int B, int Cin, int H, int W, cudaStream_t s);
 // head: y fp32 [B*H*W, C] (NHWC) -> out NCHW fp32
 int launch_nhwc_to_nchw(const float* y, float* out, int B, int C, int H, int W, cudaStream_t s);
-// dout NCHW fp32 [B,C,H,W] -> bf16 [B*H*W, Cpad] (zero padded)
-int launch_nchw_to_nhwc_bf16(const float* x, bf16* out, int B, int C, int H, int W, int Cpad, cudaStream_t s);
+// dout NCHW fp32 [B,C,H,W] -> h16 [B*H*W, Cpad] (zero padded)
+int launch_nchw_to_nhwc_h16(const float* x, h16* out, const float* gscale, int B, int C, int H, int W, int Cpad,
+                            cudaStream_t s);
+// Range scale of the backward pass: gscale[0] = 2^k with 2^k * max|x| in [2^-4, 2^-3) (1 when x == 0 or in the bf16
+// build), gscale[1] = 2^-k.  The h16 activation gradients are carried multiplied by gscale[0]; every fp32 gradient
+// output (weights, biases, norms, d context, dx) is multiplied by gscale[1].  One block; n = B*C*H*W.
+int launch_grad_scale(const float* x, long long n, float* gscale, cudaStream_t s);
 // L1 loss of p_losses (ddpm_enc.py:297-301,1198-1213): loss += mean|eps_hat-noise| ; deps = sign(eps_hat-noise)/numel
 int launch_l1_loss(const float* eps_hat, const float* noise, float* loss, float* deps, long long n, cudaStream_t s);
 // DDIM update (ddim.py:197-206); coef = {a_t, a_prev, sigma_t, sqrt_one_minus_at} (device fp32[4]); noise may be null
@@ -95,7 +102,7 @@ int launch_ddim_update_indexed(const float* x, const float* e_t, const float* no
 struct PackEntry {
   const float* src;      // fp32 parameter, reference layout [rows, cin, taps]
   const float* src2;     // second addend for kind 3
-  long long dst_off;     // element offset in the destination arena (bf16 for kinds 0/1, fp32 for kind 2/3)
+  long long dst_off;     // element offset in the destination arena (h16 for kinds 0/1, fp32 for kind 2/3)
   long long prefix;      // first global element index of this entry
   int kind;              // 0: dst[row0+r][col0 + tap*cin_pad + ci]   (forward, K = tap-major)
                          // 1: dst[row0+ci][col0 + tap*rows_pad + r]  (transposed, for the input gradient)
@@ -107,7 +114,7 @@ struct PackEntry {
   int cin_pad, rows_pad;
   int dst_ld, row0, col0;
 };
-int launch_pack(const PackEntry* table_dev, int n_entries, long long total, bf16* arena_bf16, float* arena_f32,
+int launch_pack(const PackEntry* table_dev, int n_entries, long long total, h16* arena_h16, float* arena_f32,
                 cudaStream_t s);
 
 // fused AdamW (+ optional EMA) over a flat fp32 parameter buffer (ddpm_enc.py:1598-1639, ema.py:25-44)

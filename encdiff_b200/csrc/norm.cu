@@ -10,7 +10,7 @@ namespace edb {
 // ---------------------------------------------------------------------------------------------------------------
 struct GnThread {
   int C, nv, HW, chunk, prow, rp, c0;
-  const bf16* src;  // sample base of the source holding this thread's chunk
+  const h16* src;  // sample base of the source holding this thread's chunk
   int ld, cofs;
 };
 
@@ -35,8 +35,8 @@ __device__ __forceinline__ GnThread gn_thread(const GnParams& p, int b) {
   return t;
 }
 
-__device__ __forceinline__ void load8(const bf16* p, float* f) { unpack8(*reinterpret_cast<const uint4*>(p), f); }
-__device__ __forceinline__ void store8(bf16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
+__device__ __forceinline__ void load8(const h16* p, float* f) { unpack8(*reinterpret_cast<const uint4*>(p), f); }
+__device__ __forceinline__ void store8(h16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
 
 __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
   extern __shared__ float sm[];
@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
   }
   const int W = p.W, H = p.H;
   if (p.resample == RESAMPLE_NONE) {
-    bf16* dst = p.act + static_cast<long long>(b) * t.HW * C + t.c0;
+    h16* dst = p.act + static_cast<long long>(b) * t.HW * C + t.c0;
     for (int pix = t.prow; pix < t.HW; pix += t.rp) {
       float f[8];
       load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
@@ -127,8 +127,8 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
     }
   } else if (p.resample == RESAMPLE_DOWN) {
     const int Wo = W / 2, HWo = (H / 2) * Wo;
-    bf16* dst = p.act + static_cast<long long>(b) * HWo * C + t.c0;
-    bf16* dxs = p.xs ? p.xs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
+    h16* dst = p.act + static_cast<long long>(b) * HWo * C + t.c0;
+    h16* dxs = p.xs ? p.xs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
     for (int op = t.prow; op < HWo; op += t.rp) {
       const int oy = op / Wo, ox = op - oy * Wo;
       float ya[8], xa[8];
@@ -156,8 +156,8 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
     }
   } else {  // RESAMPLE_UP
     const int Wo = W * 2, HWo = 4 * t.HW;
-    bf16* dst = p.act + static_cast<long long>(b) * HWo * C + t.c0;
-    bf16* dxs = p.xs ? p.xs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
+    h16* dst = p.act + static_cast<long long>(b) * HWo * C + t.c0;
+    h16* dxs = p.xs ? p.xs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
     for (int pix = t.prow; pix < t.HW; pix += t.rp) {
       const int y = pix / W, x = pix - y * W;
       float f[8], ya[8];
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
 }
 
 // gradient arriving at input pixel (y, x) of a tensor that was resampled AFTER this point
-__device__ __forceinline__ void gather_resampled(const bf16* g, int C, int resample, int y, int x, int W, float* d) {
+__device__ __forceinline__ void gather_resampled(const h16* g, int C, int resample, int y, int x, int W, float* d) {
   if (resample == RESAMPLE_NONE) {
     load8(g + static_cast<long long>(y * W + x) * C, d);
   } else if (resample == RESAMPLE_DOWN) {
@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     S2[c] = 0.f;
   }
   __syncthreads();
-  const bf16* dact = p.dact + static_cast<long long>(b) * HWo * C + t.c0;
+  const h16* dact = p.dact + static_cast<long long>(b) * HWo * C + t.c0;
   float a[8], bb[8], mu[8], rs[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
@@ -275,13 +275,14 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     if (p.film) {
       sc = 1.f + p.film[static_cast<long long>(b) * p.ldfilm + p.film_off + c];
       if (p.dfilm) {
-        bf16* df = p.dfilm + static_cast<long long>(b) * p.lddfilm + p.film_off;
-        df[c] = __float2bfloat16(gam * s2 + bet * s1);   // d scale
-        df[C + c] = __float2bfloat16(s1);                // d shift
+        h16* df = p.dfilm + static_cast<long long>(b) * p.lddfilm + p.film_off;
+        df[c] = f2h(gam * s2 + bet * s1);   // d scale
+        df[C + c] = f2h(s1);                // d shift
       }
     }
-    if (p.dgamma) atomicAdd(&p.dgamma[c], sc * s2);
-    if (p.dbeta) atomicAdd(&p.dbeta[c], sc * s1);
+    const float ginv = p.gscale ? p.gscale[1] : 1.f;   // activation gradients carry the backward's range scale
+    if (p.dgamma) atomicAdd(&p.dgamma[c], sc * s2 * ginv);
+    if (p.dbeta) atomicAdd(&p.dbeta[c], sc * s1 * ginv);
     const float gsc = gam * sc;
     S1[c] = gsc * s1;
     S2[c] = gsc * s2;
@@ -308,7 +309,7 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     k2[k] = rs[k] * gAB[g];
     k3[k] = rs[k] * gAB[32 + g];
   }
-  bf16* dxp;
+  h16* dxp;
   int acc;
   if (t.c0 < p.C0) {
     dxp = p.dx0 + static_cast<long long>(b) * t.HW * p.C0 + t.cofs;
@@ -317,7 +318,7 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     dxp = p.dx1 + static_cast<long long>(b) * t.HW * p.C1 + t.cofs;
     acc = p.acc1;
   }
-  const bf16* dxs = p.dxs ? p.dxs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
+  const h16* dxs = p.dxs ? p.dxs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
   for (int pix = t.prow; pix < t.HW; pix += t.rp) {
     const int y = pix / W, x = pix - y * W;
     float f[8], d[8], o[8];
@@ -335,7 +336,7 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) o[k] += e[k];
     }
-    bf16* q = dxp + static_cast<long long>(pix) * t.ld;
+    h16* q = dxp + static_cast<long long>(pix) * t.ld;
     if (acc) {
       float e[8];
       load8(q, e);
@@ -390,8 +391,8 @@ __device__ __forceinline__ float group_sum(float v, int lpr) {
 }
 
 template <int CPL>
-__global__ void __launch_bounds__(256) ln_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ gamma,
-                                                     const float* __restrict__ beta, float eps, bf16* __restrict__ y,
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const h16* __restrict__ x, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, float eps, h16* __restrict__ y,
                                                      float* __restrict__ stats, int M, int C, int lpr) {
   const int nchunks = C >> 3;
   const int rows_per_block = blockDim.x / lpr;
@@ -444,11 +445,11 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const bf16* __restrict__ x,
 }
 
 template <int CPL>
-__global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ stats,
-                                                     const float* __restrict__ gamma, const bf16* __restrict__ dy,
-                                                     const bf16* __restrict__ dres, bf16* __restrict__ dx,
-                                                     float* __restrict__ dgamma, float* __restrict__ dbeta, int M, int C,
-                                                     int lpr) {
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const h16* __restrict__ x, const float* __restrict__ stats,
+                                                     const float* __restrict__ gamma, const h16* __restrict__ dy,
+                                                     const h16* __restrict__ dres, h16* __restrict__ dx,
+                                                     float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                     const float* __restrict__ gscale, int M, int C, int lpr) {
   extern __shared__ float sm[];  // [2*C] block partial sums of dgamma / dbeta
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
@@ -525,9 +526,10 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x,
     }
   }
   __syncthreads();
+  const float ginv = gscale ? gscale[1] : 1.f;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    atomicAdd(&dgamma[c], sm[c]);
-    atomicAdd(&dbeta[c], sm[C + c]);
+    atomicAdd(&dgamma[c], sm[c] * ginv);
+    atomicAdd(&dbeta[c], sm[C + c] * ginv);
   }
 }
 
@@ -540,7 +542,7 @@ static void ln_shape(int C, int* lpr, int* cpl) {
   *cpl = (nchunks + l - 1) / l;
 }
 
-int launch_ln_fwd(const bf16* x, const float* gamma, const float* beta, float eps, bf16* y, float* stats, int M, int C,
+int launch_ln_fwd(const h16* x, const float* gamma, const float* beta, float eps, h16* y, float* stats, int M, int C,
                   cudaStream_t s) {
   if (C % 8 != 0 || C < 64 || C > 1024) return static_cast<int>(cudaErrorInvalidValue);
   int lpr, cpl;
@@ -557,8 +559,8 @@ int launch_ln_fwd(const bf16* x, const float* gamma, const float* beta, float ep
   return static_cast<int>(cudaGetLastError());
 }
 
-int launch_ln_bwd(const bf16* x, const float* stats, const float* gamma, const bf16* dy, const bf16* dres, bf16* dx,
-                  float* dgamma, float* dbeta, int M, int C, cudaStream_t s) {
+int launch_ln_bwd(const h16* x, const float* stats, const float* gamma, const h16* dy, const h16* dres, h16* dx,
+                  float* dgamma, float* dbeta, const float* gscale, int M, int C, cudaStream_t s) {
   if (C % 8 != 0 || C < 64 || C > 1024) return static_cast<int>(cudaErrorInvalidValue);
   int lpr, cpl;
   ln_shape(C, &lpr, &cpl);
@@ -567,10 +569,10 @@ int launch_ln_bwd(const bf16* x, const float* stats, const float* gamma, const b
   if (grid > 148 * 4) grid = 148 * 4;
   const size_t smem = 2 * C * sizeof(float);
   switch (cpl) {
-    case 1: ln_bwd_kernel<1><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
-    case 2: ln_bwd_kernel<2><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
-    case 3: ln_bwd_kernel<3><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
-    case 4: ln_bwd_kernel<4><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, M, C, lpr); break;
+    case 1: ln_bwd_kernel<1><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
+    case 2: ln_bwd_kernel<2><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
+    case 3: ln_bwd_kernel<3><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
+    case 4: ln_bwd_kernel<4><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
   return static_cast<int>(cudaGetLastError());

@@ -23,15 +23,15 @@ struct ParamInfo {
   long long numel;
 };
 
-// a block-level activation (NHWC bf16) with its gradient buffer
+// a block-level activation (NHWC h16) with its gradient buffer
 struct Tn {
-  bf16* p = nullptr;
-  bf16* g = nullptr;
+  h16* p = nullptr;
+  h16* g = nullptr;
   int C = 0, H = 0, W = 0;
   bool ginit = false;
 };
 
-// one packed GEMM operand: bf16 [rows_pad, K] at element offset `off` of the packed bf16 arena
+// one packed GEMM operand: h16 [rows_pad, K] at element offset `off` of the packed h16 arena
 struct Packed {
   long long off = 0;
   long long rows = 0;   // padded rows
@@ -50,7 +50,7 @@ struct ResLayer {
   long long bias2_off = -1;           // fused conv2+skip bias in the fp32 arena (skipconv only)
   // plan
   Tn *x0 = nullptr, *x1 = nullptr, *y = nullptr;
-  bf16 *a1 = nullptr, *xs = nullptr, *h1 = nullptr, *a2 = nullptr;
+  h16 *a1 = nullptr, *xs = nullptr, *h1 = nullptr, *a2 = nullptr;
   float *st1 = nullptr, *st2 = nullptr;
 };
 
@@ -61,7 +61,7 @@ struct StLayer {
       ln1_w, ln1_b, ln2_w, ln2_b, ln3_w, ln3_b, pout_w, pout_b;
   Packed pinf, pint, qkvf, qkvt, o1f, o1t, q2f, q2t, o2f, o2t, ff1f, ff1t, ff2f, ff2t, poutf, poutt;
   Tn *x = nullptr, *y = nullptr;
-  bf16 *n = nullptr, *t0 = nullptr, *l1 = nullptr, *qkv = nullptr, *att = nullptr, *t1 = nullptr, *l2 = nullptr,
+  h16 *n = nullptr, *t0 = nullptr, *l1 = nullptr, *qkv = nullptr, *att = nullptr, *t1 = nullptr, *l2 = nullptr,
        *q2 = nullptr, *att2 = nullptr, *t2 = nullptr, *l3 = nullptr, *g = nullptr, *gg = nullptr, *t3 = nullptr;
   float *stn = nullptr, *ls1 = nullptr, *ls2 = nullptr, *ls3 = nullptr, *lse = nullptr;
 };
@@ -101,7 +101,7 @@ struct UNet {
   std::vector<PackEntry> table;     // src pointers resolved at bind()
   std::vector<int> table_src, table_src2;   // parameter index of each entry
   long long pack_total = 0;         // total source elements walked by the pack kernel
-  size_t table_bytes = 0, bf16_bytes = 0, f32_bytes = 0;
+  size_t table_bytes = 0, h16_bytes = 0, f32_bytes = 0;
   // binding
   std::vector<const float*> pptr;
   std::vector<float*> gptr;
@@ -114,15 +114,16 @@ struct UNet {
   size_t ws_bytes_persist = 0, ws_bytes_scratch = 0;
   std::vector<Tn> tn;               // block-level tensors; [0] = stem output
   std::vector<int> hs_of_in_block;  // tn index of each input block's output
-  bf16 *temb = nullptr, *a1e = nullptr, *a2e = nullptr, *cols = nullptr, *aH = nullptr, *dyH = nullptr, *dfilm = nullptr;
+  h16 *temb = nullptr, *a1e = nullptr, *a2e = nullptr, *cols = nullptr, *aH = nullptr, *dyH = nullptr, *dfilm = nullptr;
   float *z1 = nullptr, *z2 = nullptr, *film = nullptr, *stH = nullptr, *yH = nullptr;
+  float* gs = nullptr;       // {scale, 1/scale} of the activation gradients of the current backward (device)
   char* scratch = nullptr;
   // tensor-map caches
   std::map<std::tuple<const void*, int, int, int, int>, CUtensorMap> act_maps;
   std::map<std::tuple<const void*, long long, long long, int>, CUtensorMap> w_maps;
 
-  bf16* pbf() const { return reinterpret_cast<bf16*>(packed + table_bytes); }
-  float* pf32() const { return reinterpret_cast<float*>(packed + table_bytes + bf16_bytes); }
+  h16* pbf() const { return reinterpret_cast<h16*>(packed + table_bytes); }
+  float* pf32() const { return reinterpret_cast<float*>(packed + table_bytes + h16_bytes); }
 };
 
 int unet_build(UNet* u, const encdiff_unet_config* cfg);          // architecture + params + pack table

@@ -10,7 +10,7 @@ static long long ceil_to(long long v, long long m) { return (v + m - 1) / m * m;
 
 struct Builder {
   UNet* u;
-  long long bf_off = 0;    // bf16 arena cursor (elements)
+  long long bf_off = 0;    // h16 arena cursor (elements)
   long long f32_off = 0;   // fp32 arena cursor (elements)
 
   int add_param(const std::string& name, std::initializer_list<long long> shape) {
@@ -310,7 +310,7 @@ int unet_build(UNet* u, const encdiff_unet_config* c) {
   b.pack_t(u->headt, u->hc_w, c->out_channels, mc, 9, 0, 0);
 
   u->table_bytes = static_cast<size_t>(ceil_to(static_cast<long long>(u->table.size() * sizeof(PackEntry)), 1024));
-  u->bf16_bytes = static_cast<size_t>(ceil_to(b.bf_off * 2, 1024));
+  u->h16_bytes = static_cast<size_t>(ceil_to(b.bf_off * 2, 1024));
   u->f32_bytes = static_cast<size_t>(ceil_to(b.f32_off * 4, 1024));
   return EDB_OK;
 }

@@ -1,6 +1,7 @@
 // Workspace plan and the forward / backward launch sequences of the UNet (host only; every call enqueues kernels).
 #include <string.h>
 
+#include "common.cuh"
 #include "host.cuh"
 #include "unet.cuh"
 
@@ -37,19 +38,20 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
   a.base = ws;
   const int mc = c.model_channels, S = c.image_size;
   const size_t M0 = static_cast<size_t>(B) * S * S;
-  u->temb = a.take<bf16>(static_cast<size_t>(B) * mc);
+  u->temb = a.take<h16>(static_cast<size_t>(B) * mc);
   u->z1 = a.take<float>(static_cast<size_t>(B) * u->emb_ch);
-  u->a1e = a.take<bf16>(static_cast<size_t>(B) * u->emb_ch);
+  u->a1e = a.take<h16>(static_cast<size_t>(B) * u->emb_ch);
   u->z2 = a.take<float>(static_cast<size_t>(B) * u->emb_ch);
-  u->a2e = a.take<bf16>(static_cast<size_t>(B) * u->emb_ch);
+  u->a2e = a.take<h16>(static_cast<size_t>(B) * u->emb_ch);
   u->film = a.take<float>(static_cast<size_t>(B) * u->film_cols);
-  u->cols = a.take<bf16>(M0 * 64);
-  u->aH = a.take<bf16>(M0 * mc);
+  u->cols = a.take<h16>(M0 * 64);
+  u->aH = a.take<h16>(M0 * mc);
   u->stH = a.take<float>(static_cast<size_t>(B) * 64);
   u->yH = a.take<float>(M0 * c.out_channels);
   if (training) {
-    u->dfilm = a.take<bf16>(static_cast<size_t>(B) * u->film_cols);
-    u->dyH = a.take<bf16>(M0 * 8);
+    u->gs = a.take<float>(2);
+    u->dfilm = a.take<h16>(static_cast<size_t>(B) * u->film_cols);
+    u->dyH = a.take<h16>(M0 * 8);
   }
   // block-level tensors
   u->tn.clear();
@@ -58,8 +60,8 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
     Tn t;
     t.C = C;
     t.H = t.W = H;
-    t.p = a.take<bf16>(static_cast<size_t>(B) * H * H * C);
-    if (training) t.g = a.take<bf16>(static_cast<size_t>(B) * H * H * C);
+    t.p = a.take<h16>(static_cast<size_t>(B) * H * H * C);
+    if (training) t.g = a.take<h16>(static_cast<size_t>(B) * H * H * C);
     u->tn.push_back(t);
     return &u->tn.back();
   };
@@ -76,12 +78,12 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
         l.x0 = h;
         l.x1 = (first && skip) ? skip : nullptr;
         const int cin = l.c0 + l.c1;
-        l.a1 = a.take<bf16>(mo * cin);
-        l.xs = (l.up || l.down) ? a.take<bf16>(mo * cin) : nullptr;
+        l.a1 = a.take<h16>(mo * cin);
+        l.xs = (l.up || l.down) ? a.take<h16>(mo * cin) : nullptr;
         l.st1 = a.take<float>(static_cast<size_t>(B) * 64);
-        l.h1 = a.take<bf16>(mo * l.cout);
+        l.h1 = a.take<h16>(mo * l.cout);
         l.st2 = a.take<float>(static_cast<size_t>(B) * 64);
-        l.a2 = a.take<bf16>(mo * l.cout);
+        l.a2 = a.take<h16>(mo * l.cout);
         l.y = new_tn(l.cout, l.Hout);
         h = l.y;
       } else if (ly.kind == 2) {
@@ -89,25 +91,25 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
         const size_t m = static_cast<size_t>(B) * l.H * l.W;
         const int C = l.C;
         l.x = h;
-        l.n = a.take<bf16>(m * C);
+        l.n = a.take<h16>(m * C);
         l.stn = a.take<float>(static_cast<size_t>(B) * 64);
-        l.t0 = a.take<bf16>(m * C);
-        l.l1 = a.take<bf16>(m * C);
+        l.t0 = a.take<h16>(m * C);
+        l.l1 = a.take<h16>(m * C);
         l.ls1 = a.take<float>(m * 2);
-        l.qkv = a.take<bf16>(m * 3 * C);
-        l.att = a.take<bf16>(m * C);
+        l.qkv = a.take<h16>(m * 3 * C);
+        l.att = a.take<h16>(m * C);
         l.lse = a.take<float>(m * l.heads);
-        l.t1 = a.take<bf16>(m * C);
-        l.l2 = a.take<bf16>(m * C);
+        l.t1 = a.take<h16>(m * C);
+        l.l2 = a.take<h16>(m * C);
         l.ls2 = a.take<float>(m * 2);
-        l.q2 = a.take<bf16>(m * C);
-        l.att2 = a.take<bf16>(m * C);
-        l.t2 = a.take<bf16>(m * C);
-        l.l3 = a.take<bf16>(m * C);
+        l.q2 = a.take<h16>(m * C);
+        l.att2 = a.take<h16>(m * C);
+        l.t2 = a.take<h16>(m * C);
+        l.l3 = a.take<h16>(m * C);
         l.ls3 = a.take<float>(m * 2);
-        l.g = a.take<bf16>(m * 8 * C);
-        l.gg = a.take<bf16>(m * 4 * C);
-        l.t3 = a.take<bf16>(m * C);
+        l.g = a.take<h16>(m * 8 * C);
+        l.gg = a.take<h16>(m * 4 * C);
+        l.t3 = a.take<h16>(m * C);
         l.y = new_tn(C, l.H);
         h = l.y;
       }
@@ -155,7 +157,7 @@ size_t unet_workspace_bytes(UNet* u, int B, bool training) {
 // launch helpers
 // ---------------------------------------------------------------------------------------------------------------
 struct Src {
-  const bf16* p;
+  const h16* p;
   int C;
   int taps;
 };
@@ -197,7 +199,7 @@ struct Exec {
     }
   }
 
-  const CUtensorMap* act_map(const bf16* p, int C, int H, int W, const TileGeom& g) {
+  const CUtensorMap* act_map(const h16* p, int C, int H, int W, const TileGeom& g) {
     auto key = std::make_tuple(static_cast<const void*>(p), C, H, W, B);
     auto it = u->act_maps.find(key);
     if (it != u->act_maps.end()) return &it->second;
@@ -209,7 +211,7 @@ struct Exec {
     }
     return &u->act_maps.emplace(key, m).first->second;
   }
-  const CUtensorMap* w_map(const bf16* p, long long K, long long rows, int bn) {
+  const CUtensorMap* w_map(const h16* p, long long K, long long rows, int bn) {
     auto key = std::make_tuple(static_cast<const void*>(p), K, rows, bn);
     auto it = u->w_maps.find(key);
     if (it != u->w_maps.end()) return &it->second;
@@ -224,7 +226,7 @@ struct Exec {
 
   // out[M, N] = act(sum_s A_s * W^T + bias) + res ;  W = packed operand `pk` starting at row `row0`
   void gemm(std::initializer_list<Src> srcs, int H, int W, const Packed& pk, long long row0, int N, int tap_sign,
-            const float* bias, const bf16* res, int ldres, int act, bool fp32, void* out, int ld) {
+            const float* bias, const h16* res, int ldres, int act, bool fp32, void* out, int ld) {
     if (err) return;
     SgemmParams p;
     memset(&p, 0, sizeof(p));
@@ -268,7 +270,7 @@ struct Exec {
   }
 
   // grad[p, q(+q_off), tap] += sum_pix dy[pix, p_off + p] * x[pix, q]
-  void wgrad(const bf16* dy, int Cdy, int p_off, int Cp, const bf16* x, int Cx, int Cq, int H, int W, int taps,
+  void wgrad(const h16* dy, int Cdy, int p_off, int Cp, const h16* x, int Cx, int Cq, int H, int W, int taps,
              float* out, long long stride_p, long long stride_q, long long stride_tap, int q_off) {
     if (err || !out) return;
     WgradParams p;
@@ -292,6 +294,7 @@ struct Exec {
     p.stride_q = stride_q;
     p.stride_tap = stride_tap;
     p.q_off = q_off;
+    p.gscale = u->gs;
     const int bn = Cq <= 64 ? 64 : 128;
     const long long ctas = static_cast<long long>((Cp + 127) / 128) * taps * ((Cq + bn - 1) / bn);
     // enough CTAs to fill the chip, but keep the number of fp32 atomics (weights x splits) bounded
@@ -304,9 +307,9 @@ struct Exec {
     fail(launch_wgrad(p, bn, static_cast<int>(splits), s), "wgrad");
   }
 
-  void colsum(const bf16* x, long long M, int ld, int col0, int N, float* d0, float* d1 = nullptr) {
+  void colsum(const h16* x, long long M, int ld, int col0, int N, float* d0, float* d1 = nullptr) {
     if (err || !d0) return;
-    fail(launch_colsum(x, M, ld, col0, N, d0, d1, s), "colsum");
+    fail(launch_colsum(x, M, ld, col0, N, d0, d1, u->gs, s), "colsum");
   }
   const float* P(int idx) const { return u->pptr[idx]; }
   float* G(int idx) const { return u->gptr.empty() ? nullptr : u->gptr[idx]; }
@@ -370,7 +373,7 @@ static void res_forward(ResLayer& l, Exec& e) {
       e.gemm({{l.a2, l.cout, 9}, {l.x0->p, l.c0, 1}}, l.Hout, l.Wout, l.w2f, 0, l.cout, 1, bias, nullptr, 0, ACT_NONE,
              false, l.y->p, l.cout);
   } else {
-    const bf16* skip = (l.up || l.down) ? l.xs : l.x0->p;
+    const h16* skip = (l.up || l.down) ? l.xs : l.x0->p;
     e.gemm({{l.a2, l.cout, 9}}, l.Hout, l.Wout, l.w2f, 0, l.cout, 1, e.P(l.conv2_b), skip, l.cout, ACT_NONE, false,
            l.y->p, l.cout);
   }

@@ -320,7 +320,7 @@ class UNetModel(nn.Module):
         (B, _training), ws = next(iter(self._ws.items()))
         off = ptr.value - ws.data_ptr()
         n = B * h.value * w.value * c.value
-        t = ws[off:off + 2 * n].view(torch.bfloat16).view(B, h.value, w.value, c.value)
+        t = ws[off:off + 2 * n].view(_lib.act_dtype()).view(B, h.value, w.value, c.value)
         return t.float().permute(0, 3, 1, 2).contiguous()
 
     # ------------------------------------------------------------------------------------------------------------

@@ -22,6 +22,9 @@ extern "C" {
 
 /* Message of the last failing call on this thread ("" if none). */
 const char* encdiff_last_error(void);
+/* The 16-bit storage / tensor-core operand type the library was built with: 0 = fp16 (default), 1 = bf16
+ * (-DEDB_ACT_BF16).  Wherever this header says "h16" it means that type. */
+int encdiff_act_format(void);
 
 /* ---------------------------------------------------------------------------------------------------------------
  * Operator level: tensor-core GEMM families (tcgen05 + TMEM + TMA).
@@ -29,12 +32,12 @@ const char* encdiff_last_error(void);
  * ------------------------------------------------------------------------------------------------------------- */
 
 /* out[M = B*H*W, N] = act( sum_s conv_taps(A_s) * Wp^T + bias ) + res
- *   a_ptrs[s]     bf16 [B,H,W,a_channels[s]]; a_taps[s] = 1 (1x1 conv / linear) or 9 (3x3 conv, zero pad 1)
- *   w_packed      bf16 [w_rows, K], K = sum_s 64*ceil(a_channels[s]/64)*a_taps[s]; K order = source, tap (ky*3+kx),
+ *   a_ptrs[s]     h16 [B,H,W,a_channels[s]]; a_taps[s] = 1 (1x1 conv / linear) or 9 (3x3 conv, zero pad 1)
+ *   w_packed      h16 [w_rows, K], K = sum_s 64*ceil(a_channels[s]/64)*a_taps[s]; K order = source, tap (ky*3+kx),
  *                 channel; rows >= N padded to the N tile `bn` (0 = pick)
  *   tap_sign      +1 forward convolution, -1 mirrored taps (input gradient with transposed weights)
- *   bias          fp32 [N] or NULL; res bf16 [M, ldres] or NULL; act 0 none / 1 SiLU
- *   out0/out1     bf16 (out_fp32 = 0) or fp32 destinations; columns < split_col go to out0 (leading dim ld0), the
+ *   bias          fp32 [N] or NULL; res h16 [M, ldres] or NULL; act 0 none / 1 SiLU
+ *   out0/out1     h16 (out_fp32 = 0) or fp32 destinations; columns < split_col go to out0 (leading dim ld0), the
  *                 rest to out1 (ld1); out1 = NULL for a single destination                                      */
 int encdiff_op_sgemm(int nsrc, const void* const* a_ptrs /*host array*/, const int* a_channels /*host*/,
                      const int* a_taps /*host*/, int H, int W, int B, const void* w_packed, long long w_rows, int N,
@@ -42,7 +45,7 @@ int encdiff_op_sgemm(int nsrc, const void* const* a_ptrs /*host array*/, const i
                      int ld0, int split_col, void* out1, int ld1, int bn, void* stream);
 
 /* out[p*stride_p + (q+q_off)*stride_q + tap*stride_tap] += sum_pixels dy[pix, p] * x(shifted by tap)[pix, q]
- *   dy bf16 [B,H,W,Cp], x bf16 [B,H,W,Cq], out fp32 (atomically accumulated), taps 1 or 9,
+ *   dy h16 [B,H,W,Cp], x h16 [B,H,W,Cq], out fp32 (atomically accumulated), taps 1 or 9,
  *   splits = CTAs sharing the pixel reduction (>= 1), bn = Cq tile (0 = pick)                                   */
 int encdiff_op_wgrad(const void* dy, int Cp, const void* x, int Cq, int H, int W, int B, int taps, float* out,
                      long long stride_p, long long stride_q, long long stride_tap, int q_off, int bn, int splits,
@@ -77,7 +80,7 @@ int encdiff_unet_num_params(const encdiff_unet* h);
 int encdiff_unet_param_info(const encdiff_unet* h, int i, char* name /*host*/, int name_cap, long long* shape4 /*host*/,
                             int* ndim /*host*/);
 
-/* Sizes of the two caller-owned device buffers (bytes): the packed bf16 weight arena and the activation workspace
+/* Sizes of the two caller-owned device buffers (bytes): the packed h16 weight arena and the activation workspace
  * for a batch (training != 0 keeps every activation and adds gradient buffers). */
 long long encdiff_unet_packed_bytes(const encdiff_unet* h);
 long long encdiff_unet_workspace_bytes(encdiff_unet* h, int batch, int training);
@@ -87,7 +90,7 @@ long long encdiff_unet_workspace_bytes(encdiff_unet* h, int batch, int training)
  * inventory order.  Synchronises `stream` once (not a hot call). */
 int encdiff_unet_bind(encdiff_unet* h, const float* const* params /*host*/, float* const* grads /*host, may be NULL*/,
                       void* packed, void* stream);
-/* Re-pack fp32 parameters into bf16 GEMM operands (forward and transposed layouts).  Call after every optimiser /
+/* Re-pack fp32 parameters into h16 GEMM operands (forward and transposed layouts).  Call after every optimiser /
  * EMA update of the parameters (the reference mutates them in place, ema.py:46-76). */
 int encdiff_unet_pack_weights(encdiff_unet* h, void* stream);
 /* Assign the workspace (1 KB aligned, >= workspace_bytes(batch, training)); cheap when unchanged. */
@@ -112,7 +115,7 @@ int encdiff_unet_backward(encdiff_unet* h, int batch, const float* dout, const f
 int encdiff_unet_profile(encdiff_unet* h, int enable);
 long long encdiff_unet_profile_read(encdiff_unet* h, char* buf /*host*/, long long cap);
 
-/* Debug / parity-test hook: device pointer and shape of the NHWC bf16 output of one block of the LAST forward.
+/* Debug / parity-test hook: device pointer and shape of the NHWC h16 output of one block of the LAST forward.
  * section 0 = input_blocks[index], 1 = middle_block, 2 = output_blocks[index]; the tensor is [B, H, W, C].  The
  * reference exposes the same tensors through forward hooks on input_blocks / middle_block / output_blocks. */
 int encdiff_unet_debug_block(encdiff_unet* h, int section, int index, void** ptr /*host*/, int* C /*host*/,
@@ -136,8 +139,8 @@ int encdiff_ddim_select(const float* t_table, int* cursor, float* ts, int* idx, 
 int encdiff_ddim_update_indexed(const float* x, const float* e_t, const float* noise_table, const float* coef_table,
                                 const int* idx, float temperature, float* x_prev, float* pred_x0, long long n,
                                 void* stream);
-/* timestep_embedding (ldm/modules/diffusionmodules/util.py:179-199): t [B] fp32 -> bf16 [B, dim], cosine half first */
-int encdiff_timestep_embedding(const float* t, void* out_bf16, int batch, int dim, void* stream);
+/* timestep_embedding (ldm/modules/diffusionmodules/util.py:179-199): t [B] fp32 -> h16 [B, dim], cosine half first */
+int encdiff_timestep_embedding(const float* t, void* out_h16, int batch, int dim, void* stream);
 /* Fused AdamW (+EMA when ema != NULL) over flat fp32 buffers: torch.optim.AdamW as configured by
  * LatentDiffusion.configure_optimizers (ddpm_enc.py:1598-1639) and LitEma.forward (ldm/modules/ema.py:25-44). */
 int encdiff_adamw_step(float* p, const float* g, float* m, float* v, float* ema, long long n, float lr, float beta1,

@@ -1,5 +1,5 @@
 """UNet forward/backward parity on the GPU: CUDA path (through the C ABI) vs the CPU oracle on the same seeded inputs
-and vs the reference-generated golden vectors.  bf16 tensor-core math with fp32 accumulation: the north-star bar is
+and vs the reference-generated golden vectors.  16-bit tensor-core operands with fp32 accumulation: the north-star bar is
 max relative error <= 1e-2 on the eps prediction (relative to the output scale, the reference's own TF32 path is ~1e-3)."""
 import os
 
@@ -13,8 +13,30 @@ from oracle.make_golden import CONFIGS, seeded_inputs
 
 pytestmark = pytest.mark.gpu
 # North-star bar for the 16-bit path: max|err| / max|ref| <= 1e-2.
-GRAD_TOL = float(os.environ.get("ENCDIFF_GRAD_TOL", "4e-2"))   # per-tensor max|err| / max|ref| of dx / dctx; 2x for weights
-EPS_TOL = float(os.environ.get("ENCDIFF_EPS_TOL", "2e-2"))
+# fp16 build: the north-star bar itself (measured 2e-3).  bf16 build (-DEDB_ACT_BF16): 2e-2 — bf16 operand rounding alone
+# (weights + GEMM inputs, no other store) already gives 1.2e-2 on this network, see tools/precision_model.py and DESIGN.md.
+
+
+def _bf16_build():
+    from encdiff_b200 import _lib
+    return _lib.act_dtype() == torch.bfloat16
+
+
+def _tol(name, fp16, bf16):
+    return float(os.environ.get(name, bf16 if _bf16_build() else fp16))
+
+
+class _Tol:
+    @property
+    def eps(self):
+        return _tol("ENCDIFF_TOL.eps", 1e-2, 2e-2)
+
+    @property
+    def grad(self):      # per-tensor max|err| / max|ref| of dx / dctx; 2x for the 734 weight tensors
+        return _tol("ENCDIFF_TOL.grad", 1e-2, 4e-2)
+
+
+TOL = _Tol()
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 
 
@@ -47,7 +69,7 @@ def test_forward_vs_golden(cuda_device, fixture, cfgname):
     assert eps.shape == x.shape and eps.dtype == x.dtype
     err = rel_err(eps, g["eps"])
     print(f"{cfgname}: eps rel err {err:.3e}")
-    assert err <= EPS_TOL
+    assert err <= TOL.eps
 
 
 @pytest.mark.parametrize("cfgname,B", [("tiny", 5), ("shapes3d", 4)])
@@ -71,7 +93,7 @@ def test_forward_backward_vs_oracle(cuda_device, cfgname, B):
     eps = m(xd, t.to(cuda_device), context=[cd])
     loss = (eps - noise.to(cuda_device)).abs().mean()
     eps.backward(dout_o.to(cuda_device))
-    assert rel_err(eps.detach(), eps_o.detach()) <= EPS_TOL
+    assert rel_err(eps.detach(), eps_o.detach()) <= TOL.eps
     assert abs(loss.item() - loss_o.item()) <= 2e-3 * abs(loss_o.item())
     # gradients: bf16 activations/gradients with fp32 accumulation -> 3e-2 of each tensor's scale
     errs = {}
@@ -81,9 +103,9 @@ def test_forward_backward_vs_oracle(cuda_device, cfgname, B):
     worst = sorted(errs.items(), key=lambda kv: -kv[1])[:5]
     print("worst param-grad rel errs:", worst)
     print("dx", rel_err(xd.grad, xo.grad), "dctx", rel_err(cd.grad, co.grad))
-    assert rel_err(xd.grad, xo.grad) <= GRAD_TOL
-    assert rel_err(cd.grad, co.grad) <= GRAD_TOL
-    assert worst[0][1] <= 2 * GRAD_TOL, worst
+    assert rel_err(xd.grad, xo.grad) <= TOL.grad
+    assert rel_err(cd.grad, co.grad) <= TOL.grad
+    assert worst[0][1] <= 2 * TOL.grad, worst
     # global direction check: cosine between flattened gradients
     ga = torch.cat([prm.grad.flatten().cpu().double() for _, prm in m.named_parameters()])
     gb = torch.cat([p[n].grad.flatten().double() for n, _ in m.named_parameters()])
