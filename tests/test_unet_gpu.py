@@ -29,11 +29,11 @@ def _tol(name, fp16, bf16):
 class _Tol:
     @property
     def eps(self):
-        return _tol("ENCDIFF_TOL.eps", 1e-2, 2e-2)
+        return _tol("ENCDIFF_EPS_TOL", 1e-2, 2e-2)
 
     @property
     def grad(self):      # per-tensor max|err| / max|ref| of dx / dctx; 2x for the 734 weight tensors
-        return _tol("ENCDIFF_TOL.grad", 1e-2, 4e-2)
+        return _tol("ENCDIFF_GRAD_TOL", 1e-2, 4e-2)
 
 
 TOL = _Tol()
