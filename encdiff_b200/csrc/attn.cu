@@ -292,23 +292,39 @@ int launch_self_attn_bwd(const h16* qkv, const h16* out, const h16* dout, const 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// cross-attention against T <= 32 context tokens: one CTA per sample
+// cross-attention against T <= 32 concept tokens (attention.py:170-193 with context; openaimodel_enc.py:729).
+// CTA = (sample, chunk of TQ <= 32 query tokens); item = (head, token) with the token fastest, so a warp works on one
+// head and every K/V read from shared memory is a broadcast.  to_k / to_v (K = context_dim = 16) are applied inside
+// the CTA: K, V [heads][T][D] fp32 stay resident in shared memory, softmax over T in registers.
 // ---------------------------------------------------------------------------------------------------------------
 static constexpr int kMaxT = 32;
+static constexpr int kMaxDc = 16;
 
-// K[j][c] = sum_e ctx[b][j][e] * wk[c][e]   (to_k / to_v without bias, attention.py:161-162)
+// Ks/Vs[(h*T + j)*D + d] = sum_e ctx_s[j][e] * w[h*D + d][e]      (to_k / to_v, no bias: attention.py:161-162)
+template <int D>
 __device__ __forceinline__ void project_ctx(const float* __restrict__ ctx_s, const float* __restrict__ wk,
                                             const float* __restrict__ wv, float* Ks, float* Vs, int T, int C, int Dc) {
-  for (int idx = threadIdx.x; idx < T * C; idx += blockDim.x) {
-    const int j = idx / C, c = idx - j * C;
-    float k = 0.f, v = 0.f;
-    for (int e = 0; e < Dc; ++e) {
-      const float x = ctx_s[j * Dc + e];
-      k += x * __ldg(wk + c * Dc + e);
-      v += x * __ldg(wv + c * Dc + e);
+  const int groups = blockDim.x >= C ? blockDim.x / C : 1;
+  for (int cc = threadIdx.x; cc < C * groups; cc += blockDim.x) {
+    const int c = cc % C, jg = cc / C;
+    float wkr[kMaxDc], wvr[kMaxDc];
+#pragma unroll
+    for (int e = 0; e < kMaxDc; ++e) {
+      wkr[e] = e < Dc ? __ldg(wk + c * Dc + e) : 0.f;
+      wvr[e] = e < Dc ? __ldg(wv + c * Dc + e) : 0.f;
     }
-    Ks[idx] = k;
-    Vs[idx] = v;
+    const int h = c / D, d = c - h * D;
+    for (int j = jg; j < T; j += groups) {
+      float k = 0.f, v = 0.f;
+#pragma unroll
+      for (int e = 0; e < kMaxDc; ++e) {
+        const float x = e < Dc ? ctx_s[j * Dc + e] : 0.f;
+        k += x * wkr[e];
+        v += x * wvr[e];
+      }
+      Ks[(h * T + j) * D + d] = k;
+      Vs[(h * T + j) * D + d] = v;
+    }
   }
 }
 
@@ -316,24 +332,27 @@ template <int D>
 __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restrict__ q, const float* __restrict__ ctx,
                                                              const float* __restrict__ wk, const float* __restrict__ wv,
                                                              h16* __restrict__ out, int N, int heads, int T, int Dc,
-                                                             float scale_log2) {
+                                                             int TQ, float scale_log2) {
   extern __shared__ float sm[];
   const int C = heads * D;
   float* Ks = sm;
   float* Vs = Ks + T * C;
   float* ctx_s = Vs + T * C;
-  const int b = blockIdx.x;
+  const int b = blockIdx.y, t0 = blockIdx.x * TQ;
   for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
   __syncthreads();
-  project_ctx(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
+  project_ctx<D>(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
   __syncthreads();
   constexpr int DC = D / 8;
-  for (int e = threadIdx.x; e < N * heads; e += blockDim.x) {
-    const int i = e / heads, h = e - i * heads;
-    const long long row = static_cast<long long>(b) * N + i;
+  for (int it = threadIdx.x; it < heads * TQ; it += blockDim.x) {
+    const int h = it / TQ, tk = t0 + (it - h * TQ);
+    if (tk >= N) continue;
+    const long long row = static_cast<long long>(b) * N + tk;
     float qv[D];
 #pragma unroll
     for (int dc = 0; dc < DC; ++dc) unpack8(*reinterpret_cast<const uint4*>(q + row * C + h * D + dc * 8), qv + dc * 8);
+    const float* Kh = Ks + h * T * D;
+    const float* Vh = Vs + h * T * D;
     float s[kMaxT];
     float m = -INFINITY;
 #pragma unroll
@@ -341,7 +360,10 @@ __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restri
       if (j < T) {
         float a = 0.f;
 #pragma unroll
-        for (int d = 0; d < D; ++d) a += qv[d] * Ks[j * C + h * D + d];
+        for (int d4 = 0; d4 < D / 4; ++d4) {
+          const float4 kv = *reinterpret_cast<const float4*>(Kh + j * D + 4 * d4);
+          a += qv[4 * d4] * kv.x + qv[4 * d4 + 1] * kv.y + qv[4 * d4 + 2] * kv.z + qv[4 * d4 + 3] * kv.w;
+        }
         s[j] = a * scale_log2;
         m = fmaxf(m, s[j]);
       }
@@ -363,7 +385,13 @@ __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restri
       if (j < T) {
         const float p = s[j] * inv;
 #pragma unroll
-        for (int d = 0; d < D; ++d) acc[d] += p * Vs[j * C + h * D + d];
+        for (int d4 = 0; d4 < D / 4; ++d4) {
+          const float4 vv = *reinterpret_cast<const float4*>(Vh + j * D + 4 * d4);
+          acc[4 * d4] += p * vv.x;
+          acc[4 * d4 + 1] += p * vv.y;
+          acc[4 * d4 + 2] += p * vv.z;
+          acc[4 * d4 + 3] += p * vv.w;
+        }
       }
     }
 #pragma unroll
@@ -371,136 +399,225 @@ __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restri
   }
 }
 
+// Backward, kernel 1 (same CTA / item mapping as the forward): per (head, token) recompute p, then
+//   dS = p * (dO.V - delta) * scale ;  dq = dS K ;  and, through a shared-memory mini-GEMM over the chunk's tokens,
+//   dK[j][c] += sum_t dS[t][j] q[t][c],  dV[j][c] += sum_t p[t][j] dO[t][c]   -> fp32 atomics into dkv[b][j][0..2C)
+// (at most N / TQ <= 8 CTAs add into the same sample's rows).  All chunk-local arrays are token-fastest with a row
+// pitch of TQP = TQ + 4 floats: stores by (head, token) items and float4 reads by (channel, key-group) threads are
+// both bank-conflict free.
 template <int D>
 __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const h16* __restrict__ q, const float* __restrict__ ctx,
                                                              const float* __restrict__ wk, const float* __restrict__ wv,
                                                              const h16* __restrict__ dout, h16* __restrict__ dq,
-                                                             float* __restrict__ dwk, float* __restrict__ dwv,
-                                                             float* __restrict__ dctx,
-                                                             const float* __restrict__ gscale, int N, int heads, int T,
-                                                             int Dc, float scale) {
-  const float ginv = gscale ? gscale[1] : 1.f;
+                                                             float* __restrict__ dkv, int N, int heads, int T, int Dc,
+                                                             int TQ, float scale) {
   extern __shared__ float sm[];
   const int C = heads * D;
-  float* Ks = sm;                   // [T][C]
-  float* Vs = Ks + T * C;           // [T][C]
-  float* ctx_s = Vs + T * C;        // [T][Dc]
-  float* dctx_s = ctx_s + T * Dc;   // [T][Dc]
-  float* Ps = dctx_s + T * Dc;      // [N][T]
-  float* dSs = Ps + N * T;          // [N][T]
-  float* dKh = dSs + N * T;         // [T][D]
-  float* dVh = dKh + T * D;         // [T][D]
-  const int b = blockIdx.x;
+  const int TQP = TQ + 4;
+  float* Ks = sm;                        // [heads][T][D]
+  float* Vs = Ks + T * C;
+  float* ctx_s = Vs + T * C;             // [T][Dc]
+  float* Ps = ctx_s + T * Dc;            // [heads][T][TQP]
+  float* dSs = Ps + heads * T * TQP;     // [heads][T][TQP]
+  float* qs = dSs + heads * T * TQP;     // [C][TQP]
+  float* dOs = qs + C * TQP;             // [C][TQP]
+  const int b = blockIdx.y, t0 = blockIdx.x * TQ;
   const float scale_log2 = scale * kLog2e;
-  for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) {
-    ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
-    dctx_s[i] = 0.f;
-  }
+  for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
   __syncthreads();
-  project_ctx(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
+  project_ctx<D>(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
   __syncthreads();
   constexpr int DC = D / 8;
-  for (int h = 0; h < heads; ++h) {
-    // phase 1: per query row -> p, dS, dq
-    for (int i = threadIdx.x; i < N; i += blockDim.x) {
-      const long long row = static_cast<long long>(b) * N + i;
-      float qv[D], dO[D];
+  for (int it = threadIdx.x; it < heads * TQ; it += blockDim.x) {
+    const int h = it / TQ, tl = it - h * TQ, tk = t0 + tl;
+    float* Pr = Ps + h * T * TQP + tl;       // element j at Pr[j * TQP]
+    float* dSr = dSs + h * T * TQP + tl;
+    float* qr = qs + h * D * TQP + tl;       // element d at qr[d * TQP]
+    float* dOr = dOs + h * D * TQP + tl;
+    if (tk >= N) {   // tail chunk: contribute zeros to the mini-GEMM
+      for (int j = 0; j < T; ++j) Pr[j * TQP] = dSr[j * TQP] = 0.f;
+      for (int d = 0; d < D; ++d) qr[d * TQP] = dOr[d * TQP] = 0.f;
+      continue;
+    }
+    const long long row = static_cast<long long>(b) * N + tk;
+    float qv[D], dO[D];
 #pragma unroll
-      for (int dc = 0; dc < DC; ++dc) {
-        unpack8(*reinterpret_cast<const uint4*>(q + row * C + h * D + dc * 8), qv + dc * 8);
-        unpack8(*reinterpret_cast<const uint4*>(dout + row * C + h * D + dc * 8), dO + dc * 8);
+    for (int dc = 0; dc < DC; ++dc) {
+      unpack8(*reinterpret_cast<const uint4*>(q + row * C + h * D + dc * 8), qv + dc * 8);
+      unpack8(*reinterpret_cast<const uint4*>(dout + row * C + h * D + dc * 8), dO + dc * 8);
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      qr[d * TQP] = qv[d];
+      dOr[d * TQP] = dO[d];
+    }
+    const float* Kh = Ks + h * T * D;
+    const float* Vh = Vs + h * T * D;
+    float s[kMaxT], dp[kMaxT];
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < kMaxT; ++j) {
+      if (j < T) {
+        float a = 0.f, c = 0.f;
+#pragma unroll
+        for (int d4 = 0; d4 < D / 4; ++d4) {
+          const float4 kv = *reinterpret_cast<const float4*>(Kh + j * D + 4 * d4);
+          const float4 vv = *reinterpret_cast<const float4*>(Vh + j * D + 4 * d4);
+          a += qv[4 * d4] * kv.x + qv[4 * d4 + 1] * kv.y + qv[4 * d4 + 2] * kv.z + qv[4 * d4 + 3] * kv.w;
+          c += dO[4 * d4] * vv.x + dO[4 * d4 + 1] * vv.y + dO[4 * d4 + 2] * vv.z + dO[4 * d4 + 3] * vv.w;
+        }
+        s[j] = a * scale_log2;
+        dp[j] = c;
+        m = fmaxf(m, s[j]);
       }
-      float s[kMaxT], dp[kMaxT];
-      float m = -INFINITY;
+    }
+    float l = 0.f;
 #pragma unroll
-      for (int j = 0; j < kMaxT; ++j) {
-        if (j < T) {
-          float a = 0.f, c = 0.f;
+    for (int j = 0; j < kMaxT; ++j) {
+      if (j < T) {
+        s[j] = exp2f(s[j] - m);
+        l += s[j];
+      }
+    }
+    const float inv = 1.f / l;
+    float delta = 0.f;
 #pragma unroll
-          for (int d = 0; d < D; ++d) {
-            a += qv[d] * Ks[j * C + h * D + d];
-            c += dO[d] * Vs[j * C + h * D + d];
-          }
-          s[j] = a * scale_log2;
-          dp[j] = c;
-          m = fmaxf(m, s[j]);
+    for (int j = 0; j < kMaxT; ++j) {
+      if (j < T) {
+        s[j] *= inv;
+        delta += s[j] * dp[j];
+      }
+    }
+    float dqv[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) dqv[d] = 0.f;
+#pragma unroll
+    for (int j = 0; j < kMaxT; ++j) {
+      if (j < T) {
+        const float ds = s[j] * (dp[j] - delta) * scale;
+        Pr[j * TQP] = s[j];
+        dSr[j * TQP] = ds;
+#pragma unroll
+        for (int d4 = 0; d4 < D / 4; ++d4) {
+          const float4 kv = *reinterpret_cast<const float4*>(Kh + j * D + 4 * d4);
+          dqv[4 * d4] += ds * kv.x;
+          dqv[4 * d4 + 1] += ds * kv.y;
+          dqv[4 * d4 + 2] += ds * kv.z;
+          dqv[4 * d4 + 3] += ds * kv.w;
         }
       }
-      float l = 0.f;
-#pragma unroll
-      for (int j = 0; j < kMaxT; ++j) {
-        if (j < T) {
-          s[j] = exp2f(s[j] - m);
-          l += s[j];
-        }
-      }
-      const float inv = 1.f / l;
-      float delta = 0.f;
-#pragma unroll
-      for (int j = 0; j < kMaxT; ++j) {
-        if (j < T) {
-          s[j] *= inv;
-          delta += s[j] * dp[j];
-        }
-      }
-      float dqv[D];
-#pragma unroll
-      for (int d = 0; d < D; ++d) dqv[d] = 0.f;
-#pragma unroll
-      for (int j = 0; j < kMaxT; ++j) {
-        if (j < T) {
-          const float ds = s[j] * (dp[j] - delta) * scale;
-          Ps[i * T + j] = s[j];
-          dSs[i * T + j] = ds;
-#pragma unroll
-          for (int d = 0; d < D; ++d) dqv[d] += ds * Ks[j * C + h * D + d];
-        }
-      }
-#pragma unroll
-      for (int dc = 0; dc < DC; ++dc) *reinterpret_cast<uint4*>(dq + row * C + h * D + dc * 8) = pack8(dqv + dc * 8);
     }
-    __syncthreads();
-    // phase 2: dK_h[j][d] = sum_i dS[i][j] q[i][d],  dV_h[j][d] = sum_i P[i][j] dO[i][d]
-    for (int e = threadIdx.x; e < T * D; e += blockDim.x) {
-      const int j = e / D, d = e - j * D;
-      float ak = 0.f, av = 0.f;
-      const h16* qc = q + static_cast<long long>(b) * N * C + h * D + d;
-      const h16* oc = dout + static_cast<long long>(b) * N * C + h * D + d;
-      for (int i = 0; i < N; ++i) {
-        ak += dSs[i * T + j] * h2f(qc[static_cast<long long>(i) * C]);
-        av += Ps[i * T + j] * h2f(oc[static_cast<long long>(i) * C]);
-      }
-      dKh[e] = ak;
-      dVh[e] = av;
-    }
-    __syncthreads();
-    // phase 3: weight and context gradients of this head
-    for (int e = threadIdx.x; e < D * Dc; e += blockDim.x) {
-      const int d = e / Dc, x = e - d * Dc;
-      float ak = 0.f, av = 0.f;
-      for (int j = 0; j < T; ++j) {
-        ak += dKh[j * D + d] * ctx_s[j * Dc + x];
-        av += dVh[j * D + d] * ctx_s[j * Dc + x];
-      }
-      atomicAdd(dwk + (h * D + d) * Dc + x, ak * ginv);
-      atomicAdd(dwv + (h * D + d) * Dc + x, av * ginv);
-    }
-    for (int e = threadIdx.x; e < T * Dc; e += blockDim.x) {
-      const int j = e / Dc, x = e - j * Dc;
-      float a = 0.f;
-      for (int d = 0; d < D; ++d)
-        a += dKh[j * D + d] * __ldg(wk + (h * D + d) * Dc + x) + dVh[j * D + d] * __ldg(wv + (h * D + d) * Dc + x);
-      dctx_s[e] += a;  // element e is owned by the same thread for every head
-    }
-    __syncthreads();
+#pragma unroll
+    for (int dc = 0; dc < DC; ++dc) *reinterpret_cast<uint4*>(dq + row * C + h * D + dc * 8) = pack8(dqv + dc * 8);
   }
-  for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) dctx[static_cast<long long>(b) * T * Dc + i] += dctx_s[i] * ginv;
+  __syncthreads();
+  // mini-GEMM: thread = (channel c, key group jg); q / dO columns are read once per 4 tokens and reused for its keys
+  float* dst = dkv + static_cast<long long>(b) * T * 2 * C;
+  const int groups = blockDim.x >= C ? blockDim.x / C : 1;
+  constexpr int kJ = 8;                   // keys per pass held in registers
+  for (int cc = threadIdx.x; cc < C * groups; cc += blockDim.x) {
+    const int c = cc % C, jg = cc / C, h = c / D;
+    const float* qc = qs + c * TQP;
+    const float* oc = dOs + c * TQP;
+    const float* Ph = Ps + h * T * TQP;
+    const float* dSh = dSs + h * T * TQP;
+    const int jper = (T + groups - 1) / groups;
+    const int jbeg = jg * jper, jend = min(T, jbeg + jper);
+    for (int j0 = jbeg; j0 < jend; j0 += kJ) {
+      float ak[kJ], av[kJ];
+#pragma unroll
+      for (int k = 0; k < kJ; ++k) ak[k] = av[k] = 0.f;
+      for (int t = 0; t < TQ; t += 4) {
+        const float4 q4 = *reinterpret_cast<const float4*>(qc + t);
+        const float4 o4 = *reinterpret_cast<const float4*>(oc + t);
+#pragma unroll
+        for (int k = 0; k < kJ; ++k) {
+          if (j0 + k < jend) {
+            const float4 d4 = *reinterpret_cast<const float4*>(dSh + (j0 + k) * TQP + t);
+            const float4 p4 = *reinterpret_cast<const float4*>(Ph + (j0 + k) * TQP + t);
+            ak[k] += d4.x * q4.x + d4.y * q4.y + d4.z * q4.z + d4.w * q4.w;
+            av[k] += p4.x * o4.x + p4.y * o4.y + p4.z * o4.z + p4.w * o4.w;
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kJ; ++k) {
+        if (j0 + k < jend) {
+          atomicAdd(dst + (j0 + k) * 2 * C + c, ak[k]);
+          atomicAdd(dst + (j0 + k) * 2 * C + C + c, av[k]);
+        }
+      }
+    }
+  }
 }
+
+// Backward, kernel 2: CTA handles samples blockIdx.x, blockIdx.x + gridDim.x, ...
+//   dctx[b][j][e] += ginv * sum_c (dK[b][j][c] wk[c][e] + dV[b][j][c] wv[c][e])           (single writer per sample)
+//   dwk[c][e]     += ginv * sum_b sum_j dK[b][j][c] ctx[b][j][e]   (registers over the CTA's samples, then atomics)
+__global__ void __launch_bounds__(256) cross_attn_bwd_proj_kernel(const float* __restrict__ dkv,
+                                                                  const float* __restrict__ ctx,
+                                                                  const float* __restrict__ wk,
+                                                                  const float* __restrict__ wv, float* __restrict__ dwk,
+                                                                  float* __restrict__ dwv, float* __restrict__ dctx,
+                                                                  const float* __restrict__ gscale, int B, int C, int T,
+                                                                  int Dc) {
+  extern __shared__ float sm[];
+  float* w_s = sm;                    // [2C][Dc]: wk rows then wv rows
+  float* g_s = w_s + 2 * C * Dc;      // [T][2C] dK | dV of the current sample
+  float* ctx_s = g_s + T * 2 * C;     // [T][Dc]
+  const float ginv = gscale ? gscale[1] : 1.f;
+  for (int i = threadIdx.x; i < C * Dc; i += blockDim.x) {
+    w_s[i] = wk[i];
+    w_s[C * Dc + i] = wv[i];
+  }
+  constexpr int kRows = 4;            // rows (of 2C) owned per thread for the weight gradient: 2C <= 4 * 256
+  float acc[kRows][kMaxDc];
+#pragma unroll
+  for (int r = 0; r < kRows; ++r)
+#pragma unroll
+    for (int e = 0; e < kMaxDc; ++e) acc[r][e] = 0.f;
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < T * 2 * C; i += blockDim.x) g_s[i] = dkv[static_cast<long long>(b) * T * 2 * C + i];
+    for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
+    __syncthreads();
+    for (int o = threadIdx.x; o < T * Dc; o += blockDim.x) {
+      const int j = o / Dc, e = o - j * Dc;
+      float a = 0.f;
+      for (int c = 0; c < 2 * C; ++c) a += g_s[j * 2 * C + c] * w_s[c * Dc + e];
+      dctx[static_cast<long long>(b) * T * Dc + o] += a * ginv;
+    }
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      const int row = threadIdx.x + r * 256;
+      if (row < 2 * C) {
+        for (int j = 0; j < T; ++j) {
+          const float g = g_s[j * 2 * C + row];
+#pragma unroll
+          for (int e = 0; e < kMaxDc; ++e)
+            if (e < Dc) acc[r][e] += g * ctx_s[j * Dc + e];
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) {
+    const int row = threadIdx.x + r * 256;
+    if (row < 2 * C) {
+      float* dst = row < C ? dwk + row * Dc : dwv + (row - C) * Dc;
+#pragma unroll
+      for (int e = 0; e < kMaxDc; ++e)
+        if (e < Dc) atomicAdd(dst + e, acc[r][e] * ginv);
+    }
+  }
+}
+
+static int cross_tq(int N) { return N < 32 ? N : 32; }
 
 template <int D>
 static int cross_fwd_t(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
                        int heads, int T, int Dc, cudaStream_t st) {
-  const int C = heads * D;
+  const int C = heads * D, TQ = cross_tq(N);
   const size_t smem = (2ull * T * C + T * Dc) * sizeof(float);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
@@ -508,31 +625,34 @@ static int cross_fwd_t(const h16* q, const float* ctx, const float* wk, const fl
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = smem;
   }
-  cross_attn_fwd_kernel<D><<<B, 256, smem, st>>>(q, ctx, wk, wv, out, N, heads, T, Dc,
-                                                 rsqrtf(static_cast<float>(D)) * kLog2e);
+  const int threads = heads * TQ >= 256 ? 256 : ((heads * TQ + 31) / 32) * 32;
+  dim3 grid((N + TQ - 1) / TQ, B);
+  cross_attn_fwd_kernel<D><<<grid, threads < 64 ? 64 : threads, smem, st>>>(q, ctx, wk, wv, out, N, heads, T, Dc, TQ,
+                                                                            rsqrtf(static_cast<float>(D)) * kLog2e);
   return static_cast<int>(cudaGetLastError());
 }
 
 template <int D>
 static int cross_bwd_t(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
-                       float* dwk, float* dwv, float* dctx, const float* gscale, int B, int N, int heads, int T, int Dc,
-                       cudaStream_t st) {
-  const int C = heads * D;
-  const size_t smem = (2ull * T * C + 2ull * T * Dc + 2ull * N * T + 2ull * T * D) * sizeof(float);
+                       float* dkv, int B, int N, int heads, int T, int Dc, cudaStream_t st) {
+  const int C = heads * D, TQ = cross_tq(N);
+  const size_t smem = (2ull * T * C + T * Dc + 2ull * heads * T * (TQ + 4) + 2ull * C * (TQ + 4)) * sizeof(float);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(cross_attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = smem;
   }
-  cross_attn_bwd_kernel<D><<<B, 256, smem, st>>>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, N, heads, T, Dc,
-                                                 rsqrtf(static_cast<float>(D)));
+  const int threads = heads * TQ >= 256 ? 256 : ((heads * TQ + 31) / 32) * 32;
+  dim3 grid((N + TQ - 1) / TQ, B);
+  cross_attn_bwd_kernel<D><<<grid, threads < 64 ? 64 : threads, smem, st>>>(q, ctx, wk, wv, dout, dq, dkv, N, heads, T, Dc,
+                                                                            TQ, rsqrtf(static_cast<float>(D)));
   return static_cast<int>(cudaGetLastError());
 }
 
 int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
                           int heads, int D, int T, int Dc, cudaStream_t s) {
-  if (T < 1 || T > kMaxT) return static_cast<int>(cudaErrorInvalidValue);
+  if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc) return static_cast<int>(cudaErrorInvalidValue);
   switch (D) {
     case 8: return cross_fwd_t<8>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s);
     case 16: return cross_fwd_t<16>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s);
@@ -542,17 +662,36 @@ int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const
   }
 }
 
+size_t cross_attn_bwd_scratch_bytes(int B, int heads, int D, int T) {
+  return static_cast<size_t>(B) * T * 2 * heads * D * sizeof(float);
+}
+
 int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
-                          float* dwk, float* dwv, float* dctx, const float* gscale, int B, int N, int heads, int D, int T,
-                          int Dc, cudaStream_t s) {
-  if (T < 1 || T > kMaxT) return static_cast<int>(cudaErrorInvalidValue);
+                          float* dwk, float* dwv, float* dctx, const float* gscale, float* dkv_scratch, int B, int N,
+                          int heads, int D, int T, int Dc, cudaStream_t s) {
+  if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc || 2 * heads * D > 4 * 256) return static_cast<int>(cudaErrorInvalidValue);
+  const int C = heads * D;
+  cudaError_t e = cudaMemsetAsync(dkv_scratch, 0, cross_attn_bwd_scratch_bytes(B, heads, D, T), s);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  int rc;
   switch (D) {
-    case 8: return cross_bwd_t<8>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
-    case 16: return cross_bwd_t<16>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
-    case 32: return cross_bwd_t<32>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
-    case 64: return cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dwk, dwv, dctx, gscale, B, N, heads, T, Dc, s);
+    case 8: rc = cross_bwd_t<8>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
+    case 16: rc = cross_bwd_t<16>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
+    case 32: rc = cross_bwd_t<32>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
+    case 64: rc = cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
+  if (rc) return rc;
+  const size_t smem = (2ull * C * Dc + 2ull * T * C + T * Dc) * sizeof(float);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    e = cudaFuncSetAttribute(cross_attn_bwd_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = smem;
+  }
+  const int grid = B < 148 ? B : 148;
+  cross_attn_bwd_proj_kernel<<<grid, 256, smem, s>>>(dkv_scratch, ctx, wk, wv, dwk, dwv, dctx, gscale, B, C, T, Dc);
+  return static_cast<int>(cudaGetLastError());
 }
 
 }  // namespace edb

@@ -55,8 +55,10 @@ int launch_self_attn_bwd(const h16* qkv, const h16* out, const h16* dout, const 
 int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
                           int heads, int D, int T, int Dc, cudaStream_t s);
 int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
-                          float* dwk, float* dwv, float* dctx, const float* gscale, int B, int N, int heads, int D, int T,
-                          int Dc, cudaStream_t s);
+                          float* dwk, float* dwv, float* dctx, const float* gscale, float* dkv_scratch, int B, int N,
+                          int heads, int D, int T, int Dc, cudaStream_t s);
+// bytes of the fp32 scratch [B, T, 2*heads*D] the backward needs (per-sample dK | dV before the to_k / to_v transpose)
+size_t cross_attn_bwd_scratch_bytes(int B, int heads, int D, int T);
 
 // ---- elementwise glue -------------------------------------------------------------------------------------------
 // sinusoidal timestep embedding, cos half first (util.py:179-199): t [B] fp32 -> h16 [B, dim]

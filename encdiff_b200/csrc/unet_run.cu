@@ -28,7 +28,7 @@ static size_t res_scratch(const ResLayer& l, int B) {
 }
 static size_t st_scratch(const StLayer& l, int B) {
   const size_t m = static_cast<size_t>(B) * l.H * l.W;
-  return m * l.C * 27 * 2 + 32768;   // dt3 dl3 dt2 datt2 dq2 dl2 dt1 datt dl1 dt0 dn (11) + dqkv (3) + dgg (4) + dg (8)
+  return m * l.C * 27 * 2 + static_cast<size_t>(B) * 32 * 2 * l.C * 4 + 65536;   // + cross-attention dK|dV scratch (T <= 32)   // dt3 dl3 dt2 datt2 dq2 dl2 dt1 datt dl1 dt0 dn (11) + dqkv (3) + dgg (4) + dg (8)
 }
 
 int unet_plan(UNet* u, int B, char* ws, bool training) {
