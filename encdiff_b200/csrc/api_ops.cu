@@ -1,6 +1,7 @@
 // C-ABI, operator level: the two tensor-core GEMM families exposed with raw pointers so that each can be checked
 // against the reference nn.Conv2d / nn.Linear call sites on its own (tests/test_gemm_gpu.py).
 #include "../../include/encdiff_b200.h"
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -28,6 +29,37 @@ extern "C" int encdiff_op_sgemm(int nsrc, const void* const* a_ptrs, const int* 
     p.src_chunks[s] = (a_channels[s] + 63) / 64;
     p.src_taps[s] = a_taps[s];
     K += 64LL * p.src_chunks[s] * a_taps[s];
+  }
+  const bool old_only = getenv("ENCDIFF_OLD_GEMM") != nullptr;
+  if (bn <= 0 && !out_fp32 && !out1 && ld0 == N && !old_only) {
+    const int sms = device_sm_count();
+    const int m_tiles = (B * H * W + 127) / 128;
+    const int bn2 = sgemm2_pick_bn(m_tiles, N, sms);
+    if (bn2) {   // persistent kernel (gemm2.cu)
+      Sgemm2Params q;
+      memset(&q, 0, sizeof(q));
+      for (int s = 0; s < nsrc; ++s) {
+        q.amap[s] = p.amap[s];
+        q.src_chunks[s] = p.src_chunks[s];
+        q.src_taps[s] = p.src_taps[s];
+      }
+      q.nsrc = nsrc;
+      q.g = p.g;
+      int rc2 = make_w_tmap(&q.bmap, w_packed, K, w_rows, bn2);
+      if (rc2) return rc2;
+      rc2 = make_out_tmap(&q.omap, out0, static_cast<long long>(B) * H * W, N, ld0);
+      if (rc2) return rc2;
+      q.tap_sign = tap_sign;
+      q.M = B * H * W;
+      q.N = N;
+      q.m_tiles = m_tiles;
+      q.bias = bias;
+      q.res = res;
+      q.ldres = ldres;
+      q.act = act;
+      EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_sgemm2(q, bn2, sms, static_cast<cudaStream_t>(stream))));
+      return EDB_OK;
+    }
   }
   if (bn <= 0) bn = sgemm_pick_bn(N);
   EDB_REQUIRE(w_rows >= ((N + bn - 1) / bn) * bn, "sgemm: packed weight rows must be padded to the N tile");

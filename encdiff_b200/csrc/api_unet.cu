@@ -1,4 +1,5 @@
 // C-ABI, model level: the UNet denoiser handle and the diffusion glue kernels (see include/encdiff_b200.h).
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -16,6 +17,7 @@ extern "C" int encdiff_unet_create(const encdiff_unet_config* cfg, encdiff_unet*
   EDB_REQUIRE(cfg && out, "unet_create: null argument");
   encdiff_unet* h = new (std::nothrow) encdiff_unet();
   EDB_REQUIRE(h, "unet_create: out of host memory");
+  h->u.force_old_gemm = getenv("ENCDIFF_OLD_GEMM") != nullptr;
   int rc = unet_build(&h->u, cfg);
   if (rc) {
     delete h;
@@ -78,6 +80,8 @@ extern "C" int encdiff_unet_bind(encdiff_unet* h, const float* const* params, fl
   EDB_CHECK_CUDA(cudaMemcpyAsync(packed, u.table.data(), u.table.size() * sizeof(PackEntry), cudaMemcpyHostToDevice, s));
   EDB_CHECK_CUDA(cudaStreamSynchronize(s));   // the host table may be re-bound later; bind is not a hot call
   u.w_maps.clear();
+  u.grad_maps.clear();
+  u.fin_dirty = true;
   u.bound = true;
   return EDB_OK;
 }

@@ -46,6 +46,23 @@ struct SgemmParams {
   int ld1;
 };
 
+// persistent kernel (gemm2.cu): 16-bit output with N % 64 == 0 and a dense [M, N] destination (leading dimension ldo)
+struct Sgemm2Params {
+  CUtensorMap amap[3];  // as SgemmParams
+  CUtensorMap bmap;     // 2D (Ktot, Nrows) packed weights, box (64, BN)
+  CUtensorMap omap;     // 2D (N, M) output, box (64, 128), SWIZZLE_128B (store side)
+  int nsrc;
+  int src_chunks[3];
+  int src_taps[3];
+  int tap_sign;
+  TileGeom g;
+  int M, N, m_tiles;
+  const float* bias;    // [N] fp32 or null
+  const void* res;      // 16-bit [M, ldres] or null
+  int ldres;
+  int act;
+};
+
 struct WgradParams {
   CUtensorMap pmap;     // dY   4D (Cp, W, H, B) box (64, ...)
   CUtensorMap qmap;     // X    4D (Cq, W, H, B) box (64, ...)
@@ -61,9 +78,34 @@ struct WgradParams {
   const float* gscale;  // device {scale, 1/scale} of dY (null = 1): the fp32 result is multiplied by gscale[1]
 };
 
+// persistent weight-gradient kernel (wgrad2.cu)
+struct Wgrad2Params {
+  CUtensorMap pmap;     // dY  4D (Cdy, W, H, B) box (64, ...)
+  CUtensorMap qmap;     // X   4D (Cx, W, H, B) box (64, ...)
+  CUtensorMap omap;     // fp32 destination: 2D (Cq_total, Cp) [linear / 1x1] or 3D (Cq, Cp, 9) tap-major staging
+                        // [conv3x3]; box (32, 128[, 1]), SWIZZLE_128B
+  TileGeom g;
+  int taps, m_tiles, tiles_per_split, splits, p_tiles, q_tiles;   // the last four are filled by the launcher
+  int Cp, Cq, p_off, q_off;
+  int out3d;            // 1: omap is the 3D staging map
+  float* bias0;         // += sum_pix dY[pix, p]   (null: the layer has no bias)
+  float* bias1;         // second destination of the same sum (conv2 + fused skip conv share dY) or null
+  const float* gscale;  // device {scale, 1/scale} of dY (null = 1)
+};
+struct WgradFinalizeEntry {
+  float* stage;         // [9][Cp][Cq]
+  float* grad;          // [Cp][Cq][9] reference layout
+  long long prefix;     // first global (p, q) index of this entry
+  long long pq;         // Cp * Cq
+};
+int launch_wgrad2(const Wgrad2Params& p, int num_sms, cudaStream_t stream);
+int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total, cudaStream_t s);
+
 // BN in {32(padded small N), 64, 128, 256}; returns cudaError_t as int
 int launch_sgemm(const SgemmParams& p, int bn, cudaStream_t stream);
 int launch_wgrad(const WgradParams& p, int bn, int splits, cudaStream_t stream);
 int sgemm_pick_bn(int N);
+int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t stream);
+int sgemm2_pick_bn(int m_tiles, int N, int num_sms);   // 0: shape not supported by the persistent kernel
 
 }  // namespace edb

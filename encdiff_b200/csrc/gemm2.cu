@@ -1,0 +1,248 @@
+// Persistent tcgen05 / TMEM / TMA implicit-GEMM kernel (sm_100a): the workhorse behind every conv3x3 / conv1x1 /
+// linear forward and input-gradient whose output is 16-bit with N % 64 == 0 (see gemm.cuh for the math; gemm.cu keeps
+// the one-tile-per-CTA kernel for fp32 / odd-N outputs).
+//
+//   grid = min(#tiles, #SMs); CTA c works on tiles c, c + grid, ... (n-tile fastest, so concurrently running CTAs
+//   share the A tile in L2).
+//   warp 0      TMA producer: A boxes (tap-shifted 4D loads, zero fill = conv padding) + weight boxes into a ring of
+//               STAGES shared-memory stages that runs ACROSS tiles (the next tile's loads start while the current
+//               tile's MMAs drain).
+//   warp 1      MMA issuer: one elected lane, tcgen05.mma into one of TWO TMEM accumulator stages.
+//   warps 2..5  epilogue: TMEM -> registers (tcgen05.ld) -> bias / SiLU / residual -> 16-bit -> 128B-swizzled staging
+//               panel in shared memory -> TMA store.  Runs concurrently with the mainloop of the next tile.
+#include "common.cuh"
+#include "gemm.cuh"
+
+namespace edb {
+
+static constexpr int kTileM2 = 128;
+static constexpr int kChunk2 = 64;
+static constexpr int kABytes2 = kTileM2 * kChunk2 * 2;   // 16 KB: one [128 x 64] 16-bit box
+static constexpr int kPanelBytes = kTileM2 * 128;        // 16 KB: [128 rows x 64 cols] 16-bit staging panel
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+__device__ __forceinline__ void tile_origin2(const TileGeom& g, int tile, int& b0, int& y0) {
+  if (g.tiles_per_img > 1) {
+    b0 = tile / g.tiles_per_img;
+    y0 = (tile - b0 * g.tiles_per_img) * g.box_h;
+  } else {
+    b0 = tile * g.box_b;
+    y0 = 0;
+  }
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(192, 1) sgemm2_kernel(const __grid_constant__ Sgemm2Params p) {
+  constexpr int B_BYTES = BN * kChunk2 * 2;
+  constexpr int STAGE_BYTES = kABytes2 + B_BYTES;
+  constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+  constexpr int PANELS = BN / 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + STAGES * STAGE_BYTES;                      // 2 panels
+  float* bias_s = reinterpret_cast<float*>(staging + 2 * kPanelBytes);  // [2][BN]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + 2 * BN);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull = empty_bar + STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n_tiles = (p.N + BN - 1) / BN;
+  const int total_tiles = p.m_tiles * n_tiles;
+
+  int nkb = 0;
+  for (int s = 0; s < p.nsrc; ++s) nkb += p.src_chunks[s] * p.src_taps[s];
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < p.nsrc; ++s) tma_prefetch_desc(&p.amap[s]);
+    tma_prefetch_desc(&p.bmap);
+    tma_prefetch_desc(&p.omap);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull[s], 1);
+      mbar_init(&tempty[s], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;   // running k-block counter across tiles
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m_tile = t / n_tiles, n_tile = t - m_tile * n_tiles;
+        int b0, y0;
+        tile_origin2(p.g, m_tile, b0, y0);
+        int kb = 0;
+        for (int s = 0; s < p.nsrc; ++s) {
+          const int taps = p.src_taps[s];
+          for (int tp = 0; tp < taps; ++tp) {
+            int dx = 0, dy = 0;
+            if (taps == 9) {
+              dy = (tp / 3 - 1) * p.tap_sign;
+              dx = (tp % 3 - 1) * p.tap_sign;
+            }
+            for (int c = 0; c < p.src_chunks[s]; ++c, ++kb, ++it) {
+              const int st = it % STAGES;
+              const uint32_t ph = (it / STAGES) & 1;
+              mbar_wait(&empty_bar[st], ph ^ 1);
+              uint8_t* sa = smem + st * STAGE_BYTES;
+              mbar_arrive_expect_tx(&full_bar[st], STAGE_BYTES);
+              tma_load_4d(sa, &p.amap[s], &full_bar[st], c * kChunk2, dx, y0 + dy, b0);
+              tma_load_2d(sa + kABytes2, &p.bmap, &full_bar[st], kb * kChunk2, n_tile * BN);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BN, false, false);
+      uint32_t it = 0, lt = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
+        const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+        mbar_wait(&tempty[acc], aph ^ 1);   // the epilogue has drained this accumulator stage
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + acc * BN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int st = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&full_bar[st], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
+          const uint64_t da = make_sdesc(sa, 16, 1024);
+          const uint64_t db = make_sdesc(sa + kABytes2, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kChunk2 / 16; ++k) umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          umma_commit(&empty_bar[st]);
+        }
+        umma_commit(&tfull[acc]);
+      }
+    }
+  } else {
+    const int q = warp & 3;                      // TMEM lane quarter this warp may read
+    const int r = q * 32 + lane;                 // row of the tile owned by this thread
+    const bool storer = (warp == 2 && lane == 0);
+    uint32_t lt = 0, pc = 0;                     // local tile counter, running panel counter
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
+      const int m_tile = t / n_tiles, n_tile = t - m_tile * n_tiles;
+      const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+      const long long row = static_cast<long long>(m_tile) * kTileM2 + r;
+      const bool row_ok = row < p.M;
+      float* bs = bias_s + acc * BN;
+      if (p.bias) {
+        for (int i = threadIdx.x - 64; i < BN; i += 128) {
+          const int n = n_tile * BN + i;
+          bs[i] = n < p.N ? __ldg(p.bias + n) : 0.f;
+        }
+      }
+      mbar_wait(&tfull[acc], aph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int pn = 0; pn < PANELS; ++pn) {
+        const int n0 = n_tile * BN + pn * 64;
+        if (n0 >= p.N) break;                    // uniform over the CTA
+        float v[64];
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + pn * 64;
+        tmem_ld32(taddr, v);
+        tmem_ld32(taddr + 32, v + 32);
+        tmem_ld_wait();
+        uint8_t* slot = staging + (pc & 1) * kPanelBytes;
+        if (storer) bulk_wait_read<1>();         // the store that last used this slot has finished reading it
+        epi_bar();                               // slot free; bias staged
+        if (p.bias) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) v[i] += bs[pn * 64 + i];
+        }
+        if (p.act == ACT_SILU) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) v[i] = silu_f(v[i]);
+        }
+        if (p.res && row_ok) {
+          const h16* rp = reinterpret_cast<const h16*>(p.res) + row * p.ldres + n0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float f[8];
+            unpack8(__ldg(reinterpret_cast<const uint4*>(rp + 8 * j)), f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[8 * j + i] += f[i];
+          }
+        }
+        uint8_t* rowp = slot + r * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(rowp + ((j ^ (r & 7)) << 4)) = pack8(v + 8 * j);
+        fence_async_smem();
+        epi_bar();
+        if (storer) {
+          tma_store_2d(&p.omap, slot, n0, m_tile * kTileM2);
+          bulk_commit();
+        }
+        ++pc;
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty[acc]);
+    }
+    if (storer) bulk_wait_read<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+template <int BN, int STAGES>
+static int launch_sgemm2_t(const Sgemm2Params& p, int num_sms, cudaStream_t stream) {
+  constexpr int smem = STAGES * (kABytes2 + BN * kChunk2 * 2) + 2 * kPanelBytes + 2 * BN * 4 + 1024 + 256;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(sgemm2_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  const int tiles = p.m_tiles * ((p.N + BN - 1) / BN);
+  const int grid = tiles < num_sms ? tiles : num_sms;
+  sgemm2_kernel<BN, STAGES><<<grid, 192, smem, stream>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// N tile: as wide as possible while the tile count still fills the chip
+int sgemm2_pick_bn(int m_tiles, int N, int num_sms) {
+  if (N % 64 != 0) return 0;
+  if (N >= 256 && N % 256 == 0 && m_tiles * (N / 256) >= num_sms) return 256;
+  if (N >= 128 && m_tiles * ((N + 127) / 128) >= num_sms) return 128;
+  return 64;
+}
+
+int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t stream) {
+  switch (bn) {
+    case 64: return launch_sgemm2_t<64, 6>(p, num_sms, stream);
+    case 128: return launch_sgemm2_t<128, 5>(p, num_sms, stream);
+    case 256: return launch_sgemm2_t<256, 3>(p, num_sms, stream);
+    default: return static_cast<int>(cudaErrorInvalidValue);
+  }
+}
+
+}  // namespace edb

@@ -98,4 +98,58 @@ int make_w_tmap(CUtensorMap* m, const void* base, long long K, long long rows, i
   return EDB_OK;
 }
 
+int make_out_tmap(CUtensorMap* m, const void* base, long long M, int N, int ld) {
+  auto enc = get_encode();
+  if (!enc) {
+    set_last_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+    return EDB_ERR_CUDA;
+  }
+  EDB_REQUIRE((N % 64) == 0 && (ld % 8) == 0, "output map: N must be a multiple of 64 and ld of 8");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "output base must be 16-byte aligned");
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(N), static_cast<cuuint64_t>(M)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint32_t box[2] = {64, 128};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, kMapType, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled(output) failed with CUresult " + std::to_string(static_cast<int>(r)));
+    return EDB_ERR_CUDA;
+  }
+  return EDB_OK;
+}
+
+int make_grad_tmap(CUtensorMap* m, float* base, int cols, int rows, bool three_d) {
+  auto enc = get_encode();
+  if (!enc) {
+    set_last_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+    return EDB_ERR_CUDA;
+  }
+  EDB_REQUIRE((cols % 4) == 0, "gradient map: row pitch must be a multiple of 16 bytes");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "gradient base must be 16-byte aligned");
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows), 9};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(cols) * 4, static_cast<cuuint64_t>(cols) * rows * 4};
+  cuuint32_t box[3] = {32, 128, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, three_d ? 3 : 2, base, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled(gradient) failed with CUresult " + std::to_string(static_cast<int>(r)));
+    return EDB_ERR_CUDA;
+  }
+  return EDB_OK;
+}
+
+int device_sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
 }  // namespace edb

@@ -45,5 +45,11 @@ bool make_geom(int H, int W, TileGeom* g);
 int make_act_tmap(CUtensorMap* m, const void* base, int C, int H, int W, int B, const TileGeom& g);
 // 2D (K, rows) h16 packed-weight map, box (64, bn), SWIZZLE_128B.
 int make_w_tmap(CUtensorMap* m, const void* base, long long K, long long rows, int bn);
+// 2D (N, M) 16-bit output map with row pitch ld elements, box (64, 128), SWIZZLE_128B (TMA store side of gemm2.cu).
+int make_out_tmap(CUtensorMap* m, const void* base, long long M, int N, int ld);
+int device_sm_count();
+// fp32 gradient destination of wgrad2.cu: 2D (cols, rows) with row pitch `cols` floats, or 3D (cols, rows, 9);
+// box (32, 128[, 1]), SWIZZLE_128B.  cols must be a multiple of 4 (16-byte row pitch).
+int make_grad_tmap(CUtensorMap* m, float* base, int cols, int rows, bool three_d);
 
 }  // namespace edb

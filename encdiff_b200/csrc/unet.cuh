@@ -121,6 +121,16 @@ struct UNet {
   // tensor-map caches
   std::map<std::tuple<const void*, int, int, int, int>, CUtensorMap> act_maps;
   std::map<std::tuple<const void*, long long, long long, int>, CUtensorMap> w_maps;
+  std::map<std::tuple<const void*, long long, int, int>, CUtensorMap> out_maps;
+  // conv3x3 weight-gradient staging (tap-major fp32, wgrad2.cu) + the finalize table that folds it into the grads
+  struct ConvStage { int param; long long Cp, Cq; float* ptr; };
+  std::vector<ConvStage> conv_stage;
+  std::vector<WgradFinalizeEntry> fin_host;
+  WgradFinalizeEntry* fin_dev = nullptr;
+  long long fin_total = 0;
+  bool fin_dirty = true;      // staging needs zeroing / table needs (re)building: after plan() or bind()
+  std::map<std::tuple<const void*, int, int, int>, CUtensorMap> grad_maps;
+  bool force_old_gemm = false;   // parity A/B switch: route every GEMM through the one-tile-per-CTA kernel
 
   h16* pbf() const { return reinterpret_cast<h16*>(packed + table_bytes); }
   float* pf32() const { return reinterpret_cast<float*>(packed + table_bytes + h16_bytes); }

@@ -48,7 +48,18 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
   u->aH = a.take<h16>(M0 * mc);
   u->stH = a.take<float>(static_cast<size_t>(B) * 64);
   u->yH = a.take<float>(M0 * c.out_channels);
+  u->conv_stage.clear();
   if (training) {
+    auto stage = [&](int param, long long Cp, long long Cq) {
+      u->conv_stage.push_back(UNet::ConvStage{param, Cp, Cq, a.take<float>(static_cast<size_t>(9 * Cp * Cq))});
+    };
+    for (const ResLayer& l : u->res) {
+      stage(l.conv1_w, l.cout, l.c0 + l.c1);
+      stage(l.conv2_w, l.cout, l.cout);
+    }
+    stage(u->hc_w, c.out_channels, mc);
+    u->fin_dev = reinterpret_cast<WgradFinalizeEntry*>(a.take<char>(u->conv_stage.size() * sizeof(WgradFinalizeEntry)));
+    u->fin_dirty = true;
     u->gs = a.take<float>(2);
     u->dfilm = a.take<h16>(static_cast<size_t>(B) * u->film_cols);
     u->dyH = a.take<h16>(M0 * 8);
@@ -142,6 +153,8 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
     u->plan_ws = ws;
     u->plan_training = training;
     u->act_maps.clear();
+    u->out_maps.clear();
+    u->grad_maps.clear();
   } else {
     u->planB = -1;
   }
@@ -211,6 +224,18 @@ struct Exec {
     }
     return &u->act_maps.emplace(key, m).first->second;
   }
+  const CUtensorMap* out_map(const void* p, long long M, int N, int ld) {
+    auto key = std::make_tuple(p, M, N, ld);
+    auto it = u->out_maps.find(key);
+    if (it != u->out_maps.end()) return &it->second;
+    CUtensorMap m;
+    int rc = make_out_tmap(&m, p, M, N, ld);
+    if (rc) {
+      if (!err) err = rc;
+      return nullptr;
+    }
+    return &u->out_maps.emplace(key, m).first->second;
+  }
   const CUtensorMap* w_map(const h16* p, long long K, long long rows, int bn) {
     auto key = std::make_tuple(static_cast<const void*>(p), K, rows, bn);
     auto it = u->w_maps.find(key);
@@ -250,6 +275,36 @@ struct Exec {
       return;
     }
     p.nsrc = i;
+    const int sms = device_sm_count();
+    const int m_tiles = (B * H * W + 127) / 128;
+    const int bn2 = (!fp32 && ld == N && !u->force_old_gemm) ? sgemm2_pick_bn(m_tiles, N, sms) : 0;
+    if (bn2) {
+      Sgemm2Params q;
+      memset(&q, 0, sizeof(q));
+      for (int k = 0; k < 3; ++k) {
+        q.amap[k] = p.amap[k];
+        q.src_chunks[k] = p.src_chunks[k];
+        q.src_taps[k] = p.src_taps[k];
+      }
+      q.nsrc = p.nsrc;
+      q.g = p.g;
+      const CUtensorMap* wm2 = w_map(u->pbf() + pk.off + row0 * pk.K, pk.K, pk.rows - row0, bn2);
+      const CUtensorMap* om = out_map(out, static_cast<long long>(B) * H * W, N, ld);
+      if (!wm2 || !om) return;
+      q.bmap = *wm2;
+      q.omap = *om;
+      q.tap_sign = tap_sign;
+      q.M = B * H * W;
+      q.N = N;
+      q.m_tiles = m_tiles;
+      q.bias = bias;
+      q.res = res;
+      q.ldres = ldres;
+      q.act = act;
+      next_flops = 2.0 * q.M * static_cast<double>(N) * static_cast<double>(K);
+      fail(launch_sgemm2(q, bn2, sms, s), "sgemm");
+      return;
+    }
     const int bn = sgemm_pick_bn(N);
     const CUtensorMap* wm = w_map(u->pbf() + pk.off + row0 * pk.K, pk.K, pk.rows - row0, bn);
     if (!wm) return;
@@ -269,10 +324,73 @@ struct Exec {
     fail(launch_sgemm(p, bn, s), "sgemm");
   }
 
-  // grad[p, q(+q_off), tap] += sum_pix dy[pix, p_off + p] * x[pix, q]
+  void colsum(const h16* x, long long M, int ld, int col0, int N, float* d0, float* d1 = nullptr) {
+    if (err || !d0) return;
+    fail(launch_colsum(x, M, ld, col0, N, d0, d1, u->gs, s), "colsum");
+  }
+
+  const CUtensorMap* grad_map(float* base, int cols, int rows, bool three_d) {
+    auto key = std::make_tuple(static_cast<const void*>(base), cols, rows, three_d ? 1 : 0);
+    auto it = u->grad_maps.find(key);
+    if (it != u->grad_maps.end()) return &it->second;
+    CUtensorMap m;
+    int rc = make_grad_tmap(&m, base, cols, rows, three_d);
+    if (rc) {
+      if (!err) err = rc;
+      return nullptr;
+    }
+    return &u->grad_maps.emplace(key, m).first->second;
+  }
+
+  // grad[p, q(+q_off), tap] += sum_pix dy[pix, p_off + p] * x[pix, q];  bias0/bias1[p] += sum_pix dy[pix, p_off + p]
   void wgrad(const h16* dy, int Cdy, int p_off, int Cp, const h16* x, int Cx, int Cq, int H, int W, int taps,
-             float* out, long long stride_p, long long stride_q, long long stride_tap, int q_off) {
+             float* out, long long stride_p, long long stride_q, long long stride_tap, int q_off,
+             float* bias0 = nullptr, float* bias1 = nullptr) {
     if (err || !out) return;
+    // persistent kernel with TMA reduce-add epilogue and fused bias gradient (wgrad2.cu)
+    float* dst = nullptr;
+    bool three_d = false;
+    int cols = 0;
+    if (!u->force_old_gemm) {
+      if (taps == 1 && stride_q == 1 && (stride_p % 4) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+        dst = out;
+        cols = static_cast<int>(stride_p);
+      } else if (taps == 9 && stride_q == 9 && stride_tap == 1 && stride_p == 9LL * Cq && q_off == 0 && (Cq % 4) == 0) {
+        for (const UNet::ConvStage& cs : u->conv_stage)
+          if (u->gptr[cs.param] == out && cs.Cp == Cp && cs.Cq == Cq) dst = cs.ptr;
+        three_d = true;
+        cols = Cq;
+      }
+    }
+    if (dst) {
+      Wgrad2Params q;
+      memset(&q, 0, sizeof(q));
+      if (!make_geom(H, W, &q.g)) {
+        invalid("wgrad geometry: H*W must be a power of two, W <= 128");
+        return;
+      }
+      const CUtensorMap* pm = act_map(dy, Cdy, H, W, q.g);
+      const CUtensorMap* qm = act_map(x, Cx, H, W, q.g);
+      const CUtensorMap* om = grad_map(dst, cols, Cp, three_d);
+      if (!pm || !qm || !om) return;
+      q.pmap = *pm;
+      q.qmap = *qm;
+      q.omap = *om;
+      q.taps = taps;
+      q.m_tiles = (B * H * W + 127) / 128;
+      q.Cp = Cp;
+      q.Cq = Cq;
+      q.p_off = p_off;
+      q.q_off = q_off;
+      q.out3d = three_d ? 1 : 0;
+      q.bias0 = bias0;
+      q.bias1 = bias1;
+      q.gscale = u->gs;
+      next_flops = 2.0 * B * H * W * static_cast<double>(Cp) * Cq * taps;
+      fail(launch_wgrad2(q, device_sm_count(), s), "wgrad");
+      return;
+    }
+    if (bias0) colsum(dy, static_cast<long long>(B) * H * W, Cdy, p_off, Cp, bias0, bias1);
     WgradParams p;
     memset(&p, 0, sizeof(p));
     if (!make_geom(H, W, &p.g)) {
@@ -307,10 +425,6 @@ struct Exec {
     fail(launch_wgrad(p, bn, static_cast<int>(splits), s), "wgrad");
   }
 
-  void colsum(const h16* x, long long M, int ld, int col0, int N, float* d0, float* d1 = nullptr) {
-    if (err || !d0) return;
-    fail(launch_colsum(x, M, ld, col0, N, d0, d1, u->gs, s), "colsum");
-  }
   const float* P(int idx) const { return u->pptr[idx]; }
   float* G(int idx) const { return u->gptr.empty() ? nullptr : u->gptr[idx]; }
 };

@@ -1,0 +1,292 @@
+// Persistent tcgen05 weight-gradient kernel (sm_100a).  See gemm.cuh (Wgrad2Params) for the math.
+//
+//   work item = (split, p_tile, tap, q_tile): D[128 x 64(+16)] = sum over the split's 128-pixel tiles of
+//               dY^T[128 ch x 128 pix] * [ X(shifted by tap)[128 pix x 64 ch] | 1 ]      (both operands MN-major)
+//   The extra all-ones block of the B operand makes column 64 of D the per-channel sum of dY: the bias gradient costs
+//   no extra pass over dY (it replaces a separate column-sum kernel per layer).
+//   warp 0 TMA producer, warp 1 MMA issuer (two TMEM accumulator stages), warps 2..5 epilogue:
+//   TMEM -> registers -> * 1/gscale -> 128B-swizzled fp32 panel in shared memory -> cp.reduce.async.bulk.tensor (.add)
+//   into the fp32 gradient: one bulk L2 reduction per [128 x 32] panel instead of 4096 scalar atomics.
+//   Conv3x3 gradients are reduced into a tap-major staging tensor [9][Cp][Cq] (the reference layout [Cp][Cq][3][3] has
+//   no 16-byte contiguous run per tap, which TMA needs); wgrad_finalize_kernel transposes it into the reference layout
+//   once per backward.
+#include "common.cuh"
+#include "gemm.cuh"
+
+namespace edb {
+
+static constexpr int kPix = 128;                       // pixels per reduction step (UMMA K = 8 x 16)
+static constexpr int kBox = kPix * 64 * 2;             // 16 KB: one [128 pix x 64 ch] 16-bit box
+static constexpr int kWBN = 64;                        // X channels per work item
+static constexpr int kWN = kWBN + 16;                  // MMA N: 64 weight columns + the ones block (16 columns)
+static constexpr int kWStages = 3;
+static constexpr int kWStageBytes = 3 * kBox;          // dY: 2 boxes (M = 128), X: 1 box
+static constexpr int kFPanel = 128 * 128;              // 16 KB: [128 rows x 32 fp32] staging panel
+
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void w_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void w_bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void w_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void w_epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+__device__ __forceinline__ void w_tile_origin(const TileGeom& g, int tile, int& b0, int& y0) {
+  if (g.tiles_per_img > 1) {
+    b0 = tile / g.tiles_per_img;
+    y0 = (tile - b0 * g.tiles_per_img) * g.box_h;
+  } else {
+    b0 = tile * g.box_b;
+    y0 = 0;
+  }
+}
+
+struct WItem {
+  int split, p_tile, tap, q_tile;
+};
+__device__ __forceinline__ WItem w_decode(const Wgrad2Params& p, int item) {
+  WItem w;
+  w.q_tile = item % p.q_tiles;
+  item /= p.q_tiles;
+  w.tap = item % p.taps;
+  item /= p.taps;
+  w.p_tile = item % p.p_tiles;
+  w.split = item / p.p_tiles;
+  return w;
+}
+
+__global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ Wgrad2Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* ones = smem + kWStages * kWStageBytes;      // [128 pix x 64 ch] of 1.0: the shared extra N block
+  uint8_t* staging = ones + kBox;                      // 2 fp32 panels
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + 2 * kFPanel);
+  uint64_t* empty_bar = full_bar + kWStages;
+  uint64_t* tfull = empty_bar + kWStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total = p.q_tiles * p.taps * p.p_tiles * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.pmap);
+    tma_prefetch_desc(&p.qmap);
+    tma_prefetch_desc(&p.omap);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kWStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull[s], 1);
+      mbar_init(&tempty[s], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<256>(tmem_slot);
+  {
+    const h162 one2 = f22h2(1.f, 1.f);
+    uint4 o4;
+    o4.x = o4.y = o4.z = o4.w = *reinterpret_cast<const uint32_t*>(&one2);
+    for (int i = threadIdx.x; i < kBox / 16; i += blockDim.x) reinterpret_cast<uint4*>(ones)[i] = o4;
+    w_fence_async_smem();   // generic-proxy writes -> visible to the tensor core (async proxy)
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int item = blockIdx.x; item < total; item += gridDim.x) {
+        const WItem w = w_decode(p, item);
+        int dx = 0, dy = 0;
+        if (p.taps == 9) {
+          dy = w.tap / 3 - 1;
+          dx = w.tap % 3 - 1;
+        }
+        const int t_begin = w.split * p.tiles_per_split;
+        const int t_end = min(p.m_tiles, t_begin + p.tiles_per_split);
+        for (int t = t_begin; t < t_end; ++t, ++it) {
+          const int st = it % kWStages;
+          const uint32_t ph = (it / kWStages) & 1;
+          int b0, y0;
+          w_tile_origin(p.g, t, b0, y0);
+          mbar_wait(&empty_bar[st], ph ^ 1);
+          uint8_t* sp = smem + st * kWStageBytes;
+          mbar_arrive_expect_tx(&full_bar[st], kWStageBytes);
+          tma_load_4d(sp, &p.pmap, &full_bar[st], p.p_off + w.p_tile * 128, 0, y0, b0);
+          tma_load_4d(sp + kBox, &p.pmap, &full_bar[st], p.p_off + w.p_tile * 128 + 64, 0, y0, b0);
+          tma_load_4d(sp + 2 * kBox, &p.qmap, &full_bar[st], w.q_tile * kWBN, dx, y0 + dy, b0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kWN, true, true);
+      const uint32_t ones_addr = smem_u32(ones);
+      uint32_t it = 0, lt = 0;
+      for (int item = blockIdx.x; item < total; item += gridDim.x, ++lt) {
+        const WItem w = w_decode(p, item);
+        const int t_begin = w.split * p.tiles_per_split;
+        const int nsteps = min(p.m_tiles, t_begin + p.tiles_per_split) - t_begin;
+        const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+        mbar_wait(&tempty[acc], aph ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + acc * 128;
+        for (int i = 0; i < nsteps; ++i, ++it) {
+          const int st = it % kWStages;
+          const uint32_t ph = (it / kWStages) & 1;
+          mbar_wait(&full_bar[st], ph);
+          tc_fence_after();
+          const uint32_t sp = smem_u32(smem + st * kWStageBytes);
+          const uint32_t sq = sp + 2 * kBox;
+#pragma unroll
+          for (int k = 0; k < kPix / 16; ++k) {
+            // 16 pixels (the reduction) = 16 rows of 128 B = 2048 B per MMA step.  A: second 64-channel block kBox
+            // away.  B: second N block = the shared ones box (same k offset inside it).
+            const uint64_t da = make_sdesc(sp + k * 2048, kBox, 1024);
+            const uint64_t db = make_sdesc(sq + k * 2048, ones_addr - sq, 1024);
+            umma_f16(tacc, da, db, idesc, (i | k) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[st]);
+        }
+        umma_commit(&tfull[acc]);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const bool storer = (warp == 2 && lane == 0);
+    const float ginv = p.gscale ? __ldg(p.gscale + 1) : 1.f;
+    uint32_t lt = 0, pc = 0;
+    for (int item = blockIdx.x; item < total; item += gridDim.x, ++lt) {
+      const WItem w = w_decode(p, item);
+      const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+      const int pch = w.p_tile * 128 + r;     // dY channel of this thread's row
+      mbar_wait(&tfull[acc], aph);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 128;
+#pragma unroll 1
+      for (int pn = 0; pn < kWBN / 32; ++pn) {
+        const int qc0 = w.q_tile * kWBN + pn * 32;
+        if (qc0 >= p.Cq) break;
+        float v[32];
+        tmem_ld32(trow + pn * 32, v);
+        tmem_ld_wait();
+        uint8_t* slot = staging + (pc & 1) * kFPanel;
+        if (storer) w_bulk_wait_read<1>();
+        w_epi_bar();
+        uint8_t* rowp = slot + r * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(rowp + ((j ^ (r & 7)) << 4)) =
+              make_float4(v[4 * j] * ginv, v[4 * j + 1] * ginv, v[4 * j + 2] * ginv, v[4 * j + 3] * ginv);
+        w_fence_async_smem();
+        w_epi_bar();
+        if (storer) {
+          if (p.out3d) tma_reduce_add_3d(&p.omap, slot, qc0, w.p_tile * 128, w.tap);
+          else tma_reduce_add_2d(&p.omap, slot, p.q_off + qc0, w.p_tile * 128);
+          w_bulk_commit();
+        }
+        ++pc;
+      }
+      if (p.bias0 && w.q_tile == 0 && w.tap == 0) {   // column 64 = sum over pixels of dY (ones block)
+        float bsum[16];
+        uint32_t* u = reinterpret_cast<uint32_t*>(bsum);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+              "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+            : "r"(trow + kWBN)
+            : "memory");
+        tmem_ld_wait();
+        if (pch < p.Cp) {
+          atomicAdd(p.bias0 + pch, bsum[0] * ginv);
+          if (p.bias1) atomicAdd(p.bias1 + pch, bsum[0] * ginv);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty[acc]);
+    }
+    if (storer) w_bulk_wait_read<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<256>(tmem_base);
+}
+
+int launch_wgrad2(const Wgrad2Params& p0, int num_sms, cudaStream_t stream) {
+  constexpr int smem = kWStages * kWStageBytes + kBox + 2 * kFPanel + 1024 + 256;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  Wgrad2Params p = p0;
+  p.p_tiles = (p.Cp + 127) / 128;
+  p.q_tiles = (p.Cq + kWBN - 1) / kWBN;
+  const int base = p.p_tiles * p.q_tiles * p.taps;
+  // enough items to fill the chip about twice, at least 4 pixel tiles of reduction per item
+  int splits = (2 * num_sms + base - 1) / base;
+  const int max_splits = (p.m_tiles + 3) / 4;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  p.tiles_per_split = (p.m_tiles + splits - 1) / splits;
+  p.splits = (p.m_tiles + p.tiles_per_split - 1) / p.tiles_per_split;
+  const int total = base * p.splits;
+  const int grid = total < num_sms ? total : num_sms;
+  wgrad2_kernel<<<grid, 192, smem, stream>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// grad[p][q][tap] += stage[tap][p][q]; stage = 0       (one launch per backward for every conv3x3 weight)
+__global__ void wgrad_finalize_kernel(const WgradFinalizeEntry* __restrict__ tab, int n_entries, long long total) {
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    int lo = 0, hi = n_entries - 1;   // last entry with prefix <= idx
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (tab[mid].prefix <= idx) lo = mid; else hi = mid - 1;
+    }
+    const WgradFinalizeEntry& en = tab[lo];
+    const long long e = idx - en.prefix;          // = p * Cq + q
+    float* st = en.stage + e;
+    float* g = en.grad + e * 9;
+    float v[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      v[t] = st[t * en.pq];
+      st[t * en.pq] = 0.f;
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) g[t] += v[t];
+  }
+}
+int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total, cudaStream_t s) {
+  if (n_entries <= 0) return 0;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  wgrad_finalize_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(tab_dev, n_entries, total);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace edb
