@@ -2,6 +2,8 @@
 // query per thread, online softmax in the exp2 domain, scores never touch HBM.  Cross-attention: the T (~20)
 // concept tokens' K/V are projected inside the kernel and kept in shared memory; softmax over T in registers.
 // Reference: CrossAttention.forward, ldm/modules/attention.py:170-193.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -270,6 +272,11 @@ static int self_attn_bwd_t(const h16* qkv, const h16* out, const h16* dout, cons
 
 int launch_self_attn_fwd(const h16* qkv, h16* out, float* lse, int B, int N, int heads, int D, cudaStream_t s) {
   if (N < 4 || (N & 3)) return static_cast<int>(cudaErrorInvalidValue);
+  static const bool cuda_core_only = getenv("ENCDIFF_ATTN_CUDA_CORE") != nullptr;
+  if (!cuda_core_only) {
+    const int rc = launch_self_attn_fwd_mma(qkv, out, lse, B, N, heads, D, s);
+    if (rc != -1) return rc;
+  }
   switch (D) {
     case 8: return self_attn_fwd_t<8>(qkv, out, lse, B, N, heads, s);
     case 16: return self_attn_fwd_t<16>(qkv, out, lse, B, N, heads, s);
@@ -282,6 +289,11 @@ int launch_self_attn_fwd(const h16* qkv, h16* out, float* lse, int B, int N, int
 int launch_self_attn_bwd(const h16* qkv, const h16* out, const h16* dout, const float* lse, h16* dqkv, int B, int N,
                          int heads, int D, cudaStream_t s) {
   if (N < 4 || (N & 3)) return static_cast<int>(cudaErrorInvalidValue);
+  static const bool cuda_core_only = getenv("ENCDIFF_ATTN_CUDA_CORE") != nullptr;
+  if (!cuda_core_only) {
+    const int rc = launch_self_attn_bwd_mma(qkv, out, dout, lse, dqkv, B, N, heads, D, s);
+    if (rc != -1) return rc;
+  }
   switch (D) {
     case 8: return self_attn_bwd_t<8>(qkv, out, dout, lse, dqkv, B, N, heads, s);
     case 16: return self_attn_bwd_t<16>(qkv, out, dout, lse, dqkv, B, N, heads, s);

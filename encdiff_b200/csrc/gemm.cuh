@@ -95,11 +95,11 @@ struct Wgrad2Params {
 struct WgradFinalizeEntry {
   float* stage;         // [9][Cp][Cq]
   float* grad;          // [Cp][Cq][9] reference layout
-  long long prefix;     // first global (p, q) index of this entry
+  long long prefix;     // first index of this entry in the block-padded (multiples of 256) global (p, q) space
   long long pq;         // Cp * Cq
 };
 int launch_wgrad2(const Wgrad2Params& p, int num_sms, cudaStream_t stream);
-int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total, cudaStream_t s);
+int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total_padded, cudaStream_t s);
 
 // BN in {32(padded small N), 64, 128, 256}; returns cudaError_t as int
 int launch_sgemm(const SgemmParams& p, int bn, cudaStream_t stream);

@@ -47,6 +47,10 @@ int launch_ln_bwd(const h16* x, const float* stats, const float* gamma, const h1
 // Self-attention over N tokens per sample (CrossAttention.forward with context=None, attention.py:170-193).
 // qkv [B*N, 3C] (q | k | v, head h at columns h*D), out [B*N, C], lse [B*heads*N] (log2 domain).
 int launch_self_attn_fwd(const h16* qkv, h16* out, float* lse, int B, int N, int heads, int D, cudaStream_t s);
+// tensor-core (mma.sync) variants, attn_mma.cu; return -1 when the shape is not handled (N % 16, N > 256, D not 8/16/32)
+int launch_self_attn_fwd_mma(const h16* qkv, h16* out, float* lse, int B, int N, int heads, int D, cudaStream_t s);
+int launch_self_attn_bwd_mma(const h16* qkv, const h16* out, const h16* dout, const float* lse, h16* dqkv, int B, int N,
+                             int heads, int D, cudaStream_t s);
 int launch_self_attn_bwd(const h16* qkv, const h16* out, const h16* dout, const float* lse, h16* dqkv, int B, int N,
                          int heads, int D, cudaStream_t s);
 

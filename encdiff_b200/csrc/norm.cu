@@ -35,6 +35,51 @@ __device__ __forceinline__ GnThread gn_thread(const GnParams& p, int b) {
   return t;
 }
 
+// Per-channel block reduction of two 8-channel register vectors (one per thread) without shared-memory atomics:
+// lanes of a warp that hold the same chunk are combined by shuffles (when nv divides 32), each remaining holder
+// writes one row of `part` ([rows][2][C]), and the rows are summed per channel into out0 / out1.
+// Must be called by every thread of the block (contains __syncthreads).
+__device__ __forceinline__ void gn_channel_reduce(const GnThread& t, bool active, float* s, float* q, float* part,
+                                                  float* out0, float* out1) {
+  const int C = t.C;
+  int rows;
+  if ((32 % t.nv) == 0) {   // blockDim.x == 512: full warps, lane % nv == chunk
+    for (int o = t.nv; o < 32; o <<= 1) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
+        q[k] += __shfl_xor_sync(0xffffffffu, q[k], o);
+      }
+    }
+    rows = blockDim.x >> 5;
+    if ((threadIdx.x & 31) < t.nv) {
+      float* pr = part + (threadIdx.x >> 5) * 2 * C;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        pr[t.c0 + k] = s[k];
+        pr[C + t.c0 + k] = q[k];
+      }
+    }
+  } else {
+    rows = t.rp;
+    if (active) {
+      float* pr = part + t.prow * 2 * C;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        pr[t.c0 + k] = s[k];
+        pr[C + t.c0 + k] = q[k];
+      }
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+    float a = 0.f;
+    for (int r = 0; r < rows; ++r) a += part[r * 2 * C + c];
+    if (c < C) out0[c] = a; else out1[c - C] = a;
+  }
+  __syncthreads();
+}
+
 __device__ __forceinline__ void load8(const h16* p, float* f) { unpack8(*reinterpret_cast<const uint4*>(p), f); }
 __device__ __forceinline__ void store8(h16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
 
@@ -48,8 +93,7 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
   float* cA = sm + 2 * C;
   float* cB = sm + 3 * C;
   float* gstat = sm + 4 * C;  // [64]
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
+  float* part = gstat + 64;   // [rows][2][C] partial sums, rows <= 32
   const bool active = t.prow < t.rp;  // threads beyond nv*rp idle (blockDim is a multiple of nv, so all active)
   {
     float s[8], q[8];
@@ -65,14 +109,9 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
           q[k] += f[k] * f[k];
         }
       }
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        atomicAdd(&chsum[t.c0 + k], s[k]);
-        atomicAdd(&chsq[t.c0 + k], q[k]);
-      }
     }
+    gn_channel_reduce(t, active, s, q, part, chsum, chsq);
   }
-  __syncthreads();
   const int cpg = C / 32;
   if (threadIdx.x < 32) {
     const int g = threadIdx.x;
@@ -211,6 +250,7 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
   float* S2 = sm + 5 * C;   // sum dyp * xhat   -> later k2
   float* K3 = sm + 6 * C;
   float* gAB = sm + 7 * C;  // [64] group sums
+  float* part = gAB + 64;   // [rows][2][C] partial sums, rows <= 32
   const int cpg = C / 32;
   const int W = p.W;
   int HWo = t.HW;
@@ -231,8 +271,6 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     cB[c] = be;
     cM[c] = mean;
     cR[c] = rstd;
-    S1[c] = 0.f;
-    S2[c] = 0.f;
   }
   __syncthreads();
   const h16* dact = p.dact + static_cast<long long>(b) * HWo * C + t.c0;
@@ -260,13 +298,8 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
         s2[k] += dyp * (f[k] - mu[k]) * rs[k];
       }
     }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      atomicAdd(&S1[t.c0 + k], s1[k]);
-      atomicAdd(&S2[t.c0 + k], s2[k]);
-    }
+    gn_channel_reduce(t, t.prow < t.rp, s1, s2, part, S1, S2);
   }
-  __syncthreads();
   // per-channel parameter gradients; turn S1/S2 into gsc-weighted values for the group sums
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const float s1 = S1[c], s2 = S2[c];
@@ -354,10 +387,18 @@ static int gn_threads(int C) {
   return nv * rp;
 }
 
+static size_t gn_part_floats(int C) {
+  const int nv = C / 8;
+  int rp = 512 / nv;
+  if (rp < 1) rp = 1;
+  const int rows = (32 % nv) == 0 ? 16 : rp;
+  return static_cast<size_t>(rows) * 2 * C;
+}
+
 int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s) {
   const int C = p.C0 + p.C1;
   if (C % 32 != 0 || (p.C0 % 8) != 0 || C > 8192) return static_cast<int>(cudaErrorInvalidValue);
-  const size_t smem = (4 * C + 64) * sizeof(float);
+  const size_t smem = (4 * C + 64 + gn_part_floats(C)) * sizeof(float);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(gn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -371,7 +412,7 @@ int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s) {
 int launch_gn_bwd(const GnParams& p, int B, cudaStream_t s) {
   const int C = p.C0 + p.C1;
   if (C % 32 != 0 || (p.C0 % 8) != 0 || C > 4096) return static_cast<int>(cudaErrorInvalidValue);
-  const size_t smem = (7 * C + 64) * sizeof(float);
+  const size_t smem = (7 * C + 64 + gn_part_floats(C)) * sizeof(float);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(gn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));

@@ -259,33 +259,40 @@ int launch_wgrad2(const Wgrad2Params& p0, int num_sms, cudaStream_t stream) {
 }
 
 // grad[p][q][tap] += stage[tap][p][q]; stage = 0       (one launch per backward for every conv3x3 weight)
-__global__ void wgrad_finalize_kernel(const WgradFinalizeEntry* __restrict__ tab, int n_entries, long long total) {
-  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-    int lo = 0, hi = n_entries - 1;   // last entry with prefix <= idx
+// The (p, q) index space of every entry is padded to a multiple of 256, so a block works on 256 consecutive (p, q) of
+// ONE entry: 9 coalesced reads per thread, transpose through shared memory, 2304 contiguous floats written.
+__global__ void __launch_bounds__(256) wgrad_finalize_kernel(const WgradFinalizeEntry* __restrict__ tab, int n_entries) {
+  __shared__ float tile[256 * 9];
+  __shared__ int s_entry;
+  const long long base = static_cast<long long>(blockIdx.x) * 256;
+  if (threadIdx.x == 0) {
+    int lo = 0, hi = n_entries - 1;   // last entry with (padded) prefix <= base
     while (lo < hi) {
       const int mid = (lo + hi + 1) >> 1;
-      if (tab[mid].prefix <= idx) lo = mid; else hi = mid - 1;
+      if (tab[mid].prefix <= base) lo = mid; else hi = mid - 1;
     }
-    const WgradFinalizeEntry& en = tab[lo];
-    const long long e = idx - en.prefix;          // = p * Cq + q
+    s_entry = lo;
+  }
+  __syncthreads();
+  const WgradFinalizeEntry en = tab[s_entry];
+  const long long e0 = base - en.prefix;            // first (p, q) of this block
+  const long long e = e0 + threadIdx.x;
+  if (e < en.pq) {
     float* st = en.stage + e;
-    float* g = en.grad + e * 9;
-    float v[9];
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
-      v[t] = st[t * en.pq];
+      tile[threadIdx.x * 9 + t] = st[t * en.pq];
       st[t * en.pq] = 0.f;
     }
-#pragma unroll
-    for (int t = 0; t < 9; ++t) g[t] += v[t];
   }
+  __syncthreads();
+  const long long n = min(static_cast<long long>(256), en.pq - e0) * 9;   // floats of this block
+  float* g = en.grad + e0 * 9;
+  for (int i = threadIdx.x; i < n; i += 256) g[i] += tile[i];
 }
-int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total, cudaStream_t s) {
+int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total_padded, cudaStream_t s) {
   if (n_entries <= 0) return 0;
-  long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  wgrad_finalize_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(tab_dev, n_entries, total);
+  wgrad_finalize_kernel<<<static_cast<unsigned>(total_padded / 256), 256, 0, s>>>(tab_dev, n_entries);
   return static_cast<int>(cudaGetLastError());
 }
 
