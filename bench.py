@@ -146,7 +146,14 @@ def run_reference(args):
 # ---------------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------------
-FAMILY = {"sgemm": "sgemm_kernel", "wgrad": "wgrad_kernel"}
+def measured_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/r01_sgemm2_dram.json, written
+    by tools/ncu_dram_summary.py from `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`); None if absent."""
+    p = os.path.join(ROOT, "profiles", "r01_sgemm2_dram.json")
+    if not os.path.exists(p):
+        return None, None
+    d = json.load(open(p))
+    return d.get("dram_bytes_per_launch"), d.get("algorithmic_bytes_per_launch")
 
 
 def build_model(dev):
@@ -192,6 +199,8 @@ def run_b200(args):
         torch.distributed.init_process_group("nccl", device_id=dev)
     from encdiff_b200 import DDIMSampler
     from encdiff_b200.train import DenoiserTrainer
+    from encdiff_b200 import _lib as edb_lib
+    act = "bf16" if edb_lib.act_dtype() == torch.bfloat16 else "fp16"      # 16-bit operands, fp32 accumulate / masters
     B, K, W = args.batch, args.steps, args.warmup
     model = build_model(dev)
     trainer = DenoiserTrainer(model, lr=1e-4, use_cuda_graph=not args.no_graph)
@@ -240,14 +249,17 @@ def run_b200(args):
     model.profile(False)
     launches_per_step = sum(v[0] for v in prof.values()) // P + 3      # + l1_loss, adamw, pack
     fam = {}
-    for name, (n, tms, fl) in prof.items():
-        fam[name] = {"launches_per_step": n // P, "ms_per_step": tms / P, "gflop_per_step": fl / P / 1e9}
+    for name, (n, tms, fl, by) in prof.items():
+        fam[name] = {"launches_per_step": n // P, "ms_per_step": tms / P, "gflop_per_step": fl / P / 1e9,
+                     "gbyte_per_step": by / P / 1e9}
     tot_ms = sum(v["ms_per_step"] for v in fam.values())
     sg = fam.get("sgemm", {"ms_per_step": 0.0, "gflop_per_step": 0.0, "launches_per_step": 0})
     achieved = sg["gflop_per_step"] / max(sg["ms_per_step"], 1e-9)        # GFLOP/ms == TFLOP/s
-    roof = {"bound": "tensor", "kernel": "sgemm_kernel (tcgen05 implicit GEMM: conv3x3/1x1/linear fwd + dgrad)",
+    traffic, _ = measured_traffic()
+    alg_bytes = sg.get("gbyte_per_step", 0.0) * 1e9 / max(sg["launches_per_step"], 1)
+    roof = {"bound": "tensor", "kernel": "sgemm2_kernel (persistent tcgen05 implicit GEMM: conv3x3/1x1/linear fwd + dgrad)",
             "achieved": achieved, "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
-            "traffic": None, "peak_source": pk["source"] + " (sustained cuBLAS bf16)",
+            "traffic": traffic, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": pk["source"] + " (sustained cuBLAS bf16)",
             "launches_per_step": sg["launches_per_step"], "share_of_step": sg["ms_per_step"] / max(tot_ms, 1e-9),
             "families": {k: {"ms": round(v["ms_per_step"], 4), "n": v["launches_per_step"],
                              "share": round(v["ms_per_step"] / max(tot_ms, 1e-9), 4)}
@@ -265,13 +277,14 @@ def run_b200(args):
     img_s = world * B * K / (ms / 1e3)
     e2e_img_s = world * B * K / (ms_e2e / 1e3)
     line = {"metric": METRIC, "value": img_s, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": act,
             "data": "synthetic",
             "config": {"workload": "shapes3d_train_step_b256_per_gpu" if B == 256 else f"shapes3d_train_step_b{B}_per_gpu",
                        "global_batch": world * B, "parallelism": f"dp{world}", "cuda_graph": not args.no_graph,
                        "l2": "working set per step (activation workspace %.2f GB) exceeds the 126 MB L2; 4 rotating "
                              "input batches" % (model._lib.encdiff_unet_workspace_bytes(model._h, B, 1) / 1e9),
-                       "step": "q_sample+UNet fwd+L1+UNet bwd+grad all-reduce+AdamW/EMA+bf16 weight re-pack"},
+                       "step": "q_sample+UNet fwd+L1+UNet bwd+grad all-reduce+AdamW/EMA+16-bit weight re-pack",
+                       "precision": act + " tensor-core operands and activations, fp32 accumulation, fp32 master weights/optimizer"},
             "e2e": {"value": e2e_img_s, "unit": UNIT, "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches_per_step * K),
@@ -282,41 +295,19 @@ def run_b200(args):
     if ddim is not None:
         line["ddim50"] = ddim
     if world == 1 and not args.no_cpu:
-        sec, cores = cpu_train_step_time(args.cpu_batch, 3, 1)
+        sec, cores = cpu_train_step_time(args.cpu_batch, 5, 1)
         line["cpu_baseline"] = {"value": args.cpu_batch / sec, "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": f"3 timed steps of batch {args.cpu_batch} (of {B}), median, fp32 torch oracle"}
+                                "sample": f"5 timed steps of batch {args.cpu_batch} (of {B}), median, fp32 torch oracle "
+                                          "(p_losses fwd+bwd+AdamW), all host threads"}
     print(json.dumps(line), flush=True)
     if dist_on:
         torch.distributed.destroy_process_group()
 
 
-class _SamplerHost:
-    """The attributes DDIMSampler reads from LatentDiffusion, around a bare UNet."""
-
-    def __init__(self, unet, dev):
-        import numpy as np
-        from encdiff_b200.train import make_beta_schedule
-        betas = make_beta_schedule()
-        acp = np.cumprod(1.0 - betas)
-        self.num_timesteps = 1000
-        self.betas = torch.tensor(betas, dtype=torch.float32, device=dev)
-        self.alphas_cumprod = torch.tensor(acp, dtype=torch.float32, device=dev)
-        self.alphas_cumprod_prev = torch.tensor(np.append(1.0, acp[:-1]), dtype=torch.float32, device=dev)
-        self.device = dev
-        self.parameterization = "eps"
-
-        class W:
-            conditioning_key = "crossattn"
-        self.model = W()
-        self.model.diffusion_model = unet
-
-    def apply_model(self, x, t, c):
-        return self.model.diffusion_model(x, t, context=[c])
-
-
 def ddim50(model, dev, B, dist_on, world):
     from encdiff_b200 import DDIMSampler
-    host = _SamplerHost(model, dev)
+    from encdiff_b200.diffusion import DenoiserHost
+    host = DenoiserHost(model).to(dev)
     sampler = DDIMSampler(host)
     g = torch.Generator().manual_seed(5)
     cond = torch.randn(B, 320, generator=g).to(dev)
@@ -338,7 +329,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (BASELINE.json configs[1]: 256)")
-    ap.add_argument("--cpu-batch", type=int, default=8, help="bounded CPU sample of the same workload")
+    ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample of the same workload")
     ap.add_argument("--ddim-batch", type=int, default=128, help="per-GPU DDIM-50 batch (configs[2]: 1024 over 8 GPUs)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-ddim", action="store_true")

@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "gemm.cuh"
 #include "host.cuh"
+#include "kernels.cuh"
 
 using namespace edb;
 
@@ -111,3 +112,78 @@ extern "C" int encdiff_op_wgrad(const void* dy, int Cp, const void* x, int Cq, i
 
 // 0 = fp16, 1 = bf16: the 16-bit storage / operand type this library was built with (types.cuh)
 extern "C" int encdiff_act_format(void) { return EDB_FMT; }
+
+// ---- HBM-bound operators on their own (tests/test_ops_gpu.py; encdiff_b200/attention.py) ---------------------------
+extern "C" int encdiff_op_group_norm(const void* x, const float* gamma, const float* beta, float eps, int silu,
+                                     void* out, float* stats, int B, int H, int W, int C, void* stream) {
+  EDB_REQUIRE(C % 32 == 0 && C % 8 == 0, "group_norm: C must be a multiple of 32");
+  GnParams p;
+  memset(&p, 0, sizeof(p));
+  p.x0 = static_cast<const h16*>(x);
+  p.C0 = C;
+  p.H = H;
+  p.W = W;
+  p.gamma = gamma;
+  p.beta = beta;
+  p.eps = eps;
+  p.silu = silu;
+  p.resample = RESAMPLE_NONE;
+  p.stats = stats;
+  p.act = static_cast<h16*>(out);
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_gn_fwd(p, B, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_op_layer_norm(const void* x, const float* gamma, const float* beta, float eps, void* y,
+                                     float* stats, long long M, int C, void* stream) {
+  EDB_REQUIRE(C % 8 == 0, "layer_norm: C must be a multiple of 8");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_ln_fwd(static_cast<const h16*>(x), gamma, beta, eps, static_cast<h16*>(y),
+                                                        stats, static_cast<int>(M), C, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_op_self_attention(const void* qkv, void* out, float* lse, int B, int N, int heads, int D,
+                                         void* stream) {
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_self_attn_fwd(static_cast<const h16*>(qkv), static_cast<h16*>(out), lse,
+                                                               B, N, heads, D, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_op_self_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
+                                             void* dqkv, int B, int N, int heads, int D, void* stream) {
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_self_attn_bwd(static_cast<const h16*>(qkv), static_cast<const h16*>(out),
+                                                               static_cast<const h16*>(dout), lse,
+                                                               static_cast<h16*>(dqkv), B, N, heads, D,
+                                                               static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_op_cross_attention(const void* q, const float* ctx, const float* wk, const float* wv, void* out,
+                                          int B, int N, int heads, int D, int T, int Dc, void* stream) {
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_cross_attn_fwd(static_cast<const h16*>(q), ctx, wk, wv,
+                                                                static_cast<h16*>(out), B, N, heads, D, T, Dc,
+                                                                static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" long long encdiff_op_cross_attention_bwd_scratch_bytes(int B, int heads, int D, int T) {
+  return static_cast<long long>(cross_attn_bwd_scratch_bytes(B, heads, D, T));
+}
+
+extern "C" int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, const float* wk, const float* wv,
+                                              const void* dout, void* dq, float* dwk, float* dwv, float* dctx,
+                                              float* scratch, int B, int N, int heads, int D, int T, int Dc,
+                                              void* stream) {
+  EDB_REQUIRE(scratch != nullptr, "cross_attention_bwd: scratch of encdiff_op_cross_attention_bwd_scratch_bytes() needed");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_cross_attn_bwd(static_cast<const h16*>(q), ctx, wk, wv,
+                                                                static_cast<const h16*>(dout), static_cast<h16*>(dq), dwk,
+                                                                dwv, dctx, nullptr, scratch, B, N, heads, D, T, Dc,
+                                                                static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_op_geglu(const void* g, void* out, long long M, int inner, void* stream) {
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_geglu_fwd(static_cast<const h16*>(g), static_cast<h16*>(out), M, inner,
+                                                           static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}

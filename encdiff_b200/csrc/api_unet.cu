@@ -127,7 +127,7 @@ extern "C" long long encdiff_unet_profile_read(encdiff_unet* h, char* buf, long 
   if (!h || !buf || cap <= 0) return -1;
   UNet& u = h->u;
   if (!u.prof_recs.empty() && cudaEventSynchronize(u.prof_recs.back().ev) != cudaSuccess) return -1;
-  std::map<std::string, std::tuple<long long, double, double>> agg;   // launches, ms, flops
+  std::map<std::string, std::tuple<long long, double, double, double>> agg;   // launches, ms, flops, bytes
   for (size_t i = 1; i < u.prof_recs.size(); ++i) {
     const ProfRec& r = u.prof_recs[i];
     if (r.name[0] == '(') continue;   // a "(begin)" marker: the gap before it is host time between calls
@@ -137,12 +137,13 @@ extern "C" long long encdiff_unet_profile_read(encdiff_unet* h, char* buf, long 
     std::get<0>(a) += 1;
     std::get<1>(a) += ms;
     std::get<2>(a) += r.flops;
+    std::get<3>(a) += r.bytes;
   }
   std::string out;
   char line[256];
   for (auto& kv : agg) {
-    snprintf(line, sizeof(line), "%s,%lld,%.6f,%.6e\n", kv.first.c_str(), std::get<0>(kv.second),
-             std::get<1>(kv.second), std::get<2>(kv.second));
+    snprintf(line, sizeof(line), "%s,%lld,%.6f,%.6e,%.6e\n", kv.first.c_str(), std::get<0>(kv.second),
+             std::get<1>(kv.second), std::get<2>(kv.second), std::get<3>(kv.second));
     out += line;
   }
   u.prof_recs.clear();

@@ -76,6 +76,7 @@ struct Layer {
 struct ProfRec {
   const char* name;
   double flops;
+  double bytes;
   cudaEvent_t ev;
 };
 

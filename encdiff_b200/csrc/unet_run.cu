@@ -182,6 +182,7 @@ struct Exec {
   int err = 0;
 
   double next_flops = 0;   // algorithmic FLOPs of the launch about to be reported through fail()
+  double next_bytes = 0;   // algorithmic HBM bytes of it (operands read once + result written once)
 
   void mark(const char* what) {
     if (!u->prof) return;
@@ -192,8 +193,9 @@ struct Exec {
     }
     cudaEvent_t ev = u->prof_pool[u->prof_used++];
     cudaEventRecord(ev, s);
-    u->prof_recs.push_back(ProfRec{what, next_flops, ev});
+    u->prof_recs.push_back(ProfRec{what, next_flops, next_bytes, ev});
     next_flops = 0;
+    next_bytes = 0;
   }
 
   // rc is a cudaError_t returned by a launcher
@@ -261,7 +263,9 @@ struct Exec {
     }
     int i = 0;
     long long K = 0;
+    double a_bytes = 0;
     for (const Src& sc : srcs) {
+      a_bytes += 2.0 * B * H * W * sc.C;
       const CUtensorMap* m = act_map(sc.p, sc.C, H, W, p.g);
       if (!m) return;
       p.amap[i] = *m;
@@ -302,6 +306,7 @@ struct Exec {
       q.ldres = ldres;
       q.act = act;
       next_flops = 2.0 * q.M * static_cast<double>(N) * static_cast<double>(K);
+      next_bytes = a_bytes + 2.0 * N * K + 2.0 * q.M * N * (res ? 2 : 1) + (bias ? 4.0 * N : 0.0);
       fail(launch_sgemm2(q, bn2, sms, s), "sgemm");
       return;
     }
@@ -321,7 +326,8 @@ struct Exec {
     p.ld0 = ld;
     p.split_col = 1 << 30;
     next_flops = 2.0 * p.M * static_cast<double>(N) * static_cast<double>(K);
-    fail(launch_sgemm(p, bn, s), "sgemm");
+    next_bytes = a_bytes + 2.0 * N * K + (fp32 ? 4.0 : 2.0) * p.M * N + (res ? 2.0 * p.M * N : 0.0) + (bias ? 4.0 * N : 0.0);
+    fail(launch_sgemm(p, bn, s), "sgemm.1tile");
   }
 
   void colsum(const h16* x, long long M, int ld, int col0, int N, float* d0, float* d1 = nullptr) {

@@ -138,6 +138,7 @@ class DenoiserTrainer:
         sb = self.sqrt_one_minus_alphas_cumprod[t].contiguous()
         tf = t.to(torch.float32)
         u._gflat.zero_()
+        st["loss"].zero_()                 # encdiff_l1_loss accumulates with atomics
         eps = u._run_forward(st["x0"], tf, st["cond"], training=True, noise=st["noise"], sqrt_acp=sa, sqrt_1macp=sb)
         deps = torch.empty_like(eps)
         _lib.check(lib.encdiff_l1_loss(eps.data_ptr(), st["noise"].data_ptr(), st["loss"].data_ptr(), deps.data_ptr(),

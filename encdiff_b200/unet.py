@@ -300,15 +300,15 @@ class UNetModel(nn.Module):
         _lib.check(self._lib.encdiff_unet_profile(self._h, int(enable)), "unet_profile")
 
     def profile_read(self):
-        """{family: (launches, total_ms, total_flops)} since the last read."""
+        """{family: (launches, total_ms, total_flops, total_algorithmic_bytes)} since the last read."""
         buf = C.create_string_buffer(1 << 16)
         n = self._lib.encdiff_unet_profile_read(self._h, buf, len(buf))
         if n < 0:
             raise RuntimeError("encdiff_b200: profile_read failed")
         out = {}
         for line in buf.value.decode().splitlines():
-            name, k, ms, fl = line.split(",")
-            out[name] = (int(k), float(ms), float(fl))
+            name, k, ms, fl, by = line.split(",")
+            out[name] = (int(k), float(ms), float(fl), float(by))
         return out
 
     def debug_block(self, section: int, index: int = 0) -> torch.Tensor:

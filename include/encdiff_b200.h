@@ -52,6 +52,36 @@ int encdiff_op_wgrad(const void* dy, int Cp, const void* x, int Cq, int H, int W
                      void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * Operator level: the HBM-bound kernels of SpatialTransformer / CrossAttention (ldm/modules/attention.py), exposed so
+ * each can be checked against its reference call site on its own.  h16 tensors, fp32 parameters.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* GroupNorm(32 groups) (+ optional SiLU): Normalize attention.py:76-77 (eps 1e-6), GroupNorm32 util.py:227-244 (1e-5).
+ *   x, out h16 [B, H*W, C] (NHWC); gamma, beta fp32 [C]; stats fp32 [B, 32, 2] receives (mean, rstd).          */
+int encdiff_op_group_norm(const void* x, const float* gamma, const float* beta, float eps, int silu, void* out,
+                          float* stats, int B, int H, int W, int C, void* stream);
+/* nn.LayerNorm over the last dim (attention.py:203-205): x, y h16 [M, C]; stats fp32 [M, 2] = (mean, rstd).    */
+int encdiff_op_layer_norm(const void* x, const float* gamma, const float* beta, float eps, void* y, float* stats,
+                          long long M, int C, void* stream);
+/* CrossAttention.forward with context=None between the projections (attention.py:176-190):
+ *   qkv h16 [B*N, 3*heads*D] (q | k | v, head h at columns h*D), out h16 [B*N, heads*D],
+ *   lse fp32 [B*heads*N] (log2 domain, consumed by the backward).  Scale D^-1/2.                                */
+int encdiff_op_self_attention(const void* qkv, void* out, float* lse, int B, int N, int heads, int D, void* stream);
+int encdiff_op_self_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                  int B, int N, int heads, int D, void* stream);
+/* CrossAttention.forward with a context of T concept tokens of width Dc, INCLUDING to_k / to_v (attention.py:174-190):
+ *   q h16 [B*N, heads*D], ctx fp32 [B, T, Dc], wk / wv fp32 [heads*D, Dc] (reference weight layout), out h16.
+ * Backward: dq h16, dwk / dwv / dctx fp32 (accumulated: caller zeroes), scratch fp32 of ..._scratch_bytes().     */
+int encdiff_op_cross_attention(const void* q, const float* ctx, const float* wk, const float* wv, void* out, int B,
+                               int N, int heads, int D, int T, int Dc, void* stream);
+long long encdiff_op_cross_attention_bwd_scratch_bytes(int B, int heads, int D, int T);
+int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, const float* wk, const float* wv, const void* dout,
+                                   void* dq, float* dwk, float* dwv, float* dctx, float* scratch, int B, int N,
+                                   int heads, int D, int T, int Dc, void* stream);
+/* GEGLU (attention.py:37-45): g h16 [M, 2*inner] (value | gate) -> out h16 [M, inner] = value * gelu_erf(gate)  */
+int encdiff_op_geglu(const void* g, void* out, long long M, int inner, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
  * Model level: the UNet denoiser.
  *   Replaces UNetModel.__init__/forward (ldm/modules/diffusionmodules/openaimodel_enc.py:443-748) and everything
  *   it calls: ResBlock (:179-275), Upsample/Downsample (:109-160), GroupNorm32 / timestep_embedding
@@ -110,7 +140,7 @@ int encdiff_unet_backward(encdiff_unet* h, int batch, const float* dout, const f
 
 /* Live per-launch timing for bench.py's roofline figure: while enabled, forward/backward record one CUDA event after
  * every kernel launch on the launching stream.  profile_read synchronises on the last event, writes one text line
- * "family,launches,total_ms,total_flops" per kernel family into buf and clears the records; returns the byte count,
+ * "family,launches,total_ms,total_flops,total_algorithmic_bytes" per kernel family into buf and clears the records; returns the byte count,
  * or -(needed) when cap is too small, or -1 on error. */
 int encdiff_unet_profile(encdiff_unet* h, int enable);
 long long encdiff_unet_profile_read(encdiff_unet* h, char* buf /*host*/, long long cap);

@@ -1,0 +1,198 @@
+"""Operator-level parity on the GPU, each kernel through its C-ABI entry point against the oracle's restatement of
+the reference call site: attention (tensor-core and CUDA-core variants, forward and backward), cross-attention with
+the fused to_k / to_v projections, GroupNorm, LayerNorm, GEGLU, timestep embedding, L1 loss, and the stand-alone
+SpatialTransformer / CrossAttention modules."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import unet_oracle as UO
+
+pytestmark = pytest.mark.gpu
+
+
+def lib_and_dtype():
+    from encdiff_b200 import _lib
+    return _lib, _lib.load(), _lib.act_dtype()
+
+
+def tol16():
+    from encdiff_b200 import _lib
+    return 2.5e-2 if _lib.act_dtype() == torch.bfloat16 else 4e-3
+
+
+def rel_err(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return ((a - b).abs().max() / (b.abs().max() + 1e-12)).item()
+
+
+def ref_attention(q, k, v, heads):
+    """attention.py:176-190 on fp32 [B, N, heads*D] tensors."""
+    B, N, C = q.shape
+    D = C // heads
+    sp = lambda t: t.view(B, -1, heads, D).transpose(1, 2)
+    s = torch.einsum("bhid,bhjd->bhij", sp(q), sp(k)) * D ** -0.5
+    o = torch.einsum("bhij,bhjd->bhid", s.softmax(-1), sp(v))
+    return o.transpose(1, 2).reshape(B, N, C)
+
+
+@pytest.mark.parametrize("N,D", [(256, 8), (64, 16), (16, 32), (4, 32), (64, 64)])
+def test_self_attention_fwd_bwd(cuda_device, N, D):
+    _lib, lib, dt = lib_and_dtype()
+    B, heads = 3, 8
+    C = heads * D
+    gen = torch.Generator().manual_seed(N + D)
+    qkv = (torch.randn(B, N, 3 * C, generator=gen) * 1.5).to(dt)
+    dout = (torch.randn(B, N, C, generator=gen) * 2.0 ** -6).to(dt)
+    q, k, v = (t.float().requires_grad_(True) for t in qkv.float().split(C, dim=-1))
+    want = ref_attention(q, k, v, heads)
+    want.backward(dout.float())
+    qd, dd = qkv.to(cuda_device).contiguous(), dout.to(cuda_device).contiguous()
+    out = torch.empty(B, N, C, dtype=dt, device=cuda_device)
+    lse = torch.empty(B * heads * N, dtype=torch.float32, device=cuda_device)
+    dqkv = torch.zeros_like(qd)
+    _lib.check(lib.encdiff_op_self_attention(qd.data_ptr(), out.data_ptr(), lse.data_ptr(), B, N, heads, D,
+                                             _lib.current_stream()))
+    _lib.check(lib.encdiff_op_self_attention_bwd(qd.data_ptr(), out.data_ptr(), dd.data_ptr(), lse.data_ptr(),
+                                                 dqkv.data_ptr(), B, N, heads, D, _lib.current_stream()))
+    torch.cuda.synchronize()
+    assert rel_err(out.float(), want.detach()) <= tol16()
+    for name, got, ref in zip("qkv", dqkv.float().split(C, dim=-1), (q.grad, k.grad, v.grad)):
+        assert rel_err(got, ref) <= 2 * tol16(), name
+
+
+@pytest.mark.parametrize("N,D", [(256, 8), (64, 16), (16, 32), (4, 32)])
+def test_cross_attention_fwd_bwd(cuda_device, N, D):
+    _lib, lib, dt = lib_and_dtype()
+    B, heads, T, Dc = 5, 8, 20, 16
+    C = heads * D
+    gen = torch.Generator().manual_seed(7 * N + D)
+    q16 = torch.randn(B, N, C, generator=gen).to(dt)
+    dout = (torch.randn(B, N, C, generator=gen) * 2.0 ** -6).to(dt)
+    ctx = torch.randn(B, T, Dc, generator=gen).requires_grad_(True)
+    wk = (torch.randn(C, Dc, generator=gen) * 0.3).requires_grad_(True)
+    wv = (torch.randn(C, Dc, generator=gen) * 0.3).requires_grad_(True)
+    q = q16.float().requires_grad_(True)
+    want = ref_attention(q, ctx @ wk.t(), ctx @ wv.t(), heads)
+    want.backward(dout.float())
+    dev = cuda_device
+    qd, dd = q16.to(dev).contiguous(), dout.to(dev).contiguous()
+    cd, wkd, wvd = ctx.detach().to(dev), wk.detach().to(dev), wv.detach().to(dev)
+    out = torch.empty(B, N, C, dtype=dt, device=dev)
+    _lib.check(lib.encdiff_op_cross_attention(qd.data_ptr(), cd.data_ptr(), wkd.data_ptr(), wvd.data_ptr(),
+                                              out.data_ptr(), B, N, heads, D, T, Dc, _lib.current_stream()))
+    dq = torch.zeros_like(qd)
+    dwk, dwv, dctx = torch.zeros_like(wkd), torch.zeros_like(wvd), torch.zeros_like(cd)
+    scratch = torch.empty(lib.encdiff_op_cross_attention_bwd_scratch_bytes(B, heads, D, T) // 4, dtype=torch.float32,
+                          device=dev)
+    _lib.check(lib.encdiff_op_cross_attention_bwd(qd.data_ptr(), cd.data_ptr(), wkd.data_ptr(), wvd.data_ptr(),
+                                                  dd.data_ptr(), dq.data_ptr(), dwk.data_ptr(), dwv.data_ptr(),
+                                                  dctx.data_ptr(), scratch.data_ptr(), B, N, heads, D, T, Dc,
+                                                  _lib.current_stream()))
+    torch.cuda.synchronize()
+    assert rel_err(out.float(), want.detach()) <= tol16()
+    assert rel_err(dq.float(), q.grad) <= 2 * tol16()
+    assert rel_err(dwk, wk.grad) <= 2 * tol16()
+    assert rel_err(dwv, wv.grad) <= 2 * tol16()
+    assert rel_err(dctx, ctx.grad) <= 2 * tol16()
+
+
+@pytest.mark.parametrize("C,H,eps,silu", [(64, 16, 1e-5, 1), (128, 8, 1e-6, 0), (256, 4, 1e-5, 1), (256, 2, 1e-6, 0)])
+def test_group_norm(cuda_device, C, H, eps, silu):
+    _lib, lib, dt = lib_and_dtype()
+    B = 4
+    gen = torch.Generator().manual_seed(C + H)
+    x = (torch.randn(B, C, H, H, generator=gen) * 2 + 0.5).to(dt)
+    w, b = torch.randn(C, generator=gen), torch.randn(C, generator=gen)
+    want = UO.group_norm32(x.float(), w, b, eps)
+    if silu:
+        want = F.silu(want)
+    xt = x.permute(0, 2, 3, 1).contiguous().to(cuda_device)
+    out = torch.empty_like(xt)
+    stats = torch.empty(B, 32, 2, dtype=torch.float32, device=cuda_device)
+    wd, bd = w.to(cuda_device), b.to(cuda_device)       # keep the device copies alive across the launch
+    _lib.check(lib.encdiff_op_group_norm(xt.data_ptr(), wd.data_ptr(), bd.data_ptr(),
+                                         eps, silu, out.data_ptr(), stats.data_ptr(), B, H, H, C, _lib.current_stream()))
+    assert rel_err(out.float().permute(0, 3, 1, 2), want) <= tol16()
+    xg = x.float().view(B, 32, -1)
+    assert rel_err(stats[:, :, 0], xg.mean(-1)) <= 1e-4
+    assert rel_err(stats[:, :, 1], (xg.var(-1, unbiased=False) + eps).rsqrt()) <= 1e-4
+
+
+@pytest.mark.parametrize("C", [64, 128, 256])
+def test_layer_norm_and_geglu(cuda_device, C):
+    _lib, lib, dt = lib_and_dtype()
+    M = 1000
+    gen = torch.Generator().manual_seed(C)
+    x = (torch.randn(M, C, generator=gen) * 3 - 1).to(dt)
+    w, b = torch.randn(C, generator=gen), torch.randn(C, generator=gen)
+    want = F.layer_norm(x.float(), (C,), w, b, 1e-5)
+    xd = x.to(cuda_device)
+    y = torch.empty_like(xd)
+    stats = torch.empty(M, 2, dtype=torch.float32, device=cuda_device)
+    wd, bd = w.to(cuda_device), b.to(cuda_device)
+    _lib.check(lib.encdiff_op_layer_norm(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), 1e-5,
+                                         y.data_ptr(), stats.data_ptr(), M, C, _lib.current_stream()))
+    assert rel_err(y.float(), want) <= tol16()
+    g = torch.randn(M, 8 * C, generator=gen).to(dt)
+    a, gate = g.float().chunk(2, dim=-1)
+    want = a * F.gelu(gate)                                          # erf GELU (attention.py:43-44)
+    gd = g.to(cuda_device)
+    out = torch.empty(M, 4 * C, dtype=dt, device=cuda_device)
+    _lib.check(lib.encdiff_op_geglu(gd.data_ptr(), out.data_ptr(), M, 4 * C, _lib.current_stream()))
+    assert rel_err(out.float(), want) <= tol16()
+
+
+def test_timestep_embedding_and_l1_loss(cuda_device):
+    _lib, lib, dt = lib_and_dtype()
+    t = torch.tensor([0., 1., 21., 500., 981., 999., 333.5])
+    want = UO.timestep_embedding(t, 64)
+    out = torch.empty(t.numel(), 64, dtype=dt, device=cuda_device)
+    td = t.to(cuda_device)
+    _lib.check(lib.encdiff_timestep_embedding(td.data_ptr(), out.data_ptr(), t.numel(), 64,
+                                              _lib.current_stream()))
+    assert (out.float().cpu() - want).abs().max().item() <= (8e-3 if dt == torch.bfloat16 else 1e-3)
+    gen = torch.Generator().manual_seed(0)
+    e, n = torch.randn(7, 3, 16, 16, generator=gen), torch.randn(7, 3, 16, 16, generator=gen)
+    ed, nd = e.to(cuda_device), n.to(cuda_device)
+    loss = torch.zeros(1, device=cuda_device)
+    de = torch.empty_like(ed)
+    _lib.check(lib.encdiff_l1_loss(ed.data_ptr(), nd.data_ptr(), loss.data_ptr(), de.data_ptr(), ed.numel(),
+                                   _lib.current_stream()))
+    assert abs(loss.item() - (e - n).abs().mean().item()) < 1e-6
+    assert torch.equal(de.cpu(), torch.sign(e - n) / e.numel())
+
+
+@pytest.mark.parametrize("C,H,d_head", [(64, 16, 8), (128, 8, 16), (256, 4, 32)])
+def test_standalone_spatial_transformer_and_cross_attention(cuda_device, C, H, d_head):
+    """encdiff_b200.SpatialTransformer / CrossAttention .forward (attention.py:170-193,250-261) vs the oracle."""
+    from encdiff_b200 import CrossAttention, SpatialTransformer
+    torch.manual_seed(C)
+    st = SpatialTransformer(C, 8, d_head, depth=1, context_dim=16)
+    for prm in st.parameters():
+        torch.nn.init.normal_(prm, std=0.05)
+    p = {"st." + k: v.detach().clone() for k, v in st.state_dict().items()}
+    B = 3
+    x, ctx = torch.randn(B, C, H, H), torch.randn(B, 20, 16)
+    lay = UO.Layer("st", "st", C, C, heads=8, d_head=d_head)
+    want = UO.spatial_transformer(p, lay, x, ctx)
+    st = st.to(cuda_device)
+    with torch.no_grad():
+        got = st(x.to(cuda_device), ctx.to(cuda_device))
+    assert got.shape == x.shape and got.dtype == x.dtype
+    assert rel_err(got, want) <= 2 * tol16()
+    tok = torch.randn(B, H * H, C)
+    blk = st.transformer_blocks[0]
+    assert isinstance(blk.attn2, CrossAttention)
+    with torch.no_grad():
+        got_x = blk.attn2(tok.to(cuda_device), ctx.to(cuda_device))
+        got_s = blk.attn1(tok.to(cuda_device))
+    assert rel_err(got_x, UO.attention(p, "st.transformer_blocks.0.attn2", tok, ctx, 8)) <= 2 * tol16()
+    assert rel_err(got_s, UO.attention(p, "st.transformer_blocks.0.attn1", tok, None, 8)) <= 2 * tol16()
+    with pytest.raises(RuntimeError, match="inference-only"):
+        st(x.to(cuda_device).requires_grad_(True), ctx.to(cuda_device))
+    with pytest.raises(NotImplementedError):
+        with torch.no_grad():
+            blk.attn1(tok.to(cuda_device), mask=torch.ones(B, H * H, dtype=torch.bool, device=cuda_device))

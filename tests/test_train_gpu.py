@@ -1,0 +1,101 @@
+"""Training hot path on the GPU (LatentDiffusion.p_losses forward + backward, AdamW + LitEma) against the CPU oracle:
+loss value, the fused graph-captured step, the optimiser kernel, the EMA rule and a short loss curve (north star: loss
+curve within 2 % of the reference; here on the tiny configuration so that the fp32 oracle finishes in seconds)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import diffusion_oracle as DO
+from oracle import unet_oracle as UO
+from oracle.make_golden import CONFIGS, seeded_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def make_unet(cfg, dev, seed=1):
+    from encdiff_b200 import UNetModel
+    m = UNetModel(image_size=cfg.image_size, in_channels=cfg.in_channels, out_channels=cfg.out_channels,
+                  model_channels=cfg.model_channels, attention_resolutions=list(cfg.attention_resolutions),
+                  num_res_blocks=cfg.num_res_blocks, channel_mult=list(cfg.channel_mult), num_heads=cfg.num_heads,
+                  use_scale_shift_norm=True, resblock_updown=True, use_spatial_transformer=True,
+                  context_dim=cfg.context_dim, latent_unit=cfg.latent_unit)
+    params = UO.make_params(cfg, seed=seed)
+    m.load_state_dict(params, strict=True)
+    return m.to(dev).train(), params
+
+
+def test_p_losses_matches_oracle(cuda_device):
+    from encdiff_b200.train import DenoiserTrainer
+    cfg = CONFIGS["tiny"]
+    m, params = make_unet(cfg, cuda_device)
+    tr = DenoiserTrainer(m, lr=1e-4, use_cuda_graph=False)
+    x, t, ctx, noise = seeded_inputs(cfg, 6, seed=21)
+    acp = DO.alphas_cumprod(DO.linear_betas())
+    want = DO.l1_loss(UO.unet_forward(params, cfg, DO.q_sample(x, t, noise, acp), t, [ctx]), noise)
+    cd = ctx.to(cuda_device).requires_grad_(True)
+    loss, ld = tr.p_losses(x.to(cuda_device), cd, t.to(cuda_device), noise.to(cuda_device))
+    assert abs(loss.item() - want.item()) <= 2e-3 * want.item()
+    assert set(ld) == {"train/loss_simple", "train/loss"}
+    loss.backward()
+    assert cd.grad is not None and all(p.grad is not None for p in m.parameters())
+
+
+def test_adamw_kernel_matches_torch(cuda_device):
+    """encdiff_adamw_step_dev (+EMA) against torch.optim.AdamW and the LitEma rule, 5 steps on one flat tensor."""
+    from encdiff_b200.train import FlatAdamWEMA
+    gen = torch.Generator().manual_seed(4)
+    w0 = torch.randn(10007, generator=gen)
+    ref = torch.nn.Parameter(w0.clone())
+    opt_ref = torch.optim.AdamW([ref], lr=3e-3, weight_decay=0.01)
+    prm = torch.nn.Parameter(w0.clone().to(cuda_device))
+    opt = FlatAdamWEMA([prm], lr=3e-3, weight_decay=0.01, use_ema=True)
+    shadow = w0.clone()
+    for step in range(1, 6):
+        g = torch.randn(10007, generator=gen)
+        ref.grad = g.clone()
+        opt_ref.step()
+        opt.write_hyper()
+        opt.launch(g.to(cuda_device) * 2.0, grad_scale=0.5)        # the 1/world factor is applied inside the kernel
+        decay = min(0.9999, (1 + step) / (10 + step))              # LitEma.forward, ema.py:31-42
+        shadow = shadow - (1.0 - decay) * (shadow - ref.detach())
+    torch.cuda.synchronize()
+    assert torch.allclose(prm.detach().cpu(), ref.detach(), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(opt.ema.cpu(), shadow, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_fused_step_loss_curve_vs_oracle(cuda_device, graph):
+    from encdiff_b200.train import DenoiserTrainer
+    cfg = CONFIGS["tiny"]
+    B, steps, lr = 8, 24, 2e-4
+    m, params = make_unet(cfg, cuda_device)
+    tr = DenoiserTrainer(m, lr=lr, weight_decay=0.01, use_ema=True, use_cuda_graph=graph)
+    # oracle: same batches, torch autograd + torch.optim.AdamW on CPU
+    p = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    opt = torch.optim.AdamW([p[n] for n, _ in UO.param_specs(cfg)], lr=lr, weight_decay=0.01)
+    acp = DO.alphas_cumprod(DO.linear_betas())
+    got, want = [], []
+    for i in range(steps):
+        x, t, ctx, noise = seeded_inputs(cfg, B, seed=1000 + i)
+        opt.zero_grad(set_to_none=True)
+        lo = DO.l1_loss(UO.unet_forward(p, cfg, DO.q_sample(x, t, noise, acp), t, [ctx]), noise)
+        lo.backward()
+        opt.step()
+        want.append(lo.item())
+        loss, dcond = tr.step(x.to(cuda_device), ctx.to(cuda_device), t.to(cuda_device), noise.to(cuda_device))
+        got.append(loss.item())
+        assert dcond.shape == ctx.shape
+    got, want = np.array(got), np.array(want)
+    rel = np.abs(got - want) / want
+    print(f"graph={graph}: loss {want[0]:.4f} -> {want[-1]:.4f} (oracle), {got[0]:.4f} -> {got[-1]:.4f} (cuda); "
+          f"max rel diff {rel.max():.2e}")
+    assert rel.max() <= 2e-2
+    assert want[-1] < want[0]                                   # it actually trains
+    # parameters after the run: same direction of travel as the oracle's
+    d_cuda = torch.cat([(q.detach().cpu() - params[n]).flatten() for n, q in m.named_parameters()]).double()
+    d_orac = torch.cat([(p[n].detach() - params[n]).flatten() for n, _ in m.named_parameters()]).double()
+    cos = torch.dot(d_cuda, d_orac) / (d_cuda.norm() * d_orac.norm())
+    print("parameter-update cosine", cos.item())
+    assert cos.item() > 0.98
+    ema = tr.ema_state()
+    assert set(ema) == {n for n, _ in m.named_parameters()}
