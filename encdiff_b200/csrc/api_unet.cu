@@ -18,6 +18,8 @@ extern "C" int encdiff_unet_create(const encdiff_unet_config* cfg, encdiff_unet*
   encdiff_unet* h = new (std::nothrow) encdiff_unet();
   EDB_REQUIRE(h, "unet_create: out of host memory");
   h->u.force_old_gemm = getenv("ENCDIFF_OLD_GEMM") != nullptr;
+  h->u.side_on = getenv("ENCDIFF_NO_SIDE_STREAM") == nullptr;
+  h->u.group_wgrad = getenv("ENCDIFF_NO_WGRAD_GROUP") == nullptr && !h->u.force_old_gemm;
   int rc = unet_build(&h->u, cfg);
   if (rc) {
     delete h;
@@ -28,6 +30,13 @@ extern "C" int encdiff_unet_create(const encdiff_unet_config* cfg, encdiff_unet*
 }
 
 extern "C" int encdiff_unet_destroy(encdiff_unet* h) {
+  if (h) {
+    UNet& u = h->u;
+    for (cudaEvent_t ev : u.prof_pool) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : {u.ev_fork, u.ev_join, u.ev_side_done[0], u.ev_side_done[1]})
+      if (ev) cudaEventDestroy(ev);
+    if (u.side) cudaStreamDestroy(u.side);
+  }
   delete h;
   return EDB_OK;
 }
@@ -90,7 +99,7 @@ extern "C" int encdiff_unet_pack_weights(encdiff_unet* h, void* stream) {
   EDB_REQUIRE(h && h->u.bound, "pack_weights before bind");
   UNet& u = h->u;
   EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_pack(reinterpret_cast<const PackEntry*>(u.packed),
-                                                      static_cast<int>(u.table.size()), u.pack_total, u.pbf(), u.pf32(),
+                                                      static_cast<int>(u.table.size()), u.pack_blocks, u.pbf(), u.pf32(),
                                                       static_cast<cudaStream_t>(stream))));
   return EDB_OK;
 }

@@ -18,6 +18,7 @@ template <int D>
 __global__ void __launch_bounds__(256) self_attn_fwd_kernel(const h16* __restrict__ qkv, h16* __restrict__ out,
                                                             float* __restrict__ lse, int N, int heads, int TN, int G,
                                                             int total_pairs, float scale_log2) {
+  pdl_enter();
   extern __shared__ float sm[];
   float* Ks = sm;
   float* Vs = sm + static_cast<size_t>(G) * N * D;
@@ -109,6 +110,7 @@ __global__ void __launch_bounds__(256) self_attn_bwd_kernel(const h16* __restric
                                                             const h16* __restrict__ dout, const float* __restrict__ lse,
                                                             h16* __restrict__ dqkv, int N, int heads, int TN, int G,
                                                             int total_pairs, float scale) {
+  pdl_enter();
   extern __shared__ float sm[];
   const size_t sz = static_cast<size_t>(G) * N * D;
   float* Qs = sm;
@@ -248,7 +250,7 @@ static int self_attn_fwd_t(const h16* qkv, h16* out, float* lse, int B, int N, i
   }
   dim3 grid((total + s.G - 1) / s.G, s.qtiles);
   const float scale_log2 = rsqrtf(static_cast<float>(D)) * kLog2e;
-  self_attn_fwd_kernel<D><<<grid, s.threads, smem, st>>>(qkv, out, lse, N, heads, s.TN, s.G, total, scale_log2);
+  launch_k(self_attn_fwd_kernel<D>, grid, s.threads, smem, st, qkv, out, lse, N, heads, s.TN, s.G, total, scale_log2);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -265,7 +267,7 @@ static int self_attn_bwd_t(const h16* qkv, const h16* out, const h16* dout, cons
     configured = smem;
   }
   dim3 grid((total + s.G - 1) / s.G, s.qtiles);
-  self_attn_bwd_kernel<D><<<grid, s.threads, smem, st>>>(qkv, out, dout, lse, dqkv, N, heads, s.TN, s.G, total,
+  launch_k(self_attn_bwd_kernel<D>, grid, s.threads, smem, st, qkv, out, dout, lse, dqkv, N, heads, s.TN, s.G, total,
                                                          rsqrtf(static_cast<float>(D)));
   return static_cast<int>(cudaGetLastError());
 }
@@ -345,6 +347,7 @@ __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restri
                                                              const float* __restrict__ wk, const float* __restrict__ wv,
                                                              h16* __restrict__ out, int N, int heads, int T, int Dc,
                                                              int TQ, float scale_log2) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int C = heads * D;
   float* Ks = sm;
@@ -423,6 +426,7 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const h16* __restri
                                                              const h16* __restrict__ dout, h16* __restrict__ dq,
                                                              float* __restrict__ dkv, int N, int heads, int T, int Dc,
                                                              int TQ, float scale) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int C = heads * D;
   const int TQP = TQ + 4;
@@ -573,6 +577,7 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_proj_kernel(const float* _
                                                                   float* __restrict__ dwv, float* __restrict__ dctx,
                                                                   const float* __restrict__ gscale, int B, int C, int T,
                                                                   int Dc) {
+  pdl_enter();
   extern __shared__ float sm[];
   float* w_s = sm;                    // [2C][Dc]: wk rows then wv rows
   float* g_s = w_s + 2 * C * Dc;      // [T][2C] dK | dV of the current sample
@@ -624,6 +629,91 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_proj_kernel(const float* _
   }
 }
 
+// All layers' projections in ONE launch (the backward keeps every layer's dK|dV when the weight gradients are deferred):
+// CTA = (chunk of `chunk` samples, layer).  dctx is accumulated with atomics (16 layers add into the same rows); the
+// weight gradient is summed over the CTA's samples in registers first.
+__global__ void __launch_bounds__(256) cross_attn_bwd_proj_group_kernel(const CrossProjEntry* __restrict__ tab,
+                                                                        const float* __restrict__ ctx,
+                                                                        float* __restrict__ dctx,
+                                                                        const float* __restrict__ gscale, int B, int T,
+                                                                        int Dc, int chunk) {
+  pdl_enter();
+  extern __shared__ float sm[];
+  const CrossProjEntry en = tab[blockIdx.y];
+  const int C = en.C;
+  float* w_s = sm;                    // [2C][Dc]
+  float* g_s = w_s + 2 * C * Dc;      // [T][2C]
+  float* ctx_s = g_s + T * 2 * C;     // [T][Dc]
+  const float ginv = gscale ? gscale[1] : 1.f;
+  for (int i = threadIdx.x; i < C * Dc; i += blockDim.x) {
+    w_s[i] = en.wk[i];
+    w_s[C * Dc + i] = en.wv[i];
+  }
+  constexpr int kRows = 4;
+  float acc[kRows][kMaxDc];
+#pragma unroll
+  for (int r = 0; r < kRows; ++r)
+#pragma unroll
+    for (int e = 0; e < kMaxDc; ++e) acc[r][e] = 0.f;
+  const int b_end = min(B, (static_cast<int>(blockIdx.x) + 1) * chunk);
+  for (int b = blockIdx.x * chunk; b < b_end; ++b) {
+    __syncthreads();
+    const float4* src = reinterpret_cast<const float4*>(en.dkv + static_cast<long long>(b) * T * 2 * C);
+    for (int i = threadIdx.x; i < T * 2 * C / 4; i += blockDim.x) reinterpret_cast<float4*>(g_s)[i] = src[i];
+    for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
+    __syncthreads();
+    // dctx[b][j][e]: 2C-long dot products, 8 lanes per output (T * Dc * 8 work items over the CTA)
+    for (int o = threadIdx.x >> 3; o < T * Dc; o += blockDim.x >> 3) {
+      const int j = o / Dc, e = o - j * Dc, l8 = threadIdx.x & 7;
+      float a = 0.f;
+      for (int c = l8; c < 2 * C; c += 8) a += g_s[j * 2 * C + c] * w_s[c * Dc + e];
+      a += __shfl_xor_sync(0xffffffffu, a, 1);
+      a += __shfl_xor_sync(0xffffffffu, a, 2);
+      a += __shfl_xor_sync(0xffffffffu, a, 4);
+      if (l8 == 0) atomicAdd(dctx + static_cast<long long>(b) * T * Dc + o, a * ginv);
+    }
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      const int row = threadIdx.x + r * 256;
+      if (row < 2 * C) {
+        for (int j = 0; j < T; ++j) {
+          const float g = g_s[j * 2 * C + row];
+#pragma unroll
+          for (int e = 0; e < kMaxDc; ++e)
+            if (e < Dc) acc[r][e] += g * ctx_s[j * Dc + e];
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) {
+    const int row = threadIdx.x + r * 256;
+    if (row < 2 * C) {
+      float* dst = row < C ? en.dwk + row * Dc : en.dwv + (row - C) * Dc;
+#pragma unroll
+      for (int e = 0; e < kMaxDc; ++e)
+        if (e < Dc) atomicAdd(dst + e, acc[r][e] * ginv);
+    }
+  }
+}
+
+int launch_cross_attn_bwd_proj_group(const CrossProjEntry* tab_dev, int n_layers, int max_C, const float* ctx, float* dctx,
+                                     const float* gscale, int B, int T, int Dc, cudaStream_t s) {
+  if (n_layers <= 0) return 0;
+  const size_t smem = (2ull * max_C * Dc + 2ull * T * max_C + T * Dc) * sizeof(float);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(cross_attn_bwd_proj_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = smem;
+  }
+  const int chunk = 8;
+  launch_k(cross_attn_bwd_proj_group_kernel, dim3((B + chunk - 1) / chunk, n_layers), 256, smem, s, tab_dev, ctx, dctx, gscale, B,
+           T, Dc, chunk);
+  return static_cast<int>(cudaGetLastError());
+}
+
 static int cross_tq(int N) { return N < 32 ? N : 32; }
 
 template <int D>
@@ -639,7 +729,7 @@ static int cross_fwd_t(const h16* q, const float* ctx, const float* wk, const fl
   }
   const int threads = heads * TQ >= 256 ? 256 : ((heads * TQ + 31) / 32) * 32;
   dim3 grid((N + TQ - 1) / TQ, B);
-  cross_attn_fwd_kernel<D><<<grid, threads < 64 ? 64 : threads, smem, st>>>(q, ctx, wk, wv, out, N, heads, T, Dc, TQ,
+  launch_k(cross_attn_fwd_kernel<D>, grid, threads < 64 ? 64 : threads, smem, st, q, ctx, wk, wv, out, N, heads, T, Dc, TQ,
                                                                             rsqrtf(static_cast<float>(D)) * kLog2e);
   return static_cast<int>(cudaGetLastError());
 }
@@ -657,7 +747,7 @@ static int cross_bwd_t(const h16* q, const float* ctx, const float* wk, const fl
   }
   const int threads = heads * TQ >= 256 ? 256 : ((heads * TQ + 31) / 32) * 32;
   dim3 grid((N + TQ - 1) / TQ, B);
-  cross_attn_bwd_kernel<D><<<grid, threads < 64 ? 64 : threads, smem, st>>>(q, ctx, wk, wv, dout, dq, dkv, N, heads, T, Dc,
+  launch_k(cross_attn_bwd_kernel<D>, grid, threads < 64 ? 64 : threads, smem, st, q, ctx, wk, wv, dout, dq, dkv, N, heads, T, Dc,
                                                                             TQ, rsqrtf(static_cast<float>(D)));
   return static_cast<int>(cudaGetLastError());
 }
@@ -680,7 +770,7 @@ size_t cross_attn_bwd_scratch_bytes(int B, int heads, int D, int T) {
 
 int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
                           float* dwk, float* dwv, float* dctx, const float* gscale, float* dkv_scratch, int B, int N,
-                          int heads, int D, int T, int Dc, cudaStream_t s) {
+                          int heads, int D, int T, int Dc, cudaStream_t s, bool defer_proj) {
   if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc || 2 * heads * D > 4 * 256) return static_cast<int>(cudaErrorInvalidValue);
   const int C = heads * D;
   cudaError_t e = cudaMemsetAsync(dkv_scratch, 0, cross_attn_bwd_scratch_bytes(B, heads, D, T), s);
@@ -693,7 +783,7 @@ int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const
     case 64: rc = cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
-  if (rc) return rc;
+  if (rc || defer_proj) return rc;
   const size_t smem = (2ull * C * Dc + 2ull * T * C + T * Dc) * sizeof(float);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
@@ -702,7 +792,7 @@ int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const
     configured = smem;
   }
   const int grid = B < 148 ? B : 148;
-  cross_attn_bwd_proj_kernel<<<grid, 256, smem, s>>>(dkv_scratch, ctx, wk, wv, dwk, dwv, dctx, gscale, B, C, T, Dc);
+  launch_k(cross_attn_bwd_proj_kernel, grid, 256, smem, s, dkv_scratch, ctx, wk, wv, dwk, dwv, dctx, gscale, B, C, T, Dc);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -87,6 +87,7 @@ template <int D>
 __global__ void __launch_bounds__(512) self_attn_fwd_mma_kernel(const h16* __restrict__ qkv, h16* __restrict__ out,
                                                                 float* __restrict__ lse, int N, int heads, int G,
                                                                 float scale_log2) {
+  pdl_enter();
   extern __shared__ __align__(16) uint8_t smraw[];
   const int NP = N + 8;
   h16* Ks = reinterpret_cast<h16*>(smraw);   // [G][N][D]
@@ -189,6 +190,7 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
                                                                 const h16* __restrict__ dout,
                                                                 const float* __restrict__ lse, h16* __restrict__ dqkv,
                                                                 int N, int heads, int G, float scale) {
+  pdl_enter();
   extern __shared__ __align__(16) uint8_t smraw[];
   const int NP = N + 8;
   h16* Qs = reinterpret_cast<h16*>(smraw);   // [G][N][D]
@@ -397,7 +399,7 @@ static int fwd_mma_t(const h16* qkv, h16* out, float* lse, int B, int N, int hea
     configured = smem;
   }
   const int threads = G * (N / 16) * 32;
-  self_attn_fwd_mma_kernel<D><<<B * (heads / G), threads, smem, st>>>(qkv, out, lse, N, heads, G,
+  launch_k(self_attn_fwd_mma_kernel<D>, B * (heads / G), threads, smem, st, qkv, out, lse, N, heads, G,
                                                                       rsqrtf(static_cast<float>(D)) * kLog2eM);
   return static_cast<int>(cudaGetLastError());
 }
@@ -425,7 +427,7 @@ static int bwd_mma_t(const h16* qkv, const h16* out, const h16* dout, const floa
     configured = smem;
   }
   const int threads = G * (N / 16) * 32;
-  self_attn_bwd_mma_kernel<D><<<B * (heads / G), threads, smem, st>>>(qkv, out, dout, lse, dqkv, N, heads, G,
+  launch_k(self_attn_bwd_mma_kernel<D>, B * (heads / G), threads, smem, st, qkv, out, dout, lse, dqkv, N, heads, G,
                                                                       rsqrtf(static_cast<float>(D)));
   return static_cast<int>(cudaGetLastError());
 }

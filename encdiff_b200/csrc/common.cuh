@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 #include "types.cuh"
 
@@ -214,4 +215,37 @@ __host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn_major, bool b
   return make_idesc_fmt(n, a_mn_major, b_mn_major, EDB_FMT, EDB_FMT);
 }
 
+
+// ---- programmatic dependent launch ------------------------------------------------------------------------------------
+// Every kernel of the step is launched with cudaLaunchAttributeProgrammaticStreamSerialization (launch_k below): its
+// CTAs may be scheduled while the previous kernel of the stream is still draining.  The contract each kernel keeps:
+//   * pdl_launch_dependents() as early as possible (lets the NEXT kernel's CTAs be scheduled once all of ours run);
+//   * pdl_wait() before the first global-memory access (read OR write): it returns when every prerequisite grid has
+//     completed and its writes are visible.  Only barrier / TMEM / descriptor set-up may precede it.
+// Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() {
+  pdl_launch_dependents();
+  pdl_wait();
+}
+
+bool pdl_enabled();   // host.cu: false when ENCDIFF_NO_PDL is set
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 }  // namespace edb

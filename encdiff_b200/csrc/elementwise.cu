@@ -13,6 +13,7 @@ static inline int grid_for(long long n, int block, int cap = 148 * 16) {
 
 // ---- timestep embedding (util.py:179-199): [cos(t f_i) | sin(t f_i)], f_i = exp(-ln(1e4) i / half) ---------------
 __global__ void temb_kernel(const float* __restrict__ t, h16* __restrict__ out, int B, int dim) {
+  pdl_enter();
   const int half = dim / 2;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < B * half; idx += gridDim.x * blockDim.x) {
     const int b = idx / half, i = idx - b * half;
@@ -24,33 +25,36 @@ __global__ void temb_kernel(const float* __restrict__ t, h16* __restrict__ out, 
   }
 }
 int launch_temb(const float* t, h16* out, int B, int dim, cudaStream_t s) {
-  temb_kernel<<<grid_for(static_cast<long long>(B) * (dim / 2), 256), 256, 0, s>>>(t, out, B, dim);
+  launch_k(temb_kernel, grid_for(static_cast<long long>(B) * (dim / 2), 256), 256, 0, s, t, out, B, dim);
   return static_cast<int>(cudaGetLastError());
 }
 
 // ---- SiLU on the (tiny) embedding MLP ------------------------------------------------------------------------------
 __global__ void silu_fwd_kernel(const float* __restrict__ x, h16* __restrict__ y, long long n) {
+  pdl_enter();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
     y[i] = f2h(silu_f(x[i]));
 }
 __global__ void silu_bwd_kernel(const float* __restrict__ x, const h16* __restrict__ dy, h16* __restrict__ dx,
                                 long long n) {
+  pdl_enter();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
     dx[i] = f2h(h2f(dy[i]) * silu_grad_f(x[i]));
 }
 int launch_silu_fwd(const float* x, h16* y, long long n, cudaStream_t s) {
-  silu_fwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, y, n);
+  launch_k(silu_fwd_kernel, grid_for(n, 256), 256, 0, s, x, y, n);
   return static_cast<int>(cudaGetLastError());
 }
 int launch_silu_bwd(const float* x, const h16* dy, h16* dx, long long n, cudaStream_t s) {
-  silu_bwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, dy, dx, n);
+  launch_k(silu_bwd_kernel, grid_for(n, 256), 256, 0, s, x, dy, dx, n);
   return static_cast<int>(cudaGetLastError());
 }
 
 // ---- GEGLU (attention.py:37-45) -------------------------------------------------------------------------------------
 __global__ void geglu_fwd_kernel(const h16* __restrict__ g, h16* __restrict__ out, long long M, int inner) {
+  pdl_enter();
   const int nv = inner >> 3;
   const long long total = M * nv;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -67,6 +71,7 @@ __global__ void geglu_fwd_kernel(const h16* __restrict__ g, h16* __restrict__ ou
 }
 __global__ void geglu_bwd_kernel(const h16* __restrict__ g, const h16* __restrict__ dout, h16* __restrict__ dg,
                                  long long M, int inner) {
+  pdl_enter();
   const int nv = inner >> 3;
   const long long total = M * nv;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -88,12 +93,12 @@ __global__ void geglu_bwd_kernel(const h16* __restrict__ g, const h16* __restric
 }
 int launch_geglu_fwd(const h16* g, h16* out, long long M, int inner, cudaStream_t s) {
   if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
-  geglu_fwd_kernel<<<grid_for(M * (inner / 8), 256), 256, 0, s>>>(g, out, M, inner);
+  launch_k(geglu_fwd_kernel, grid_for(M * (inner / 8), 256), 256, 0, s, g, out, M, inner);
   return static_cast<int>(cudaGetLastError());
 }
 int launch_geglu_bwd(const h16* g, const h16* dout, h16* dg, long long M, int inner, cudaStream_t s) {
   if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
-  geglu_bwd_kernel<<<grid_for(M * (inner / 8), 256), 256, 0, s>>>(g, dout, dg, M, inner);
+  launch_k(geglu_bwd_kernel, grid_for(M * (inner / 8), 256), 256, 0, s, g, dout, dg, M, inner);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -102,6 +107,7 @@ int launch_geglu_bwd(const h16* g, const h16* dout, h16* dg, long long M, int in
 __global__ void __launch_bounds__(256) colsum_kernel(const h16* __restrict__ x, long long M, int ld, int col0, int N,
                                                      float* __restrict__ dst0, float* __restrict__ dst1,
                                                      const float* __restrict__ gscale) {
+  pdl_enter();
   __shared__ float red[8][33];
   const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + cl;
@@ -128,7 +134,7 @@ int launch_colsum(const h16* x, long long M, int ld, int col0, int N, float* dst
   const long long cap = (148 * 8 + gx - 1) / gx;
   if (gy > cap) gy = cap;
   if (gy < 1) gy = 1;
-  colsum_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, 0, s>>>(x, M, ld, col0, N, dst0, dst1, gscale);
+  launch_k(colsum_kernel, dim3(gx, static_cast<unsigned>(gy)), 256, 0, s, x, M, ld, col0, N, dst0, dst1, gscale);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -136,6 +142,7 @@ int launch_colsum(const h16* x, long long M, int ld, int col0, int N, float* dst
 __global__ void stem_im2col_kernel(const float* __restrict__ x, const float* __restrict__ noise,
                                    const float* __restrict__ sa, const float* __restrict__ sb, float* __restrict__ xt,
                                    h16* __restrict__ cols, int B, int Cin, int H, int W) {
+  pdl_enter();
   const long long total = static_cast<long long>(B) * H * W;
   for (long long pix = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; pix < total;
        pix += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -167,13 +174,14 @@ __global__ void stem_im2col_kernel(const float* __restrict__ x, const float* __r
 int launch_stem_im2col(const float* x, const float* noise, const float* sa, const float* sb, float* xt, h16* cols,
                        int B, int Cin, int H, int W, cudaStream_t s) {
   if (Cin * 9 > 64) return static_cast<int>(cudaErrorInvalidValue);
-  stem_im2col_kernel<<<grid_for(static_cast<long long>(B) * H * W, 128), 128, 0, s>>>(x, noise, sa, sb, xt, cols, B,
+  launch_k(stem_im2col_kernel, grid_for(static_cast<long long>(B) * H * W, 128), 128, 0, s, x, noise, sa, sb, xt, cols, B,
                                                                                       Cin, H, W);
   return static_cast<int>(cudaGetLastError());
 }
 
 __global__ void stem_col2im_kernel(const h16* __restrict__ dcols, float* __restrict__ dx,
                                    const float* __restrict__ gscale, int B, int Cin, int H, int W) {
+  pdl_enter();
   const float ginv = gscale ? gscale[1] : 1.f;
   const long long total = static_cast<long long>(B) * Cin * H * W;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -193,12 +201,13 @@ __global__ void stem_col2im_kernel(const h16* __restrict__ dcols, float* __restr
   }
 }
 int launch_stem_col2im(const h16* dcols, float* dx, const float* gscale, int B, int Cin, int H, int W, cudaStream_t s) {
-  stem_col2im_kernel<<<grid_for(static_cast<long long>(B) * Cin * H * W, 256), 256, 0, s>>>(dcols, dx, gscale, B, Cin, H, W);
+  launch_k(stem_col2im_kernel, grid_for(static_cast<long long>(B) * Cin * H * W, 256), 256, 0, s, dcols, dx, gscale, B, Cin, H, W);
   return static_cast<int>(cudaGetLastError());
 }
 
 // ---- layout converters for the 3-channel head ------------------------------------------------------------------------
 __global__ void nhwc_to_nchw_kernel(const float* __restrict__ y, float* __restrict__ out, int B, int C, int HW) {
+  pdl_enter();
   const long long total = static_cast<long long>(B) * C * HW;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -209,10 +218,11 @@ __global__ void nhwc_to_nchw_kernel(const float* __restrict__ y, float* __restri
   }
 }
 int launch_nhwc_to_nchw(const float* y, float* out, int B, int C, int H, int W, cudaStream_t s) {
-  nhwc_to_nchw_kernel<<<grid_for(static_cast<long long>(B) * C * H * W, 256), 256, 0, s>>>(y, out, B, C, H * W);
+  launch_k(nhwc_to_nchw_kernel, grid_for(static_cast<long long>(B) * C * H * W, 256), 256, 0, s, y, out, B, C, H * W);
   return static_cast<int>(cudaGetLastError());
 }
 __global__ void grad_scale_kernel(const float* __restrict__ x, long long n, float* __restrict__ gscale) {
+  pdl_enter();
   float m = 0.f;
   for (long long i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, fabsf(x[i]));
   m = warp_max(m);
@@ -237,11 +247,12 @@ __global__ void grad_scale_kernel(const float* __restrict__ x, long long n, floa
   }
 }
 int launch_grad_scale(const float* x, long long n, float* gscale, cudaStream_t s) {
-  grad_scale_kernel<<<1, 1024, 0, s>>>(x, n, gscale);
+  launch_k(grad_scale_kernel, 1, 1024, 0, s, x, n, gscale);
   return static_cast<int>(cudaGetLastError());
 }
 __global__ void nchw_to_nhwc_h16_kernel(const float* __restrict__ x, h16* __restrict__ out,
                                          const float* __restrict__ gscale, int B, int C, int HW, int Cpad) {
+  pdl_enter();
   const float gsc = gscale ? gscale[0] : 1.f;
   const long long total = static_cast<long long>(B) * HW * Cpad;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -254,7 +265,7 @@ __global__ void nchw_to_nhwc_h16_kernel(const float* __restrict__ x, h16* __rest
 }
 int launch_nchw_to_nhwc_h16(const float* x, h16* out, const float* gscale, int B, int C, int H, int W, int Cpad,
                             cudaStream_t s) {
-  nchw_to_nhwc_h16_kernel<<<grid_for(static_cast<long long>(B) * H * W * Cpad, 256), 256, 0, s>>>(x, out, gscale, B, C,
+  launch_k(nchw_to_nhwc_h16_kernel, grid_for(static_cast<long long>(B) * H * W * Cpad, 256), 256, 0, s, x, out, gscale, B, C,
                                                                                                   H * W, Cpad);
   return static_cast<int>(cudaGetLastError());
 }
@@ -262,6 +273,7 @@ int launch_nchw_to_nhwc_h16(const float* x, h16* out, const float* gscale, int B
 // ---- L1 loss + its gradient (ddpm_enc.py:297-301,1198-1213) -----------------------------------------------------------
 __global__ void l1_loss_kernel(const float* __restrict__ e, const float* __restrict__ n, float* __restrict__ loss,
                                float* __restrict__ de, long long cnt, float inv) {
+  pdl_enter();
   float a = 0.f;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < cnt;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -280,7 +292,7 @@ __global__ void l1_loss_kernel(const float* __restrict__ e, const float* __restr
   }
 }
 int launch_l1_loss(const float* eps_hat, const float* noise, float* loss, float* deps, long long n, cudaStream_t s) {
-  l1_loss_kernel<<<grid_for(n, 256, 148 * 4), 256, 0, s>>>(eps_hat, noise, loss, deps, n, 1.0f / static_cast<float>(n));
+  launch_k(l1_loss_kernel, grid_for(n, 256, 148 * 4), 256, 0, s, eps_hat, noise, loss, deps, n, 1.0f / static_cast<float>(n));
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -288,6 +300,7 @@ int launch_l1_loss(const float* eps_hat, const float* noise, float* loss, float*
 __global__ void ddim_update_kernel(const float* __restrict__ x, const float* __restrict__ e, const float* __restrict__ nz,
                                    const float* __restrict__ coef, float temperature, float* __restrict__ x_prev,
                                    float* __restrict__ pred_x0, long long n) {
+  pdl_enter();
   const float a_t = coef[0], a_prev = coef[1], sigma = coef[2], somat = coef[3];
   const float sqrt_at = sqrtf(a_t), sqrt_ap = sqrtf(a_prev);
   const float dir = sqrtf(__fsub_rn(__fsub_rn(1.f, a_prev), __fmul_rn(sigma, sigma)));
@@ -303,7 +316,7 @@ __global__ void ddim_update_kernel(const float* __restrict__ x, const float* __r
 }
 int launch_ddim_update(const float* x, const float* e_t, const float* noise, const float* coef, float temperature,
                        float* x_prev, float* pred_x0, long long n, cudaStream_t s) {
-  ddim_update_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, e_t, noise, coef, temperature, x_prev, pred_x0, n);
+  launch_k(ddim_update_kernel, grid_for(n, 256), 256, 0, s, x, e_t, noise, coef, temperature, x_prev, pred_x0, n);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -311,6 +324,7 @@ int launch_ddim_update(const float* x, const float* e_t, const float* noise, con
 // cursor[0] = loop iteration i; writes ts[b] = t_table[i] (ddim.py:143), idx[0] = i, then advances the cursor.
 __global__ void ddim_select_kernel(const float* __restrict__ t_table, int* __restrict__ cursor, float* __restrict__ ts,
                                    int* __restrict__ idx, int B) {
+  pdl_enter();
   const int i = *cursor;
   __syncthreads();
   const float t = t_table[i];
@@ -321,13 +335,14 @@ __global__ void ddim_select_kernel(const float* __restrict__ t_table, int* __res
   }
 }
 int launch_ddim_select(const float* t_table, int* cursor, float* ts, int* idx, int B, cudaStream_t s) {
-  ddim_select_kernel<<<1, 256, 0, s>>>(t_table, cursor, ts, idx, B);
+  launch_k(ddim_select_kernel, 1, 256, 0, s, t_table, cursor, ts, idx, B);
   return static_cast<int>(cudaGetLastError());
 }
 __global__ void ddim_update_indexed_kernel(const float* __restrict__ x, const float* __restrict__ e,
                                            const float* __restrict__ noise_table, const float* __restrict__ coef_table,
                                            const int* __restrict__ idx, float temperature, float* __restrict__ x_prev,
                                            float* __restrict__ pred_x0, long long n) {
+  pdl_enter();
   const int it = *idx;
   const float* coef = coef_table + 4 * it;
   const float* nz = noise_table ? noise_table + static_cast<long long>(it) * n : nullptr;
@@ -347,47 +362,102 @@ __global__ void ddim_update_indexed_kernel(const float* __restrict__ x, const fl
 int launch_ddim_update_indexed(const float* x, const float* e_t, const float* noise_table, const float* coef_table,
                                const int* idx, float temperature, float* x_prev, float* pred_x0, long long n,
                                cudaStream_t s) {
-  ddim_update_indexed_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, e_t, noise_table, coef_table, idx, temperature, x_prev,
+  launch_k(ddim_update_indexed_kernel, grid_for(n, 256), 256, 0, s, x, e_t, noise_table, coef_table, idx, temperature, x_prev,
                                                              pred_x0, n);
   return static_cast<int>(cudaGetLastError());
 }
 
 // ---- weight packing: fp32 reference-layout parameters -> h16 GEMM operands (and fused fp32 biases) -------------------
-__global__ void pack_kernel(const PackEntry* __restrict__ tab, int n_entries, long long total, h16* __restrict__ abf,
-                            float* __restrict__ af32) {
-  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-    int lo = 0, hi = n_entries - 1;   // last entry with prefix <= idx
+// One block = one unit of one table entry (PackEntry::blk0 = first block of the entry):
+//   kinds 0 / 1 (weights): a tile of 32 rows x kPackCols source columns (cin-tile * taps) goes through shared memory, so
+//     the fp32 reads are contiguous runs of the reference tensor and the 16-bit writes are contiguous runs of the
+//     operand, for the forward (tap-major K) and the transposed layout alike;
+//   other kinds (biases, stem): 256 consecutive source elements, element-wise.
+static constexpr int kPackCols = 288;      // 32 input channels x 9 taps, or 288 input channels x 1 tap
+__global__ void __launch_bounds__(256) pack_kernel(const PackEntry* __restrict__ tab, int n_entries,
+                                                   h16* __restrict__ abf, float* __restrict__ af32) {
+  pdl_enter();
+  __shared__ float tile[32][kPackCols + 1];
+  __shared__ int s_entry;
+  if (threadIdx.x == 0) {
+    int lo = 0, hi = n_entries - 1;   // last entry with blk0 <= blockIdx.x
+    const int bid = static_cast<int>(blockIdx.x);
     while (lo < hi) {
       const int mid = (lo + hi + 1) >> 1;
-      if (tab[mid].prefix <= idx) lo = mid; else hi = mid - 1;
+      if (tab[mid].blk0 <= bid) lo = mid; else hi = mid - 1;
     }
-    const PackEntry& en = tab[lo];
-    const long long e = idx - en.prefix;
-    const float v = en.src[e];
-    if (en.kind == 2) {
-      af32[en.dst_off + en.col0 + e] = v;
-    } else if (en.kind == 3) {
-      af32[en.dst_off + en.col0 + e] = v + en.src2[e];
-    } else {
-      const int per_row = en.cin * en.taps;
-      const int r = static_cast<int>(e / per_row);
-      const int rem = static_cast<int>(e - static_cast<long long>(r) * per_row);
-      const int ci = rem / en.taps, tap = rem - ci * en.taps;
-      long long row, col;
-      switch (en.kind) {
-        case 0: row = en.row0 + r; col = en.col0 + tap * en.cin_pad + ci; break;
-        case 1: row = en.row0 + ci; col = en.col0 + tap * en.rows_pad + r; break;
-        case 4: row = en.row0 + r; col = en.col0 + rem; break;
-        default: row = en.row0 + rem; col = en.col0 + r; break;   // 5
+    s_entry = lo;
+  }
+  __syncthreads();
+  const PackEntry en = tab[s_entry];
+  const int tb = static_cast<int>(blockIdx.x) - en.blk0;
+  if (en.kind == 0 || en.kind == 1) {
+    const int ci_tile = kPackCols / en.taps;
+    const int cts = (en.cin + ci_tile - 1) / ci_tile;
+    const int rt = tb / cts, cit = tb - rt * cts;
+    const int r0 = rt * 32, ci0 = cit * ci_tile;
+    const int nr = min(32, en.rows - r0), nci = min(ci_tile, en.cin - ci0);
+    const int w = nci * en.taps;                          // source columns of this tile
+    const long long row_len = static_cast<long long>(en.cin) * en.taps;
+    for (int i = threadIdx.x; i < nr * w; i += blockDim.x) {
+      const int rr = i / w, k = i - rr * w;
+      tile[rr][k] = en.src[(r0 + rr) * row_len + static_cast<long long>(ci0) * en.taps + k];
+    }
+    __syncthreads();
+    h16* dst = abf + en.dst_off;
+    if (en.kind == 0) {         // dst[row0 + r][col0 + tap * cin_pad + ci]: ci fastest
+      for (int i = threadIdx.x; i < nr * w; i += blockDim.x) {
+        const int rr = i / w, rem = i - rr * w;
+        const int tap = rem / nci, c = rem - tap * nci;
+        dst[static_cast<long long>(en.row0 + r0 + rr) * en.dst_ld + en.col0 + tap * en.cin_pad + ci0 + c] =
+            f2h(tile[rr][c * en.taps + tap]);
       }
-      abf[en.dst_off + row * en.dst_ld + col] = f2h(v);
+    } else {                    // dst[row0 + ci][col0 + tap * rows_pad + r]: r fastest
+      const int per_c = en.taps * nr;
+      for (int i = threadIdx.x; i < nci * per_c; i += blockDim.x) {
+        const int c = i / per_c, rem = i - c * per_c;
+        const int tap = rem / nr, rr = rem - tap * nr;
+        dst[static_cast<long long>(en.row0 + ci0 + c) * en.dst_ld + en.col0 + tap * en.rows_pad + r0 + rr] =
+            f2h(tile[rr][c * en.taps + tap]);
+      }
     }
+    return;
+  }
+  const long long n = static_cast<long long>(en.rows) * en.cin * en.taps;
+  const long long e = static_cast<long long>(tb) * 256 + threadIdx.x;
+  if (e >= n) return;
+  const float v = en.src[e];
+  if (en.kind == 2) {
+    af32[en.dst_off + en.col0 + e] = v;
+  } else if (en.kind == 3) {
+    af32[en.dst_off + en.col0 + e] = v + en.src2[e];
+  } else {
+    const int per_row = en.cin * en.taps;
+    const int r = static_cast<int>(e / per_row);
+    const int rem = static_cast<int>(e - static_cast<long long>(r) * per_row);
+    long long row, col;
+    if (en.kind == 4) {        // stem: flat reference order
+      row = en.row0 + r;
+      col = en.col0 + rem;
+    } else {                   // 5: stem transposed
+      row = en.row0 + rem;
+      col = en.col0 + r;
+    }
+    abf[en.dst_off + row * en.dst_ld + col] = f2h(v);
   }
 }
-int launch_pack(const PackEntry* table_dev, int n_entries, long long total, h16* arena_h16, float* arena_f32,
+int pack_entry_blocks(const PackEntry& e) {
+  if (e.kind == 0 || e.kind == 1) {
+    const int ci_tile = kPackCols / e.taps;
+    return ((e.rows + 31) / 32) * ((e.cin + ci_tile - 1) / ci_tile);
+  }
+  const long long n = static_cast<long long>(e.rows) * e.cin * e.taps;
+  return static_cast<int>((n + 255) / 256);
+}
+int launch_pack(const PackEntry* table_dev, int n_entries, int n_blocks, h16* arena_h16, float* arena_f32,
                 cudaStream_t s) {
-  pack_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, s>>>(table_dev, n_entries, total, arena_h16, arena_f32);
+  if (n_blocks <= 0) return 0;
+  launch_k(pack_kernel, n_blocks, 256, 0, s, table_dev, n_entries, arena_h16, arena_f32);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -395,6 +465,7 @@ int launch_pack(const PackEntry* table_dev, int n_entries, long long total, h16*
 __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                              float* __restrict__ v, float* __restrict__ ema, long long n, float lr, float b1, float b2,
                              float eps, float wd, float bc1, float bc2, float ema_decay) {
+  pdl_enter();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     float w = p[i];
@@ -412,7 +483,7 @@ __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
 }
 int launch_adamw(float* p, const float* g, float* m, float* v, float* ema, long long n, float lr, float beta1,
                  float beta2, float eps, float wd, float bc1, float bc2, float ema_decay, cudaStream_t s) {
-  adamw_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, s>>>(p, g, m, v, ema, n, lr, beta1, beta2, eps, wd, bc1, bc2,
+  launch_k(adamw_kernel, grid_for(n, 256, 148 * 16), 256, 0, s, p, g, m, v, ema, n, lr, beta1, beta2, eps, wd, bc1, bc2,
                                                           ema_decay);
   return static_cast<int>(cudaGetLastError());
 }
@@ -423,6 +494,7 @@ __global__ void adamw_dev_kernel(float* __restrict__ p, const float* __restrict_
                                  float* __restrict__ v, float* __restrict__ ema, long long n,
                                  const float* __restrict__ hyper, float b1, float b2, float eps, float wd,
                                  float grad_scale) {
+  pdl_enter();
   const float lr = hyper[0], bc1 = hyper[1], bc2 = hyper[2], ema_decay = hyper[3];
   const float rs = rsqrtf(bc2), step = lr / bc1, keep = 1.f - lr * wd, om = 1.f - ema_decay;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
@@ -440,7 +512,7 @@ __global__ void adamw_dev_kernel(float* __restrict__ p, const float* __restrict_
 }
 int launch_adamw_dev(float* p, const float* g, float* m, float* v, float* ema, long long n, const float* hyper,
                      float beta1, float beta2, float eps, float wd, float grad_scale, cudaStream_t s) {
-  adamw_dev_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, s>>>(p, g, m, v, ema, n, hyper, beta1, beta2, eps, wd,
+  launch_k(adamw_dev_kernel, grid_for(n, 256, 148 * 16), 256, 0, s, p, g, m, v, ema, n, hyper, beta1, beta2, eps, wd,
                                                               grad_scale);
   return static_cast<int>(cudaGetLastError());
 }

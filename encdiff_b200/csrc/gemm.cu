@@ -26,6 +26,7 @@ __device__ __forceinline__ void tile_origin(const TileGeom& g, int tile, int& b0
 // =============================================================================================
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192) sgemm_kernel(const __grid_constant__ SgemmParams p) {
+  pdl_launch_dependents();
   constexpr int B_BYTES = BN * kChunk * 2;
   constexpr int STAGE_BYTES = kABytes + B_BYTES;
   constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
@@ -60,6 +61,7 @@ __global__ void __launch_bounds__(192) sgemm_kernel(const __grid_constant__ Sgem
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // set-up above touched no global memory; everything below may
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -187,7 +189,7 @@ static int launch_sgemm_t(const SgemmParams& p, cudaStream_t stream) {
     configured = true;
   }
   dim3 grid((p.M + kTileM - 1) / kTileM, (p.N + BN - 1) / BN, 1);
-  sgemm_kernel<BN, STAGES><<<grid, 192, smem, stream>>>(p);
+  launch_k(sgemm_kernel<BN, STAGES>, grid, 192, smem, stream, p);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -212,6 +214,7 @@ int launch_sgemm(const SgemmParams& p, int bn, cudaStream_t stream) {
 // =============================================================================================
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ WgradParams p) {
+  pdl_launch_dependents();
   constexpr int P_BYTES = 2 * kABytes;            // two 64-channel boxes of dY -> UMMA M = 128
   constexpr int Q_BYTES = (BN / 64) * kABytes;    // BN/64 boxes of X
   constexpr int STAGE_BYTES = P_BYTES + Q_BYTES;
@@ -248,6 +251,7 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ Wgra
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // set-up above touched no global memory; everything below may
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -335,7 +339,7 @@ static int launch_wgrad_t(const WgradParams& p0, int splits, cudaStream_t stream
   p.tiles_per_split = (p.m_tiles + splits - 1) / splits;
   splits = (p.m_tiles + p.tiles_per_split - 1) / p.tiles_per_split;  // no empty CTAs
   dim3 grid((p.Cp + 127) / 128, p.taps * ((p.Cq + BN - 1) / BN), splits);
-  wgrad_kernel<BN, STAGES><<<grid, 192, smem, stream>>>(p);
+  launch_k(wgrad_kernel<BN, STAGES>, grid, 192, smem, stream, p);
   return static_cast<int>(cudaGetLastError());
 }
 

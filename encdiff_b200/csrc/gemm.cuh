@@ -79,7 +79,7 @@ struct WgradParams {
 };
 
 // persistent weight-gradient kernel (wgrad2.cu)
-struct Wgrad2Params {
+struct alignas(64) Wgrad2Params {
   CUtensorMap pmap;     // dY  4D (Cdy, W, H, B) box (64, ...)
   CUtensorMap qmap;     // X   4D (Cx, W, H, B) box (64, ...)
   CUtensorMap omap;     // fp32 destination: 2D (Cq_total, Cp) [linear / 1x1] or 3D (Cq, Cp, 9) tap-major staging
@@ -99,6 +99,9 @@ struct WgradFinalizeEntry {
   long long pq;         // Cp * Cq
 };
 int launch_wgrad2(const Wgrad2Params& p, int num_sms, cudaStream_t stream);
+// grouped form: problems in device memory (64-byte aligned), prefix[n + 1] = first global item of each problem
+int wgrad2_prepare_group(Wgrad2Params* p, int steps);
+int launch_wgrad2_group(const Wgrad2Params* tab_dev, const int* prefix_dev, int total, int num_sms, cudaStream_t stream);
 int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total_padded, cudaStream_t s);
 
 // BN in {32(padded small N), 64, 128, 256}; returns cudaError_t as int

@@ -10,6 +10,8 @@
 //   warp 1      MMA issuer: one elected lane, tcgen05.mma into one of TWO TMEM accumulator stages.
 //   warps 2..5  epilogue: TMEM -> registers (tcgen05.ld) -> bias / SiLU / residual -> 16-bit -> 128B-swizzled staging
 //               panel in shared memory -> TMA store.  Runs concurrently with the mainloop of the next tile.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "gemm.cuh"
 
@@ -44,8 +46,9 @@ __device__ __forceinline__ void tile_origin2(const TileGeom& g, int tile, int& b
   }
 }
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(192, 1) sgemm2_kernel(const __grid_constant__ Sgemm2Params p) {
+template <int BN, int STAGES, int OCC>
+__global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant__ Sgemm2Params p) {
+  pdl_launch_dependents();
   constexpr int B_BYTES = BN * kChunk2 * 2;
   constexpr int STAGE_BYTES = kABytes2 + B_BYTES;
   constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
@@ -88,6 +91,7 @@ __global__ void __launch_bounds__(192, 1) sgemm2_kernel(const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // set-up above touched no global memory; everything below may
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -160,6 +164,14 @@ __global__ void __launch_bounds__(192, 1) sgemm2_kernel(const __grid_constant__ 
           bs[i] = n < p.N ? __ldg(p.bias + n) : 0.f;
         }
       }
+      // the residual rows do not depend on the MMA: fetch panel 0's before waiting for the accumulator
+      uint4 rres[8];
+      const bool has_res = p.res && row_ok;
+      const h16* res_row = reinterpret_cast<const h16*>(p.res) + row * p.ldres + n_tile * BN;
+      if (has_res) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) rres[j] = __ldg(reinterpret_cast<const uint4*>(res_row + 8 * j));
+      }
       mbar_wait(&tfull[acc], aph);
       tc_fence_after();
 #pragma unroll 1
@@ -182,14 +194,17 @@ __global__ void __launch_bounds__(192, 1) sgemm2_kernel(const __grid_constant__ 
 #pragma unroll
           for (int i = 0; i < 64; ++i) v[i] = silu_f(v[i]);
         }
-        if (p.res && row_ok) {
-          const h16* rp = reinterpret_cast<const h16*>(p.res) + row * p.ldres + n0;
+        if (has_res) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             float f[8];
-            unpack8(__ldg(reinterpret_cast<const uint4*>(rp + 8 * j)), f);
+            unpack8(rres[j], f);
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[8 * j + i] += f[i];
+          }
+          if (pn + 1 < PANELS && n0 + 64 < p.N) {   // next panel's rows: in flight during this panel's store
+#pragma unroll
+            for (int j = 0; j < 8; ++j) rres[j] = __ldg(reinterpret_cast<const uint4*>(res_row + (pn + 1) * 64 + 8 * j));
           }
         }
         uint8_t* rowp = slot + r * 128;
@@ -213,18 +228,25 @@ __global__ void __launch_bounds__(192, 1) sgemm2_kernel(const __grid_constant__ 
   if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int OCC>
 static int launch_sgemm2_t(const Sgemm2Params& p, int num_sms, cudaStream_t stream) {
   constexpr int smem = STAGES * (kABytes2 + BN * kChunk2 * 2) + 2 * kPanelBytes + 2 * BN * 4 + 1024 + 256;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(sgemm2_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(sgemm2_kernel<BN, STAGES, OCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = true;
   }
   const int tiles = p.m_tiles * ((p.N + BN - 1) / BN);
-  const int grid = tiles < num_sms ? tiles : num_sms;
-  sgemm2_kernel<BN, STAGES><<<grid, 192, smem, stream>>>(p);
+  const int grid = tiles < OCC * num_sms ? tiles : OCC * num_sms;
+  static const bool log = getenv("ENCDIFF_GEMM_LOG") != nullptr;
+  if (log) {
+    int kb = 0;
+    for (int s = 0; s < p.nsrc; ++s) kb += p.src_chunks[s] * p.src_taps[s];
+    fprintf(stderr, "GEMMLOG sgemm2 M=%d N=%d K=%d taps=%d bn=%d st=%d grid=%d tiles=%d\n", p.M, p.N, kb * 64, p.src_taps[0], BN,
+            STAGES, grid, tiles);
+  }
+  launch_k(sgemm2_kernel<BN, STAGES, OCC>, grid, 192, smem, stream, p);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -237,10 +259,16 @@ int sgemm2_pick_bn(int m_tiles, int N, int num_sms) {
 }
 
 int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t stream) {
+  int nkb = 0;
+  for (int s = 0; s < p.nsrc; ++s) nkb += p.src_chunks[s] * p.src_taps[s];
+  // short-K GEMMs (1x1 / linear with K <= 256): a tile is 1-4 k-blocks, so a deep smem ring buys nothing; two small
+  // CTAs per SM overlap one CTA's epilogue / fill / drain with the other's loads instead
+  static const bool no_occ2 = getenv("ENCDIFF_NO_OCC2") != nullptr;
+  const bool shallow = nkb <= 4 && !no_occ2;
   switch (bn) {
-    case 64: return launch_sgemm2_t<64, 6>(p, num_sms, stream);
-    case 128: return launch_sgemm2_t<128, 5>(p, num_sms, stream);
-    case 256: return launch_sgemm2_t<256, 3>(p, num_sms, stream);
+    case 64: return shallow ? launch_sgemm2_t<64, 3, 2>(p, num_sms, stream) : launch_sgemm2_t<64, 6, 1>(p, num_sms, stream);
+    case 128: return shallow ? launch_sgemm2_t<128, 2, 2>(p, num_sms, stream) : launch_sgemm2_t<128, 5, 1>(p, num_sms, stream);
+    case 256: return launch_sgemm2_t<256, 3, 1>(p, num_sms, stream);
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
 }

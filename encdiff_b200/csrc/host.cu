@@ -1,3 +1,5 @@
+#include <stdlib.h>
+
 #include "host.cuh"
 #include "types.cuh"
 
@@ -150,6 +152,11 @@ int device_sm_count() {
       n = 148;
   }
   return n;
+}
+
+bool pdl_enabled() {
+  static const bool on = getenv("ENCDIFF_NO_PDL") == nullptr;
+  return on;
 }
 
 }  // namespace edb

@@ -60,7 +60,20 @@ int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const
                           int heads, int D, int T, int Dc, cudaStream_t s);
 int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
                           float* dwk, float* dwv, float* dctx, const float* gscale, float* dkv_scratch, int B, int N,
-                          int heads, int D, int T, int Dc, cudaStream_t s);
+                          int heads, int D, int T, int Dc, cudaStream_t s, bool defer_proj = false);
+// deferred form of the projection half (d to_k, d to_v, d context) for all layers at once: dkv of every layer must still
+// be alive; dctx is accumulated with atomics (caller zeroes it)
+struct CrossProjEntry {
+  const float* dkv;      // [B, T, 2C]
+  const float* wk;       // [C, Dc]
+  const float* wv;
+  float* dwk;
+  float* dwv;
+  int C;
+  int pad;
+};
+int launch_cross_attn_bwd_proj_group(const CrossProjEntry* tab_dev, int n_layers, int max_C, const float* ctx, float* dctx,
+                                     const float* gscale, int B, int T, int Dc, cudaStream_t s);
 // bytes of the fp32 scratch [B, T, 2*heads*D] the backward needs (per-sample dK | dV before the to_k / to_v transpose)
 size_t cross_attn_bwd_scratch_bytes(int B, int heads, int D, int T);
 
@@ -119,8 +132,11 @@ struct PackEntry {
   int rows, cin, taps;
   int cin_pad, rows_pad;
   int dst_ld, row0, col0;
+  int blk0;              // first block of this entry in the pack launch (pack_entry_blocks() blocks each)
+  int pad_;
 };
-int launch_pack(const PackEntry* table_dev, int n_entries, long long total, h16* arena_h16, float* arena_f32,
+int pack_entry_blocks(const PackEntry& e);   // taps <= 9 for kinds 0 / 1
+int launch_pack(const PackEntry* table_dev, int n_entries, int n_blocks, h16* arena_h16, float* arena_f32,
                 cudaStream_t s);
 
 // fused AdamW (+ optional EMA) over a flat fp32 parameter buffer (ddpm_enc.py:1598-1639, ema.py:25-44)

@@ -84,6 +84,7 @@ __device__ __forceinline__ void load8(const h16* p, float* f) { unpack8(*reinter
 __device__ __forceinline__ void store8(h16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
 
 __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int b = blockIdx.x;
   const GnThread t = gn_thread(p, b);
@@ -238,6 +239,7 @@ __device__ __forceinline__ void gather_resampled(const h16* g, int C, int resamp
 }
 
 __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int b = blockIdx.x;
   const GnThread t = gn_thread(p, b);
@@ -405,7 +407,7 @@ int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s) {
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = smem;
   }
-  gn_fwd_kernel<<<B, gn_threads(C), smem, s>>>(p);
+  launch_k(gn_fwd_kernel, B, gn_threads(C), smem, s, p);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -419,7 +421,7 @@ int launch_gn_bwd(const GnParams& p, int B, cudaStream_t s) {
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = smem;
   }
-  gn_bwd_kernel<<<B, gn_threads(C), smem, s>>>(p);
+  launch_k(gn_bwd_kernel, B, gn_threads(C), smem, s, p);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -435,6 +437,7 @@ template <int CPL>
 __global__ void __launch_bounds__(256) ln_fwd_kernel(const h16* __restrict__ x, const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, float eps, h16* __restrict__ y,
                                                      float* __restrict__ stats, int M, int C, int lpr) {
+  pdl_enter();
   const int nchunks = C >> 3;
   const int rows_per_block = blockDim.x / lpr;
   const int lane_in_row = threadIdx.x % lpr;
@@ -491,6 +494,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const h16* __restrict__ x, 
                                                      const h16* __restrict__ dres, h16* __restrict__ dx,
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                      const float* __restrict__ gscale, int M, int C, int lpr) {
+  pdl_enter();
   extern __shared__ float sm[];  // [2*C] block partial sums of dgamma / dbeta
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
@@ -591,10 +595,10 @@ int launch_ln_fwd(const h16* x, const float* gamma, const float* beta, float eps
   const int rows_per_block = 256 / lpr;
   const int grid = (M + rows_per_block - 1) / rows_per_block;
   switch (cpl) {
-    case 1: ln_fwd_kernel<1><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
-    case 2: ln_fwd_kernel<2><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
-    case 3: ln_fwd_kernel<3><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
-    case 4: ln_fwd_kernel<4><<<grid, 256, 0, s>>>(x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    case 1: launch_k(ln_fwd_kernel<1>, grid, 256, 0, s, x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    case 2: launch_k(ln_fwd_kernel<2>, grid, 256, 0, s, x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    case 3: launch_k(ln_fwd_kernel<3>, grid, 256, 0, s, x, gamma, beta, eps, y, stats, M, C, lpr); break;
+    case 4: launch_k(ln_fwd_kernel<4>, grid, 256, 0, s, x, gamma, beta, eps, y, stats, M, C, lpr); break;
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
   return static_cast<int>(cudaGetLastError());
@@ -610,10 +614,10 @@ int launch_ln_bwd(const h16* x, const float* stats, const float* gamma, const h1
   if (grid > 148 * 4) grid = 148 * 4;
   const size_t smem = 2 * C * sizeof(float);
   switch (cpl) {
-    case 1: ln_bwd_kernel<1><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
-    case 2: ln_bwd_kernel<2><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
-    case 3: ln_bwd_kernel<3><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
-    case 4: ln_bwd_kernel<4><<<grid, 256, smem, s>>>(x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
+    case 1: launch_k(ln_bwd_kernel<1>, grid, 256, smem, s, x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
+    case 2: launch_k(ln_bwd_kernel<2>, grid, 256, smem, s, x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
+    case 3: launch_k(ln_bwd_kernel<3>, grid, 256, smem, s, x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
+    case 4: launch_k(ln_bwd_kernel<4>, grid, 256, smem, s, x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
   return static_cast<int>(cudaGetLastError());

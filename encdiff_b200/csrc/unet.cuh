@@ -102,6 +102,7 @@ struct UNet {
   std::vector<PackEntry> table;     // src pointers resolved at bind()
   std::vector<int> table_src, table_src2;   // parameter index of each entry
   long long pack_total = 0;         // total source elements walked by the pack kernel
+  int pack_blocks = 0;              // blocks of the pack launch
   size_t table_bytes = 0, h16_bytes = 0, f32_bytes = 0;
   // binding
   std::vector<const float*> pptr;
@@ -119,6 +120,11 @@ struct UNet {
   float *z1 = nullptr, *z2 = nullptr, *film = nullptr, *stH = nullptr, *yH = nullptr;
   float* gs = nullptr;       // {scale, 1/scale} of the activation gradients of the current backward (device)
   char* scratch = nullptr;
+  size_t scratch_half = 0;   // the backward alternates between two scratch halves (layer parity)
+  // side stream of the backward: weight-gradient GEMMs run concurrently with the input-gradient chain
+  bool side_on = true;       // ENCDIFF_NO_SIDE_STREAM disables
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_side_done[2] = {nullptr, nullptr};
   // tensor-map caches
   std::map<std::tuple<const void*, int, int, int, int>, CUtensorMap> act_maps;
   std::map<std::tuple<const void*, long long, long long, int>, CUtensorMap> w_maps;
@@ -131,6 +137,20 @@ struct UNet {
   long long fin_total = 0;
   bool fin_dirty = true;      // staging needs zeroing / table needs (re)building: after plan() or bind()
   std::map<std::tuple<const void*, int, int, int>, CUtensorMap> grad_maps;
+  // deferred, grouped weight gradients (wgrad2_group_kernel): the backward only RECORDS its wgrad problems (their operand
+  // pointers are fixed by plan()/bind(), so the table is built once, on the first backward after either) and launches them
+  // all at once at the end; the per-layer activation-gradient scratch is therefore not reused inside one backward
+  bool group_wgrad = true;    // ENCDIFF_NO_WGRAD_GROUP: launch per layer (side stream) instead
+  std::vector<Wgrad2Params> wg_host;
+  std::vector<int> wg_prefix;
+  Wgrad2Params* wg_dev = nullptr;
+  int* wg_prefix_dev = nullptr;
+  int wg_total = 0;
+  std::vector<CrossProjEntry> cp_host;   // deferred cross-attention projection gradients (same life cycle as wg_host)
+  CrossProjEntry* cp_dev = nullptr;
+  int cp_max_C = 0;
+  static constexpr int kWgCap = 640;   // problems per backward (the Shapes3D plan records 273)
+  size_t scratch_total = 0;
   bool force_old_gemm = false;   // parity A/B switch: route every GEMM through the one-tile-per-CTA kernel
 
   h16* pbf() const { return reinterpret_cast<h16*>(packed + table_bytes); }

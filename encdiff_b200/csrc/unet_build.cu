@@ -53,6 +53,8 @@ struct Builder {
     e.col0 = col0;
     e.prefix = u->pack_total;
     u->pack_total += u->params[src].numel;
+    e.blk0 = u->pack_blocks;
+    u->pack_blocks += pack_entry_blocks(e);
     u->table.push_back(e);
     u->table_src.push_back(src);
     u->table_src2.push_back(src2);

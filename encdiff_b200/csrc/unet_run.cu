@@ -60,6 +60,10 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
     stage(u->hc_w, c.out_channels, mc);
     u->fin_dev = reinterpret_cast<WgradFinalizeEntry*>(a.take<char>(u->conv_stage.size() * sizeof(WgradFinalizeEntry)));
     u->fin_dirty = true;
+    u->wg_dev = reinterpret_cast<Wgrad2Params*>(a.take<char>(UNet::kWgCap * sizeof(Wgrad2Params) + 64));
+    u->wg_dev = reinterpret_cast<Wgrad2Params*>((reinterpret_cast<uintptr_t>(u->wg_dev) + 63) & ~uintptr_t(63));
+    u->wg_prefix_dev = reinterpret_cast<int*>(a.take<char>((UNet::kWgCap + 1) * sizeof(int)));
+    u->cp_dev = reinterpret_cast<CrossProjEntry*>(a.take<char>(64 * sizeof(CrossProjEntry)));
     u->gs = a.take<float>(2);
     u->dfilm = a.take<h16>(static_cast<size_t>(B) * u->film_cols);
     u->dyH = a.take<h16>(M0 * 8);
@@ -146,7 +150,17 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
   } else {
     sc = 0;
   }
-  u->ws_bytes_scratch = sc;
+  sc = (sc + 1023) & ~size_t(1023);
+  u->scratch_half = sc;
+  u->ws_bytes_scratch = 2 * sc;      // two halves: the backward alternates per layer (side-stream readers, unet_bwd.inc)
+  if (training && u->group_wgrad) {
+    // deferred wgrads read the activation gradients after the whole chain has run: one slot per layer, never reused
+    size_t tot = 3 * sc;             // head, stem, embedding MLP sections (each <= sc)
+    for (const ResLayer& l : u->res) tot += (res_scratch(l, B) + 1023) & ~size_t(1023);
+    for (const StLayer& l : u->st) tot += (st_scratch(l, B) + 1023) & ~size_t(1023);
+    u->scratch_total = tot;
+    u->ws_bytes_scratch = tot;
+  }
   u->scratch = ws ? ws + u->ws_bytes_persist : nullptr;
   if (ws) {
     u->planB = B;
@@ -180,6 +194,68 @@ struct Exec {
   int B;
   cudaStream_t s;
   int err = 0;
+
+  // ---- side stream (backward only): weight-gradient GEMMs overlap the input-gradient chain ------------------------
+  // Layer k of the backward uses scratch half (k & 1).  A wgrad launched on the side stream reads activation
+  // gradients of its layer's half, so the main stream waits for the side work of layer k-2 before layer k starts
+  // writing that half again; join() folds the side stream back before the finalize kernel / the end of the call.
+  int parity = 1;
+  bool side_layer = false, side_any = false;
+  bool done_valid[2] = {false, false};
+  bool side_ready() {
+    if (!u->side_on || u->prof) return false;      // profiling wants serialised, attributable launches
+    if (!u->side) {
+      if (cudaStreamCreateWithFlags(&u->side, cudaStreamNonBlocking) != cudaSuccess) return false;
+      bool ok = true;
+      for (cudaEvent_t* ev : {&u->ev_fork, &u->ev_join, &u->ev_side_done[0], &u->ev_side_done[1]})
+        ok = ok && cudaEventCreateWithFlags(ev, cudaEventDisableTiming) == cudaSuccess;
+      if (!ok) {
+        u->side_on = false;
+        return false;
+      }
+    }
+    return true;
+  }
+  size_t bump = 0;       // group_wgrad mode: running offset into the never-reused scratch
+  bool recording() const { return u->group_wgrad; }
+  char* begin_layer(size_t bytes) {
+    if (recording()) {
+      char* p = u->scratch + bump;
+      bump += (bytes + 1023) & ~size_t(1023);
+      if (bump > u->scratch_total) invalid("internal: backward scratch overflow");
+      return p;
+    }
+    return begin_layer();
+  }
+  char* begin_layer() {
+    parity ^= 1;
+    side_layer = false;
+    if (done_valid[parity]) {
+      cudaStreamWaitEvent(s, u->ev_side_done[parity], 0);
+      done_valid[parity] = false;
+    }
+    return u->scratch + parity * u->scratch_half;
+  }
+  void end_layer() {
+    if (side_layer) {
+      cudaEventRecord(u->ev_side_done[parity], u->side);
+      done_valid[parity] = true;
+    }
+  }
+  cudaStream_t fork_side() {      // stream for work that only depends on what the main stream has enqueued so far
+    if (!side_ready()) return s;
+    cudaEventRecord(u->ev_fork, s);
+    cudaStreamWaitEvent(u->side, u->ev_fork, 0);
+    side_layer = side_any = true;
+    return u->side;
+  }
+  void join() {
+    if (!side_any) return;
+    cudaEventRecord(u->ev_join, u->side);
+    cudaStreamWaitEvent(s, u->ev_join, 0);
+    side_any = false;
+    done_valid[0] = done_valid[1] = false;
+  }
 
   double next_flops = 0;   // algorithmic FLOPs of the launch about to be reported through fail()
   double next_bytes = 0;   // algorithmic HBM bytes of it (operands read once + result written once)
@@ -393,7 +469,18 @@ struct Exec {
       q.bias1 = bias1;
       q.gscale = u->gs;
       next_flops = 2.0 * B * H * W * static_cast<double>(Cp) * Cq * taps;
-      fail(launch_wgrad2(q, device_sm_count(), s), "wgrad");
+      if (recording()) {
+        if (!u->fin_dirty) return;          // table already built for this plan / binding
+        if (static_cast<int>(u->wg_host.size()) >= UNet::kWgCap) {
+          invalid("internal: wgrad table capacity");
+          return;
+        }
+        u->wg_prefix.push_back(u->wg_total);
+        u->wg_total += wgrad2_prepare_group(&q, 16);
+        u->wg_host.push_back(q);
+        return;
+      }
+      fail(launch_wgrad2(q, device_sm_count(), fork_side()), "wgrad");
       return;
     }
     if (bias0) colsum(dy, static_cast<long long>(B) * H * W, Cdy, p_off, Cp, bias0, bias1);

@@ -10,6 +10,8 @@
 //   Conv3x3 gradients are reduced into a tap-major staging tensor [9][Cp][Cq] (the reference layout [Cp][Cq][3][3] has
 //   no 16-byte contiguous run per tap, which TMA needs); wgrad_finalize_kernel transposes it into the reference layout
 //   once per backward.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "gemm.cuh"
 
@@ -67,7 +69,30 @@ __device__ __forceinline__ WItem w_decode(const Wgrad2Params& p, int item) {
   return w;
 }
 
-__global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ Wgrad2Params p) {
+// Problem sources.  A CTA walks the global item sequence gi = blockIdx.x, blockIdx.x + gridDim.x, ...; at() maps gi to
+// (problem, item inside the problem); `cur` is the caller's cursor into the prefix table (gi only grows).
+struct WSingle {
+  const Wgrad2Params* p;
+  int total;
+  __device__ __forceinline__ const Wgrad2Params& at(int gi, int& cur, int& item) const {
+    item = gi;
+    return *p;
+  }
+};
+struct WGroup {
+  const Wgrad2Params* tab;   // global memory, 64-byte aligned (tensor maps are fetched from here by the TMA unit)
+  const int* prefix;         // [n + 1] first global item of each problem
+  int total;
+  __device__ __forceinline__ const Wgrad2Params& at(int gi, int& cur, int& item) const {
+    while (gi >= __ldg(prefix + cur + 1)) ++cur;
+    item = gi - __ldg(prefix + cur);
+    return tab[cur];
+  }
+};
+
+template <class Src>
+__device__ __forceinline__ void wgrad2_body(const Src& src) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* ones = smem + kWStages * kWStageBytes;      // [128 pix x 64 ch] of 1.0: the shared extra N block
@@ -80,13 +105,8 @@ __global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total = p.q_tiles * p.taps * p.p_tiles * p.splits;
+  const int total = src.total;
 
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.pmap);
-    tma_prefetch_desc(&p.qmap);
-    tma_prefetch_desc(&p.omap);
-  }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kWStages; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -109,13 +129,19 @@ __global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // set-up above touched no global memory; everything below may
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     if (lane == 0) {
       uint32_t it = 0;
-      for (int item = blockIdx.x; item < total; item += gridDim.x) {
+      int cur = 0;
+      for (int gi = blockIdx.x; gi < total; gi += gridDim.x) {
+        int item;
+        const Wgrad2Params& p = src.at(gi, cur, item);
         const WItem w = w_decode(p, item);
+        const TileGeom g = p.g;
+        const int p_col = p.p_off + w.p_tile * 128;
         int dx = 0, dy = 0;
         if (p.taps == 9) {
           dy = w.tap / 3 - 1;
@@ -127,12 +153,12 @@ __global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ 
           const int st = it % kWStages;
           const uint32_t ph = (it / kWStages) & 1;
           int b0, y0;
-          w_tile_origin(p.g, t, b0, y0);
+          w_tile_origin(g, t, b0, y0);
           mbar_wait(&empty_bar[st], ph ^ 1);
           uint8_t* sp = smem + st * kWStageBytes;
           mbar_arrive_expect_tx(&full_bar[st], kWStageBytes);
-          tma_load_4d(sp, &p.pmap, &full_bar[st], p.p_off + w.p_tile * 128, 0, y0, b0);
-          tma_load_4d(sp + kBox, &p.pmap, &full_bar[st], p.p_off + w.p_tile * 128 + 64, 0, y0, b0);
+          tma_load_4d(sp, &p.pmap, &full_bar[st], p_col, 0, y0, b0);
+          tma_load_4d(sp + kBox, &p.pmap, &full_bar[st], p_col + 64, 0, y0, b0);
           tma_load_4d(sp + 2 * kBox, &p.qmap, &full_bar[st], w.q_tile * kWBN, dx, y0 + dy, b0);
         }
       }
@@ -142,7 +168,10 @@ __global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ 
       constexpr uint32_t idesc = make_idesc(kWN, true, true);
       const uint32_t ones_addr = smem_u32(ones);
       uint32_t it = 0, lt = 0;
-      for (int item = blockIdx.x; item < total; item += gridDim.x, ++lt) {
+      int cur = 0;
+      for (int gi = blockIdx.x; gi < total; gi += gridDim.x, ++lt) {
+        int item;
+        const Wgrad2Params& p = src.at(gi, cur, item);
         const WItem w = w_decode(p, item);
         const int t_begin = w.split * p.tiles_per_split;
         const int nsteps = min(p.m_tiles, t_begin + p.tiles_per_split) - t_begin;
@@ -174,9 +203,12 @@ __global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ 
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const bool storer = (warp == 2 && lane == 0);
-    const float ginv = p.gscale ? __ldg(p.gscale + 1) : 1.f;
     uint32_t lt = 0, pc = 0;
-    for (int item = blockIdx.x; item < total; item += gridDim.x, ++lt) {
+    int cur = 0;
+    for (int gi = blockIdx.x; gi < total; gi += gridDim.x, ++lt) {
+      int item;
+      const Wgrad2Params& p = src.at(gi, cur, item);
+      const float ginv = p.gscale ? __ldg(p.gscale + 1) : 1.f;
       const WItem w = w_decode(p, item);
       const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
       const int pch = w.p_tile * 128 + r;     // dY channel of this thread's row
@@ -233,6 +265,15 @@ __global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ 
   if (warp == 2) tmem_dealloc<256>(tmem_base);
 }
 
+__global__ void __launch_bounds__(192, 1) wgrad2_kernel(const __grid_constant__ Wgrad2Params p) {
+  wgrad2_body(WSingle{&p, p.q_tiles * p.taps * p.p_tiles * p.splits});
+}
+// every weight gradient of a backward pass as ONE launch: `tab` holds the problems in the order the backward met them
+__global__ void __launch_bounds__(192, 1) wgrad2_group_kernel(const Wgrad2Params* __restrict__ tab,
+                                                              const int* __restrict__ prefix, int total) {
+  wgrad2_body(WGroup{tab, prefix, total});
+}
+
 int launch_wgrad2(const Wgrad2Params& p0, int num_sms, cudaStream_t stream) {
   constexpr int smem = kWStages * kWStageBytes + kBox + 2 * kFPanel + 1024 + 256;
   static bool configured = false;
@@ -254,7 +295,38 @@ int launch_wgrad2(const Wgrad2Params& p0, int num_sms, cudaStream_t stream) {
   p.splits = (p.m_tiles + p.tiles_per_split - 1) / p.tiles_per_split;
   const int total = base * p.splits;
   const int grid = total < num_sms ? total : num_sms;
-  wgrad2_kernel<<<grid, 192, smem, stream>>>(p);
+  static const bool log = getenv("ENCDIFF_GEMM_LOG") != nullptr;
+  if (log)
+    fprintf(stderr, "GEMMLOG wgrad2 Cp=%d Cq=%d taps=%d m_tiles=%d splits=%d items=%d grid=%d\n", p.Cp, p.Cq, p.taps, p.m_tiles,
+            p.splits, total, grid);
+  launch_k(wgrad2_kernel, grid, 192, smem, stream, p);
+  return static_cast<int>(cudaGetLastError());
+}
+
+static_assert(sizeof(Wgrad2Params) % 64 == 0, "problem tables keep their tensor maps 64-byte aligned");
+
+// Split policy of a grouped problem: items of about `steps` pixel tiles each (the launch as a whole fills the chip, so
+// a problem is split only to bound the cost of one item); returns the item count
+int wgrad2_prepare_group(Wgrad2Params* p, int steps) {
+  p->p_tiles = (p->Cp + 127) / 128;
+  p->q_tiles = (p->Cq + kWBN - 1) / kWBN;
+  int splits = (p->m_tiles + steps - 1) / steps;
+  if (splits < 1) splits = 1;
+  p->tiles_per_split = (p->m_tiles + splits - 1) / splits;
+  p->splits = (p->m_tiles + p->tiles_per_split - 1) / p->tiles_per_split;
+  return p->p_tiles * p->q_tiles * p->taps * p->splits;
+}
+
+int launch_wgrad2_group(const Wgrad2Params* tab_dev, const int* prefix_dev, int total, int num_sms, cudaStream_t stream) {
+  constexpr int smem = kWStages * kWStageBytes + kBox + 2 * kFPanel + 1024 + 256;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad2_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  if (total <= 0) return 0;
+  launch_k(wgrad2_group_kernel, total < num_sms ? total : num_sms, 192, smem, stream, tab_dev, prefix_dev, total);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -262,6 +334,7 @@ int launch_wgrad2(const Wgrad2Params& p0, int num_sms, cudaStream_t stream) {
 // The (p, q) index space of every entry is padded to a multiple of 256, so a block works on 256 consecutive (p, q) of
 // ONE entry: 9 coalesced reads per thread, transpose through shared memory, 2304 contiguous floats written.
 __global__ void __launch_bounds__(256) wgrad_finalize_kernel(const WgradFinalizeEntry* __restrict__ tab, int n_entries) {
+  pdl_enter();
   __shared__ float tile[256 * 9];
   __shared__ int s_entry;
   const long long base = static_cast<long long>(blockIdx.x) * 256;
@@ -292,7 +365,7 @@ __global__ void __launch_bounds__(256) wgrad_finalize_kernel(const WgradFinalize
 }
 int launch_wgrad_finalize(const WgradFinalizeEntry* tab_dev, int n_entries, long long total_padded, cudaStream_t s) {
   if (n_entries <= 0) return 0;
-  wgrad_finalize_kernel<<<static_cast<unsigned>(total_padded / 256), 256, 0, s>>>(tab_dev, n_entries);
+  launch_k(wgrad_finalize_kernel, static_cast<unsigned>(total_padded / 256), 256, 0, s, tab_dev, n_entries);
   return static_cast<int>(cudaGetLastError());
 }
 
