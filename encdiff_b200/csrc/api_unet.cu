@@ -91,6 +91,7 @@ extern "C" int encdiff_unet_bind(encdiff_unet* h, const float* const* params, fl
   u.w_maps.clear();
   u.grad_maps.clear();
   u.fin_dirty = true;
+  u.ckv_dirty = true;
   u.bound = true;
   return EDB_OK;
 }

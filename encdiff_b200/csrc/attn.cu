@@ -342,11 +342,74 @@ __device__ __forceinline__ void project_ctx(const float* __restrict__ ctx_s, con
   }
 }
 
+// Ks/Vs from the per-(layer, sample) projections computed once per forward (cross_kv_project_kernel):
+// kv [T][2C] = K | V of this sample -> Ks/Vs[(h*T + j)*D + d]
+template <int D>
+__device__ __forceinline__ void load_kv(const float* __restrict__ kv, float* Ks, float* Vs, int T, int C) {
+  const int c4n = 2 * C / 4;
+  for (int i = threadIdx.x; i < T * c4n; i += blockDim.x) {
+    const int j = i / c4n, c = (i - j * c4n) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(kv + static_cast<long long>(j) * 2 * C + c);
+    float* dst = c < C ? Ks : Vs;
+    const int cc = c < C ? c : c - C;
+    const int h = cc / D, d = cc - h * D;
+    *reinterpret_cast<float4*>(dst + (h * T + j) * D + d) = v;
+  }
+}
+
+// K | V of every cross-attention layer for every sample in ONE launch (the context is the same for all 16 layers):
+// CTA = (chunk of samples, layer); thread = output channel of [to_k ; to_v] with its weight row in registers.
+__global__ void __launch_bounds__(256) cross_kv_project_kernel(const CrossKvEntry* __restrict__ tab,
+                                                               const float* __restrict__ ctx, int B, int T, int Dc,
+                                                               int chunk) {
+  pdl_enter();
+  __shared__ float ctx_s[kMaxT * kMaxDc];
+  const CrossKvEntry en = tab[blockIdx.y];
+  const int C = en.C;
+  constexpr int kRows = 4;     // 2C <= 4 * 256
+  float w[kRows][kMaxDc];
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) {
+    const int row = threadIdx.x + r * 256;
+    const float* src = row < C ? en.wk + row * Dc : en.wv + (row - C) * Dc;
+#pragma unroll
+    for (int e = 0; e < kMaxDc; ++e) w[r][e] = (row < 2 * C && e < Dc) ? __ldg(src + e) : 0.f;
+  }
+  const int b_end = min(B, (static_cast<int>(blockIdx.x) + 1) * chunk);
+  for (int b = blockIdx.x * chunk; b < b_end; ++b) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
+    __syncthreads();
+    float* dst = en.kv + static_cast<long long>(b) * T * 2 * C;
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      const int row = threadIdx.x + r * 256;
+      if (row < 2 * C) {
+        for (int j = 0; j < T; ++j) {
+          float a = 0.f;
+#pragma unroll
+          for (int e = 0; e < kMaxDc; ++e)
+            if (e < Dc) a += ctx_s[j * Dc + e] * w[r][e];
+          dst[j * 2 * C + row] = a;
+        }
+      }
+    }
+  }
+}
+
+int launch_cross_kv_project(const CrossKvEntry* tab_dev, int n_layers, const float* ctx, int B, int T, int Dc, cudaStream_t s) {
+  if (n_layers <= 0) return 0;
+  if (T > kMaxT || Dc > kMaxDc) return static_cast<int>(cudaErrorInvalidValue);
+  const int chunk = 8;
+  launch_k(cross_kv_project_kernel, dim3((B + chunk - 1) / chunk, n_layers), 256, 0, s, tab_dev, ctx, B, T, Dc, chunk);
+  return static_cast<int>(cudaGetLastError());
+}
+
 template <int D>
 __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restrict__ q, const float* __restrict__ ctx,
                                                              const float* __restrict__ wk, const float* __restrict__ wv,
                                                              h16* __restrict__ out, int N, int heads, int T, int Dc,
-                                                             int TQ, float scale_log2) {
+                                                             int TQ, float scale_log2, const float* __restrict__ kv) {
   pdl_enter();
   extern __shared__ float sm[];
   const int C = heads * D;
@@ -354,9 +417,13 @@ __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restri
   float* Vs = Ks + T * C;
   float* ctx_s = Vs + T * C;
   const int b = blockIdx.y, t0 = blockIdx.x * TQ;
-  for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
-  __syncthreads();
-  project_ctx<D>(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
+  if (kv) {
+    load_kv<D>(kv + static_cast<long long>(b) * T * 2 * C, Ks, Vs, T, C);
+  } else {
+    for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
+    __syncthreads();
+    project_ctx<D>(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
+  }
   __syncthreads();
   constexpr int DC = D / 8;
   for (int it = threadIdx.x; it < heads * TQ; it += blockDim.x) {
@@ -425,7 +492,7 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const h16* __restri
                                                              const float* __restrict__ wk, const float* __restrict__ wv,
                                                              const h16* __restrict__ dout, h16* __restrict__ dq,
                                                              float* __restrict__ dkv, int N, int heads, int T, int Dc,
-                                                             int TQ, float scale) {
+                                                             int TQ, float scale, const float* __restrict__ kv) {
   pdl_enter();
   extern __shared__ float sm[];
   const int C = heads * D;
@@ -439,9 +506,13 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const h16* __restri
   float* dOs = qs + C * TQP;             // [C][TQP]
   const int b = blockIdx.y, t0 = blockIdx.x * TQ;
   const float scale_log2 = scale * kLog2e;
-  for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
-  __syncthreads();
-  project_ctx<D>(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
+  if (kv) {
+    load_kv<D>(kv + static_cast<long long>(b) * T * 2 * C, Ks, Vs, T, C);
+  } else {
+    for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
+    __syncthreads();
+    project_ctx<D>(ctx_s, wk, wv, Ks, Vs, T, C, Dc);
+  }
   __syncthreads();
   constexpr int DC = D / 8;
   for (int it = threadIdx.x; it < heads * TQ; it += blockDim.x) {
@@ -718,7 +789,7 @@ static int cross_tq(int N) { return N < 32 ? N : 32; }
 
 template <int D>
 static int cross_fwd_t(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
-                       int heads, int T, int Dc, cudaStream_t st) {
+                       int heads, int T, int Dc, cudaStream_t st, const float* kv) {
   const int C = heads * D, TQ = cross_tq(N);
   const size_t smem = (2ull * T * C + T * Dc) * sizeof(float);
   static size_t configured = 48 * 1024;
@@ -730,13 +801,13 @@ static int cross_fwd_t(const h16* q, const float* ctx, const float* wk, const fl
   const int threads = heads * TQ >= 256 ? 256 : ((heads * TQ + 31) / 32) * 32;
   dim3 grid((N + TQ - 1) / TQ, B);
   launch_k(cross_attn_fwd_kernel<D>, grid, threads < 64 ? 64 : threads, smem, st, q, ctx, wk, wv, out, N, heads, T, Dc, TQ,
-                                                                            rsqrtf(static_cast<float>(D)) * kLog2e);
+           rsqrtf(static_cast<float>(D)) * kLog2e, kv);
   return static_cast<int>(cudaGetLastError());
 }
 
 template <int D>
 static int cross_bwd_t(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
-                       float* dkv, int B, int N, int heads, int T, int Dc, cudaStream_t st) {
+                       float* dkv, int B, int N, int heads, int T, int Dc, cudaStream_t st, const float* kv) {
   const int C = heads * D, TQ = cross_tq(N);
   const size_t smem = (2ull * T * C + T * Dc + 2ull * heads * T * (TQ + 4) + 2ull * C * (TQ + 4)) * sizeof(float);
   static size_t configured = 48 * 1024;
@@ -748,18 +819,18 @@ static int cross_bwd_t(const h16* q, const float* ctx, const float* wk, const fl
   const int threads = heads * TQ >= 256 ? 256 : ((heads * TQ + 31) / 32) * 32;
   dim3 grid((N + TQ - 1) / TQ, B);
   launch_k(cross_attn_bwd_kernel<D>, grid, threads < 64 ? 64 : threads, smem, st, q, ctx, wk, wv, dout, dq, dkv, N, heads, T, Dc,
-                                                                            TQ, rsqrtf(static_cast<float>(D)));
+           TQ, rsqrtf(static_cast<float>(D)), kv);
   return static_cast<int>(cudaGetLastError());
 }
 
 int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
-                          int heads, int D, int T, int Dc, cudaStream_t s) {
+                          int heads, int D, int T, int Dc, cudaStream_t s, const float* kv) {
   if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc) return static_cast<int>(cudaErrorInvalidValue);
   switch (D) {
-    case 8: return cross_fwd_t<8>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s);
-    case 16: return cross_fwd_t<16>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s);
-    case 32: return cross_fwd_t<32>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s);
-    case 64: return cross_fwd_t<64>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s);
+    case 8: return cross_fwd_t<8>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s, kv);
+    case 16: return cross_fwd_t<16>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s, kv);
+    case 32: return cross_fwd_t<32>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s, kv);
+    case 64: return cross_fwd_t<64>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s, kv);
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
 }
@@ -770,17 +841,17 @@ size_t cross_attn_bwd_scratch_bytes(int B, int heads, int D, int T) {
 
 int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
                           float* dwk, float* dwv, float* dctx, const float* gscale, float* dkv_scratch, int B, int N,
-                          int heads, int D, int T, int Dc, cudaStream_t s, bool defer_proj) {
+                          int heads, int D, int T, int Dc, cudaStream_t s, bool defer_proj, const float* kv) {
   if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc || 2 * heads * D > 4 * 256) return static_cast<int>(cudaErrorInvalidValue);
   const int C = heads * D;
   cudaError_t e = cudaMemsetAsync(dkv_scratch, 0, cross_attn_bwd_scratch_bytes(B, heads, D, T), s);
   if (e != cudaSuccess) return static_cast<int>(e);
   int rc;
   switch (D) {
-    case 8: rc = cross_bwd_t<8>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
-    case 16: rc = cross_bwd_t<16>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
-    case 32: rc = cross_bwd_t<32>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
-    case 64: rc = cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s); break;
+    case 8: rc = cross_bwd_t<8>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
+    case 16: rc = cross_bwd_t<16>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
+    case 32: rc = cross_bwd_t<32>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
+    case 64: rc = cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
   if (rc || defer_proj) return rc;

@@ -56,11 +56,21 @@ int launch_self_attn_bwd(const h16* qkv, const h16* out, const h16* dout, const 
 
 // Cross-attention against T concept tokens of width Dc (attention.py:170-193 with context; openaimodel_enc.py:729).
 // q [B*N, C] h16, ctx [B, T, Dc] fp32, wk/wv [C, Dc] fp32 (reference to_k/to_v weights), out [B*N, C].
+// kv (optional): K | V [B, T, 2C] fp32 already projected by launch_cross_kv_project (then ctx / wk / wv are not read)
 int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
-                          int heads, int D, int T, int Dc, cudaStream_t s);
+                          int heads, int D, int T, int Dc, cudaStream_t s, const float* kv = nullptr);
+struct CrossKvEntry {
+  const float* wk;       // [C, Dc] reference to_k / to_v weights
+  const float* wv;
+  float* kv;             // [B, T, 2C]
+  int C;
+  int pad;
+};
+int launch_cross_kv_project(const CrossKvEntry* tab_dev, int n_layers, const float* ctx, int B, int T, int Dc, cudaStream_t s);
 int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const float* wv, const h16* dout, h16* dq,
                           float* dwk, float* dwv, float* dctx, const float* gscale, float* dkv_scratch, int B, int N,
-                          int heads, int D, int T, int Dc, cudaStream_t s, bool defer_proj = false);
+                          int heads, int D, int T, int Dc, cudaStream_t s, bool defer_proj = false,
+                          const float* kv = nullptr);
 // deferred form of the projection half (d to_k, d to_v, d context) for all layers at once: dkv of every layer must still
 // be alive; dctx is accumulated with atomics (caller zeroes it)
 struct CrossProjEntry {

@@ -101,13 +101,25 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
     if (active) {
-      for (int pix = t.prow; pix < t.HW; pix += t.rp) {
-        float f[8];
-        load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+      // 4 independent 16-byte loads in flight per thread (the trip count is a run-time value: no compiler unrolling)
+      for (int pix0 = t.prow; pix0 < t.HW; pix0 += 4 * t.rp) {
+        uint4 raw[4];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          s[k] += f[k];
-          q[k] += f[k] * f[k];
+        for (int u = 0; u < 4; ++u) {
+          const int pix = pix0 + u * t.rp;
+          if (pix < t.HW) raw[u] = *reinterpret_cast<const uint4*>(t.src + static_cast<long long>(pix) * t.ld + t.cofs);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (pix0 + u * t.rp < t.HW) {
+            float f[8];
+            unpack8(raw[u], f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              s[k] += f[k];
+              q[k] += f[k] * f[k];
+            }
+          }
         }
       }
     }
@@ -155,15 +167,27 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
   const int W = p.W, H = p.H;
   if (p.resample == RESAMPLE_NONE) {
     h16* dst = p.act + static_cast<long long>(b) * t.HW * C + t.c0;
-    for (int pix = t.prow; pix < t.HW; pix += t.rp) {
-      float f[8];
-      load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+    for (int pix0 = t.prow; pix0 < t.HW; pix0 += 4 * t.rp) {
+      uint4 raw[4];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        float y = a[k] * f[k] + bb[k];
-        f[k] = p.silu ? silu_f(y) : y;
+      for (int u = 0; u < 4; ++u) {
+        const int pix = pix0 + u * t.rp;
+        if (pix < t.HW) raw[u] = *reinterpret_cast<const uint4*>(t.src + static_cast<long long>(pix) * t.ld + t.cofs);
       }
-      store8(dst + static_cast<long long>(pix) * C, f);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int pix = pix0 + u * t.rp;
+        if (pix < t.HW) {
+          float f[8];
+          unpack8(raw[u], f);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            float y = a[k] * f[k] + bb[k];
+            f[k] = p.silu ? silu_f(y) : y;
+          }
+          store8(dst + static_cast<long long>(pix) * C, f);
+        }
+      }
     }
   } else if (p.resample == RESAMPLE_DOWN) {
     const int Wo = W / 2, HWo = (H / 2) * Wo;
@@ -288,16 +312,45 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     float s1[8], s2[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
-    for (int pix = t.prow; pix < t.HW; pix += t.rp) {
-      const int y = pix / W, x = pix - y * W;
-      float f[8], d[8];
-      load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
-      gather_resampled(dact, C, p.resample, y, x, W, d);
+    if (p.resample == RESAMPLE_NONE) {
+      // 4 x (x, dact) loads in flight per thread
+      for (int pix0 = t.prow; pix0 < t.HW; pix0 += 4 * t.rp) {
+        uint4 rx[4], rd[4];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float dyp = p.silu ? d[k] * silu_grad_f(a[k] * f[k] + bb[k]) : d[k];
-        s1[k] += dyp;
-        s2[k] += dyp * (f[k] - mu[k]) * rs[k];
+        for (int u = 0; u < 4; ++u) {
+          const int pix = pix0 + u * t.rp;
+          if (pix < t.HW) {
+            rx[u] = *reinterpret_cast<const uint4*>(t.src + static_cast<long long>(pix) * t.ld + t.cofs);
+            rd[u] = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(pix) * C);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (pix0 + u * t.rp < t.HW) {
+            float f[8], d[8];
+            unpack8(rx[u], f);
+            unpack8(rd[u], d);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const float dyp = p.silu ? d[k] * silu_grad_f(a[k] * f[k] + bb[k]) : d[k];
+              s1[k] += dyp;
+              s2[k] += dyp * (f[k] - mu[k]) * rs[k];
+            }
+          }
+        }
+      }
+    } else {
+      for (int pix = t.prow; pix < t.HW; pix += t.rp) {
+        const int y = pix / W, x = pix - y * W;
+        float f[8], d[8];
+        load8(t.src + static_cast<long long>(pix) * t.ld + t.cofs, f);
+        gather_resampled(dact, C, p.resample, y, x, W, d);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float dyp = p.silu ? d[k] * silu_grad_f(a[k] * f[k] + bb[k]) : d[k];
+          s1[k] += dyp;
+          s2[k] += dyp * (f[k] - mu[k]) * rs[k];
+        }
       }
     }
     gn_channel_reduce(t, t.prow < t.rp, s1, s2, part, S1, S2);
@@ -354,6 +407,51 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     acc = p.acc1;
   }
   const h16* dxs = p.dxs ? p.dxs + static_cast<long long>(b) * HWo * C + t.c0 : nullptr;
+  if (p.resample == RESAMPLE_NONE) {
+    // 2 pixels per step: up to 8 independent 16-byte loads in flight (x, dact, dxs, previous dx)
+    for (int pix0 = t.prow; pix0 < t.HW; pix0 += 2 * t.rp) {
+      uint4 rx[2], rd[2], re[2], ra[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int pix = pix0 + u * t.rp;
+        if (pix < t.HW) {
+          rx[u] = *reinterpret_cast<const uint4*>(t.src + static_cast<long long>(pix) * t.ld + t.cofs);
+          rd[u] = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(pix) * C);
+          if (dxs) re[u] = *reinterpret_cast<const uint4*>(dxs + static_cast<long long>(pix) * C);
+          if (acc) ra[u] = *reinterpret_cast<const uint4*>(dxp + static_cast<long long>(pix) * t.ld);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int pix = pix0 + u * t.rp;
+        if (pix < t.HW) {
+          float f[8], d[8], o[8];
+          unpack8(rx[u], f);
+          unpack8(rd[u], d);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float dyp = p.silu ? d[k] * silu_grad_f(a[k] * f[k] + bb[k]) : d[k];
+            const float xh = (f[k] - mu[k]) * rs[k];
+            o[k] = k1[k] * dyp - k2[k] - xh * k3[k];
+          }
+          if (dxs) {
+            float e[8];
+            unpack8(re[u], e);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] += e[k];
+          }
+          if (acc) {
+            float e[8];
+            unpack8(ra[u], e);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] += e[k];
+          }
+          store8(dxp + static_cast<long long>(pix) * t.ld, o);
+        }
+      }
+    }
+    return;
+  }
   for (int pix = t.prow; pix < t.HW; pix += t.rp) {
     const int y = pix / W, x = pix - y * W;
     float f[8], d[8], o[8];
@@ -489,7 +587,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const h16* __restrict__ x, 
 }
 
 template <int CPL>
-__global__ void __launch_bounds__(256) ln_bwd_kernel(const h16* __restrict__ x, const float* __restrict__ stats,
+__global__ void __launch_bounds__(256, CPL == 1 ? 4 : 1) ln_bwd_kernel(const h16* __restrict__ x, const float* __restrict__ stats,
                                                      const float* __restrict__ gamma, const h16* __restrict__ dy,
                                                      const h16* __restrict__ dres, h16* __restrict__ dx,
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -506,6 +604,14 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const h16* __restrict__ x, 
   for (int j = 0; j < CPL; ++j)
 #pragma unroll
     for (int k = 0; k < 8; ++k) ag[j][k] = ab[j][k] = 0.f;
+  // this thread's channels are the same for every row: gamma lives in registers
+  float gam[CPL][8];
+#pragma unroll
+  for (int j = 0; j < CPL; ++j) {
+    const int ch = lane_in_row + j * lpr;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) gam[j][k] = ch < nchunks ? __ldg(gamma + ch * 8 + k) : 0.f;
+  }
   for (long long row0 = static_cast<long long>(blockIdx.x) * rows_per_block; row0 < M;
        row0 += static_cast<long long>(gridDim.x) * rows_per_block) {
     const long long row = row0 + threadIdx.x / lpr;
@@ -513,23 +619,35 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const h16* __restrict__ x, 
     float xh[CPL][8], g[CPL][8];
     float s1 = 0.f, s2 = 0.f;
     float mean = 0.f, rstd = 0.f;
+    // every global load of the row is issued before the first use (x, dy, the residual-branch gradient, the statistics)
+    uint4 rx[CPL], rdy[CPL], rres[CPL];
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      const int ch = lane_in_row + j * lpr;
+      if (ok && ch < nchunks) {
+        rx[j] = *reinterpret_cast<const uint4*>(x + row * C + ch * 8);
+        rdy[j] = *reinterpret_cast<const uint4*>(dy + row * C + ch * 8);
+        if (dres) rres[j] = *reinterpret_cast<const uint4*>(dres + row * C + ch * 8);
+      }
+    }
     if (ok) {
-      mean = stats[row * 2];
-      rstd = stats[row * 2 + 1];
+      const float2 st = *reinterpret_cast<const float2*>(stats + row * 2);
+      mean = st.x;
+      rstd = st.y;
     }
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
       const int ch = lane_in_row + j * lpr;
       if (ok && ch < nchunks) {
         float xv[8], dv[8];
-        unpack8(*reinterpret_cast<const uint4*>(x + row * C + ch * 8), xv);
-        unpack8(*reinterpret_cast<const uint4*>(dy + row * C + ch * 8), dv);
+        unpack8(rx[j], xv);
+        unpack8(rdy[j], dv);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           xh[j][k] = (xv[k] - mean) * rstd;
           ag[j][k] += dv[k] * xh[j][k];
           ab[j][k] += dv[k];
-          g[j][k] = dv[k] * __ldg(gamma + ch * 8 + k);
+          g[j][k] = dv[k] * gam[j][k];
           s1 += g[j][k];
           s2 += g[j][k] * xh[j][k];
         }
@@ -550,7 +668,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const h16* __restrict__ x, 
           for (int k = 0; k < 8; ++k) o[k] = rstd * (g[j][k] - s1 - xh[j][k] * s2);
           if (dres) {
             float r[8];
-            unpack8(*reinterpret_cast<const uint4*>(dres + row * C + ch * 8), r);
+            unpack8(rres[j], r);
 #pragma unroll
             for (int k = 0; k < 8; ++k) o[k] += r[k];
           }

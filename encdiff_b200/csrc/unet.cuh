@@ -64,6 +64,7 @@ struct StLayer {
   h16 *n = nullptr, *t0 = nullptr, *l1 = nullptr, *qkv = nullptr, *att = nullptr, *t1 = nullptr, *l2 = nullptr,
        *q2 = nullptr, *att2 = nullptr, *t2 = nullptr, *l3 = nullptr, *g = nullptr, *gg = nullptr, *t3 = nullptr;
   float *stn = nullptr, *ls1 = nullptr, *ls2 = nullptr, *ls3 = nullptr, *lse = nullptr;
+  float* kv = nullptr;    // [B, T, 2C] to_k | to_v of the context, projected once per forward for all layers
 };
 
 struct Layer {
@@ -146,6 +147,9 @@ struct UNet {
   Wgrad2Params* wg_dev = nullptr;
   int* wg_prefix_dev = nullptr;
   int wg_total = 0;
+  std::vector<CrossKvEntry> ckv_host;    // K | V projection table (built on the first forward after plan() / bind())
+  CrossKvEntry* ckv_dev = nullptr;
+  bool ckv_dirty = true;
   std::vector<CrossProjEntry> cp_host;   // deferred cross-attention projection gradients (same life cycle as wg_host)
   CrossProjEntry* cp_dev = nullptr;
   int cp_max_C = 0;

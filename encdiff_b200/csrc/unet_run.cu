@@ -49,6 +49,8 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
   u->stH = a.take<float>(static_cast<size_t>(B) * 64);
   u->yH = a.take<float>(M0 * c.out_channels);
   u->conv_stage.clear();
+  u->ckv_dev = reinterpret_cast<CrossKvEntry*>(a.take<char>(64 * sizeof(CrossKvEntry)));
+  u->ckv_dirty = true;
   if (training) {
     auto stage = [&](int param, long long Cp, long long Cq) {
       u->conv_stage.push_back(UNet::ConvStage{param, Cp, Cq, a.take<float>(static_cast<size_t>(9 * Cp * Cq))});
@@ -125,6 +127,7 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
         l.g = a.take<h16>(m * 8 * C);
         l.gg = a.take<h16>(m * 4 * C);
         l.t3 = a.take<h16>(m * C);
+        l.kv = a.take<float>(static_cast<size_t>(B) * c.latent_unit * 2 * C);
         l.y = new_tn(C, l.H);
         h = l.y;
       }
@@ -614,7 +617,7 @@ static void st_forward(StLayer& l, const float* ctx, Exec& e) {
   e.fail(launch_ln_fwd(l.t1, e.P(l.ln2_w), e.P(l.ln2_b), 1e-5f, l.l2, l.ls2, M, C, e.s), "ln2");
   e.gemm({{l.l2, C, 1}}, H, W, l.q2f, 0, C, 1, nullptr, nullptr, 0, ACT_NONE, false, l.q2, C);
   e.fail(launch_cross_attn_fwd(l.q2, ctx, e.P(l.k2_w), e.P(l.v2_w), l.att2, e.B, N, l.heads, l.D, c.latent_unit,
-                               c.context_dim, e.s),
+                               c.context_dim, e.s, l.kv),
          "cross_attn");
   e.gemm({{l.att2, C, 1}}, H, W, l.o2f, 0, C, 1, e.P(l.o2_b), l.t1, C, ACT_NONE, false, l.t2, C);
   // GEGLU feed-forward
@@ -641,6 +644,20 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
   e.fail(launch_silu_fwd(u->z2, u->a2e, static_cast<long long>(B) * E, s), "silu");
   e.gemm({{u->a2e, E, 1}}, 1, 1, u->filmf, 0, u->film_cols, 1, u->pf32() + u->film_bias_off, nullptr, 0, ACT_NONE, true,
          u->film, u->film_cols);
+  // to_k / to_v of the context for all cross-attention layers at once (attention.py:174-176; one launch, not 16 x 8)
+  EDB_REQUIRE(u->st.size() <= 64, "forward: more than 64 SpatialTransformer layers");
+  if (!u->st.empty()) {
+    if (u->ckv_dirty) {      // first forward after plan() / bind(): always an eager call (warm-up before any capture)
+      u->ckv_host.clear();
+      for (const StLayer& l : u->st) u->ckv_host.push_back(CrossKvEntry{e.P(l.k2_w), e.P(l.v2_w), l.kv, l.C, 0});
+      EDB_CHECK_CUDA(cudaMemcpyAsync(u->ckv_dev, u->ckv_host.data(), u->ckv_host.size() * sizeof(CrossKvEntry),
+                                     cudaMemcpyHostToDevice, s));
+      EDB_CHECK_CUDA(cudaStreamSynchronize(s));
+      u->ckv_dirty = false;
+    }
+    e.fail(launch_cross_kv_project(u->ckv_dev, static_cast<int>(u->st.size()), ctx, B, c.latent_unit, c.context_dim, s),
+           "cross_attn.kv");
+  }
   // stem conv as one K=64 GEMM over the im2col'd 3-channel input (q_sample fused when noise != null)
   e.fail(launch_stem_im2col(x, noise, sa, sb, xt, u->cols, B, c.in_channels, S, S, s), "stem");
   e.gemm({{u->cols, 64, 1}}, S, S, u->stemf, 0, mc, 1, e.P(u->stem_b), nullptr, 0, ACT_NONE, false, u->tn[0].p, mc);
