@@ -31,12 +31,14 @@ PROTOTYPES = {
     "encdiff_op_self_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "encdiff_op_self_attention_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                               c_int, c_void_p]),
-    "encdiff_op_cross_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
-                                           c_int, c_int, c_int, c_void_p]),
+    "encdiff_op_cross_kv_project": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                            c_void_p]),
+    "encdiff_op_cross_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                           c_int, c_int, c_int, c_int, c_void_p]),
     "encdiff_op_cross_attention_bwd_scratch_bytes": (c_ll, [c_int, c_int, c_int, c_int]),
     "encdiff_op_cross_attention_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                                               c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
-                                               c_int, c_void_p]),
+                                               c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                               c_int, c_int, c_void_p]),
     "encdiff_op_geglu": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p]),
     "encdiff_unet_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
     "encdiff_unet_destroy": (c_int, [c_void_p]),

@@ -78,8 +78,13 @@ def _attention_tokens(attn, x2d, B, n_tok, context, res=None):
         q = _linear(x2d, B, n_tok, attn.to_q.weight)
         o = torch.empty(B * n_tok, inner, dtype=x2d.dtype, device=dev)
         wk, wv = _f32(attn.to_k.weight), _f32(attn.to_v.weight)
+        kv = torch.empty(B, ctx.shape[1], 2 * inner, dtype=torch.float32, device=dev)
+        tab = torch.empty(64, dtype=torch.uint8, device=dev)
+        _lib.check(lib.encdiff_op_cross_kv_project(ctx.data_ptr(), wk.data_ptr(), wv.data_ptr(), kv.data_ptr(),
+                                                   tab.data_ptr(), B, inner, ctx.shape[1], ctx.shape[2],
+                                                   _lib.current_stream()), "op_cross_kv_project")
         _lib.check(lib.encdiff_op_cross_attention(q.data_ptr(), ctx.data_ptr(), wk.data_ptr(), wv.data_ptr(),
-                                                  o.data_ptr(), B, n_tok, heads, D, ctx.shape[1], ctx.shape[2],
+                                                  kv.data_ptr(), o.data_ptr(), B, n_tok, heads, D, ctx.shape[1], ctx.shape[2],
                                                   _lib.current_stream()), "op_cross_attention")
     return _linear(o, B, n_tok, attn.to_out[0].weight, attn.to_out[0].bias, res=res)
 

@@ -158,11 +158,25 @@ extern "C" int encdiff_op_self_attention_bwd(const void* qkv, const void* out, c
   return EDB_OK;
 }
 
-extern "C" int encdiff_op_cross_attention(const void* q, const float* ctx, const float* wk, const float* wv, void* out,
-                                          int B, int N, int heads, int D, int T, int Dc, void* stream) {
+extern "C" int encdiff_op_cross_kv_project(const float* ctx, const float* wk, const float* wv, float* kv,
+                                           void* table_scratch, int B, int C, int T, int Dc, void* stream) {
+  EDB_REQUIRE(ctx && wk && wv && kv && table_scratch, "cross_kv_project: null argument");
+  EDB_REQUIRE(2 * C <= 1024, "cross_kv_project: heads * d_head must be <= 512");
+  const CrossKvEntry en{wk, wv, kv, C, 0};
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  EDB_CHECK_CUDA(cudaMemcpyAsync(table_scratch, &en, sizeof(en), cudaMemcpyHostToDevice, s));
+  EDB_CHECK_CUDA(cudaStreamSynchronize(s));      // `en` lives on this stack frame
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_cross_kv_project(static_cast<const CrossKvEntry*>(table_scratch), 1, ctx, B, T,
+                                                                  Dc, s)));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_op_cross_attention(const void* q, const float* ctx, const float* wk, const float* wv,
+                                          const float* kv, void* out, int B, int N, int heads, int D, int T, int Dc,
+                                          void* stream) {
   EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_cross_attn_fwd(static_cast<const h16*>(q), ctx, wk, wv,
                                                                 static_cast<h16*>(out), B, N, heads, D, T, Dc,
-                                                                static_cast<cudaStream_t>(stream))));
+                                                                static_cast<cudaStream_t>(stream), kv)));
   return EDB_OK;
 }
 
@@ -171,14 +185,15 @@ extern "C" long long encdiff_op_cross_attention_bwd_scratch_bytes(int B, int hea
 }
 
 extern "C" int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, const float* wk, const float* wv,
-                                              const void* dout, void* dq, float* dwk, float* dwv, float* dctx,
+                                              const float* kv, const void* dout, void* dq, float* dwk, float* dwv,
+                                              float* dctx,
                                               float* scratch, int B, int N, int heads, int D, int T, int Dc,
                                               void* stream) {
   EDB_REQUIRE(scratch != nullptr, "cross_attention_bwd: scratch of encdiff_op_cross_attention_bwd_scratch_bytes() needed");
   EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_cross_attn_bwd(static_cast<const h16*>(q), ctx, wk, wv,
                                                                 static_cast<const h16*>(dout), static_cast<h16*>(dq), dwk,
                                                                 dwv, dctx, nullptr, scratch, B, N, heads, D, T, Dc,
-                                                                static_cast<cudaStream_t>(stream))));
+                                                                static_cast<cudaStream_t>(stream), false, kv)));
   return EDB_OK;
 }
 

@@ -363,7 +363,7 @@ __global__ void __launch_bounds__(256) cross_kv_project_kernel(const CrossKvEntr
                                                                const float* __restrict__ ctx, int B, int T, int Dc,
                                                                int chunk) {
   pdl_enter();
-  __shared__ float ctx_s[kMaxT * kMaxDc];
+  __shared__ __align__(16) float ctx_s[kMaxT * kMaxDc];
   const CrossKvEntry en = tab[blockIdx.y];
   const int C = en.C;
   constexpr int kRows = 4;     // 2C <= 4 * 256
@@ -385,12 +385,24 @@ __global__ void __launch_bounds__(256) cross_kv_project_kernel(const CrossKvEntr
     for (int r = 0; r < kRows; ++r) {
       const int row = threadIdx.x + r * 256;
       if (row < 2 * C) {
-        for (int j = 0; j < T; ++j) {
-          float a = 0.f;
+        if (Dc == kMaxDc) {
+          for (int j = 0; j < T; ++j) {     // the context row as four broadcast 16-byte reads
+            float a = 0.f;
 #pragma unroll
-          for (int e = 0; e < kMaxDc; ++e)
-            if (e < Dc) a += ctx_s[j * Dc + e] * w[r][e];
-          dst[j * 2 * C + row] = a;
+            for (int e4 = 0; e4 < kMaxDc / 4; ++e4) {
+              const float4 x = *reinterpret_cast<const float4*>(ctx_s + j * kMaxDc + 4 * e4);
+              a += x.x * w[r][4 * e4] + x.y * w[r][4 * e4 + 1] + x.z * w[r][4 * e4 + 2] + x.w * w[r][4 * e4 + 3];
+            }
+            dst[j * 2 * C + row] = a;
+          }
+        } else {
+          for (int j = 0; j < T; ++j) {
+            float a = 0.f;
+#pragma unroll
+            for (int e = 0; e < kMaxDc; ++e)
+              if (e < Dc) a += ctx_s[j * Dc + e] * w[r][e];
+            dst[j * 2 * C + row] = a;
+          }
         }
       }
     }
@@ -826,6 +838,11 @@ static int cross_bwd_t(const h16* q, const float* ctx, const float* wk, const fl
 int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const float* wv, h16* out, int B, int N,
                           int heads, int D, int T, int Dc, cudaStream_t s, const float* kv) {
   if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc) return static_cast<int>(cudaErrorInvalidValue);
+  static const bool cuda_core_only = getenv("ENCDIFF_ATTN_CUDA_CORE") != nullptr;
+  if (kv && !cuda_core_only) {
+    const int rc = launch_cross_attn_fwd_mma(q, kv, out, B, N, heads, D, T, s);
+    if (rc != -1) return rc;
+  }
   switch (D) {
     case 8: return cross_fwd_t<8>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s, kv);
     case 16: return cross_fwd_t<16>(q, ctx, wk, wv, out, B, N, heads, T, Dc, s, kv);
@@ -844,15 +861,20 @@ int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const
                           int heads, int D, int T, int Dc, cudaStream_t s, bool defer_proj, const float* kv) {
   if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc || 2 * heads * D > 4 * 256) return static_cast<int>(cudaErrorInvalidValue);
   const int C = heads * D;
-  cudaError_t e = cudaMemsetAsync(dkv_scratch, 0, cross_attn_bwd_scratch_bytes(B, heads, D, T), s);
+  static const bool cuda_core_only = getenv("ENCDIFF_ATTN_CUDA_CORE") != nullptr;
+  int rc = -1;
+  if (kv && !cuda_core_only) rc = launch_cross_attn_bwd_mma(q, kv, dout, dq, dkv_scratch, B, N, heads, D, T, s);
+  cudaError_t e = cudaSuccess;
+  if (rc == -1) {
+  e = cudaMemsetAsync(dkv_scratch, 0, cross_attn_bwd_scratch_bytes(B, heads, D, T), s);
   if (e != cudaSuccess) return static_cast<int>(e);
-  int rc;
   switch (D) {
     case 8: rc = cross_bwd_t<8>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
     case 16: rc = cross_bwd_t<16>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
     case 32: rc = cross_bwd_t<32>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
     case 64: rc = cross_bwd_t<64>(q, ctx, wk, wv, dout, dq, dkv_scratch, B, N, heads, T, Dc, s, kv); break;
     default: return static_cast<int>(cudaErrorInvalidValue);
+  }
   }
   if (rc || defer_proj) return rc;
   const size_t smem = (2ull * C * Dc + 2ull * T * C + T * Dc) * sizeof(float);

@@ -443,4 +443,430 @@ int launch_self_attn_bwd_mma(const h16* qkv, const h16* out, const h16* dout, co
   }
 }
 
+
+// ===============================================================================================================
+// Cross-attention against T <= 32 concept tokens on the same fragment path (attention.py:170-193 with a context).
+// K | V come already projected (fp32 [B, T, 2C], launch_cross_kv_project); they are converted to h16 and padded to
+// NK = 32 keys in shared memory, padded keys are masked out of the softmax.  A warp owns 16 queries and sees the whole
+// score row (32 keys = four m16n8 tiles) in registers, so softmax is single pass and needs no log-sum-exp tensor.
+// CTA = (sample, G heads), warp = (head slot, 16-query tile), as in the self-attention kernels.
+// ===============================================================================================================
+static constexpr int kNK = 32;          // padded key count
+static constexpr int kNKP = kNK + 8;    // pitch of the transposed [D][keys] arrays
+
+template <int D>
+__device__ __forceinline__ void stage_kv(const float* __restrict__ kvb, int T, int C, int hg, int G, h16* Ks, h16* Vs,
+                                         h16* Kt, h16* Vt) {
+  // kvb: this sample's [T][2C];  Ks/Vs [G][kNK][D] row-major, Kt/Vt [G][D][kNKP] (any of them may be null).
+  // The G heads of the CTA are G*D contiguous floats per key: float4 loads, 4 in flight per thread, then scatter.
+  const int w4 = G * D / 4;                    // float4 per key and matrix
+  const int total = kNK * w4;
+  for (int i0 = threadIdx.x; i0 < total; i0 += 4 * blockDim.x) {
+    float4 kq[4], vq[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * blockDim.x;
+      kq[u] = vq[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < total) {
+        const int j = i / w4, c4 = i - j * w4;
+        if (j < T) {
+          const float* p = kvb + static_cast<long long>(j) * 2 * C + hg * G * D + c4 * 4;
+          kq[u] = *reinterpret_cast<const float4*>(p);
+          vq[u] = *reinterpret_cast<const float4*>(p + C);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * blockDim.x;
+      if (i < total) {
+        const int j = i / w4, c = (i - j * w4) * 4;
+        const int slot = c / D, d = c - slot * D;
+        const float kf[4] = {kq[u].x, kq[u].y, kq[u].z, kq[u].w};
+        const float vf[4] = {vq[u].x, vq[u].y, vq[u].z, vq[u].w};
+        if (Ks) {
+          *reinterpret_cast<h162*>(Ks + (slot * kNK + j) * D + d) = f22h2(kf[0], kf[1]);
+          *reinterpret_cast<h162*>(Ks + (slot * kNK + j) * D + d + 2) = f22h2(kf[2], kf[3]);
+        }
+        if (Vs) {
+          *reinterpret_cast<h162*>(Vs + (slot * kNK + j) * D + d) = f22h2(vf[0], vf[1]);
+          *reinterpret_cast<h162*>(Vs + (slot * kNK + j) * D + d + 2) = f22h2(vf[2], vf[3]);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (Kt) Kt[(slot * D + d + k) * kNKP + j] = f2h(kf[k]);
+          if (Vt) Vt[(slot * D + d + k) * kNKP + j] = f2h(vf[k]);
+        }
+      }
+    }
+  }
+}
+
+template <int D>
+__global__ void __launch_bounds__(512) cross_attn_fwd_mma_kernel(const h16* __restrict__ q, const float* __restrict__ kv,
+                                                                 h16* __restrict__ out, int N, int heads, int G, int T,
+                                                                 float scale_log2) {
+  pdl_enter();
+  extern __shared__ __align__(16) uint8_t smraw[];
+  const int NT = (N + 15) & ~15;             // query rows padded to whole 16-row tiles (zero rows, never stored)
+  h16* Qs = reinterpret_cast<h16*>(smraw);   // [G][NT][D]
+  h16* Ks = Qs + G * NT * D;                 // [G][kNK][D]
+  h16* Vt = Ks + G * kNK * D;                // [G][D][kNKP]
+  const int C = heads * D;
+  const int groups = heads / G;
+  const int b = blockIdx.x / groups, hg = blockIdx.x - b * groups;
+  constexpr int DC = D / 8;
+  for (int idx = threadIdx.x; idx < G * NT * DC; idx += blockDim.x) {
+    const int slot = idx / (NT * DC);
+    const int rem = idx - slot * NT * DC;
+    const int j = rem / DC, dc = rem - j * DC;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (j < N) v = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * N + j) * C + (hg * G + slot) * D + dc * 8);
+    *reinterpret_cast<uint4*>(Qs + (slot * NT + j) * D + dc * 8) = v;
+  }
+  stage_kv<D>(kv + static_cast<long long>(b) * T * 2 * C, T, C, hg, G, Ks, nullptr, nullptr, Vt);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int qtiles = NT >> 4;
+  const int slot = warp / qtiles, q0 = (warp - slot * qtiles) << 4;
+  if (slot >= G) return;
+  const int h = hg * G + slot;
+  const h16* Kh = Ks + slot * kNK * D;
+  const h16* Vh = Vt + slot * D * kNKP;
+  AFrag<D> qa;
+  qa.load(Qs + slot * NT * D, q0, g, t);
+  float s[4][4];
+  float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) {
+    s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+    mma_rowsT<D>(s[nt], qa, Kh, nt * 8, g, t);
+    const int key = nt * 8 + 2 * t;
+    if (key >= T) s[nt][0] = s[nt][2] = -INFINITY;
+    if (key + 1 >= T) s[nt][1] = s[nt][3] = -INFINITY;
+    m0 = fmaxf(m0, fmaxf(s[nt][0], s[nt][1]));
+    m1 = fmaxf(m1, fmaxf(s[nt][2], s[nt][3]));
+  }
+  m0 = quad_max(m0) * scale_log2;
+  m1 = quad_max(m1) * scale_log2;
+  float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) {
+    s[nt][0] = exp2f(s[nt][0] * scale_log2 - m0);
+    s[nt][1] = exp2f(s[nt][1] * scale_log2 - m0);
+    s[nt][2] = exp2f(s[nt][2] * scale_log2 - m1);
+    s[nt][3] = exp2f(s[nt][3] * scale_log2 - m1);
+    l0 += s[nt][0] + s[nt][1];
+    l1 += s[nt][2] + s[nt][3];
+  }
+  const float i0 = 1.f / quad_sum(l0), i1 = 1.f / quad_sum(l1);
+  float o[DC][4];
+#pragma unroll
+  for (int nt = 0; nt < DC; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+#pragma unroll
+  for (int kc = 0; kc < 2; ++kc) {
+    uint32_t pa[4] = {pack2(s[2 * kc][0], s[2 * kc][1]), pack2(s[2 * kc][2], s[2 * kc][3]),
+                      pack2(s[2 * kc + 1][0], s[2 * kc + 1][1]), pack2(s[2 * kc + 1][2], s[2 * kc + 1][3])};
+#pragma unroll
+    for (int nt = 0; nt < DC; ++nt) mma_T(o[nt], pa, Vh, kNKP, nt * 8, kc * 16, g, t);
+  }
+  const long long row0 = static_cast<long long>(b) * N + q0 + g;
+#pragma unroll
+  for (int nt = 0; nt < DC; ++nt) {
+    if (q0 + g < N)
+      *reinterpret_cast<uint32_t*>(out + row0 * C + h * D + nt * 8 + 2 * t) = pack2(o[nt][0] * i0, o[nt][1] * i0);
+    if (q0 + g + 8 < N)
+      *reinterpret_cast<uint32_t*>(out + (row0 + 8) * C + h * D + nt * 8 + 2 * t) = pack2(o[nt][2] * i1, o[nt][3] * i1);
+  }
+}
+
+// backward: dq [B*N, C] h16 and dkv [B, T, 2C] fp32 (dK | dV, complete sums: the CTA sees every query of its heads, so
+// no atomics in global memory and no zero-fill).  dO is normalised by a per-CTA power of two as in the self-attention
+// backward; dq carries the caller's gradient scale, dkv likewise (the projection kernel applies 1/gscale).
+template <int D>
+__global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __restrict__ q, const float* __restrict__ kv,
+                                                                 const h16* __restrict__ dout, h16* __restrict__ dq,
+                                                                 float* __restrict__ dkv, int N, int heads, int G, int T,
+                                                                 float scale) {
+  pdl_enter();
+  extern __shared__ __align__(16) uint8_t smraw[];
+  const int NT = (N + 15) & ~15;             // query rows padded to whole tiles: zero rows contribute nothing
+  const int NP = NT + 8;
+  h16* Qs = reinterpret_cast<h16*>(smraw);   // [G][NT][D]
+  h16* Os = Qs + G * NT * D;                 // f * dO
+  h16* Qt = Os + G * NT * D;                 // [G][D][NP]
+  h16* Ot = Qt + G * D * NP;
+  h16* Ks = Ot + G * D * NP;                 // [G][kNK][D]
+  h16* Vs = Ks + G * kNK * D;
+  h16* Kt = Vs + G * kNK * D;                // [G][D][kNKP]
+  float* acc = reinterpret_cast<float*>(Kt + G * D * kNKP);   // [warps][kNK][2D] per-warp dK | dV partial sums
+  float* qst = acc + (blockDim.x >> 5) * kNK * 2 * D;         // [warps][16][3] row max, 1/l, delta
+  __shared__ float s_red[16];
+  __shared__ float s_f;
+  const int C = heads * D;
+  const int groups = heads / G;
+  const int b = blockIdx.x / groups, hg = blockIdx.x - b * groups;
+  constexpr int DC = D / 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float amax = 0.f;
+  for (int idx = threadIdx.x; idx < G * N * DC; idx += blockDim.x) {
+    const int slot = idx / (N * DC);
+    const int rem = idx - slot * N * DC;
+    const int j = rem / DC, dc = rem - j * DC;
+    float f[8];
+    unpack8(*reinterpret_cast<const uint4*>(dout + (static_cast<long long>(b) * N + j) * C + (hg * G + slot) * D + dc * 8), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(f[k]));
+  }
+  amax = warp_max(amax);
+  if (lane == 0) s_red[warp] = amax;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float m = 0.f;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmaxf(m, s_red[w]);
+    float fsc = 1.f;
+    if (m > 0.f && isfinite(m)) {
+      int e;
+      frexpf(m, &e);
+      fsc = ldexpf(1.f, -e);
+    }
+    s_f = fsc;
+  }
+  __syncthreads();
+  const float fsc = s_f, finv = 1.f / s_f;
+  for (int idx = threadIdx.x; idx < G * NT * DC; idx += blockDim.x) {
+    const int slot = idx / (NT * DC);
+    const int rem = idx - slot * NT * DC;
+    const int j = rem / DC, dc = rem - j * DC;
+    const long long goff = (static_cast<long long>(b) * N + j) * C + (hg * G + slot) * D + dc * 8;
+    uint4 q4 = make_uint4(0u, 0u, 0u, 0u), o4 = q4;
+    if (j < N) {
+      q4 = *reinterpret_cast<const uint4*>(q + goff);
+      float d8[8];
+      unpack8(*reinterpret_cast<const uint4*>(dout + goff), d8);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) d8[k] *= fsc;
+      o4 = pack8(d8);
+    }
+    const int o = (slot * NT + j) * D + dc * 8;
+    *reinterpret_cast<uint4*>(Qs + o) = q4;
+    *reinterpret_cast<uint4*>(Os + o) = o4;
+    const h16* qe = reinterpret_cast<const h16*>(&q4);
+    const h16* oe = reinterpret_cast<const h16*>(&o4);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int tt = (slot * D + dc * 8 + k) * NP + j;
+      Qt[tt] = qe[k];
+      Ot[tt] = oe[k];
+    }
+  }
+  stage_kv<D>(kv + static_cast<long long>(b) * T * 2 * C, T, C, hg, G, Ks, Vs, Kt, nullptr);
+  __syncthreads();
+  const int g = lane >> 2, t = lane & 3;
+  const int qtiles = NT >> 4;
+  const int slot = warp / qtiles, q0 = (warp - slot * qtiles) << 4;
+  if (slot < G) {
+    const int h = hg * G + slot;
+    const h16* Qh = Qs + slot * NT * D;
+    const h16* Oh = Os + slot * NT * D;
+    const h16* Qth = Qt + slot * D * NP;
+    const h16* Oth = Ot + slot * D * NP;
+    const h16* Kh = Ks + slot * kNK * D;
+    const h16* Vh = Vs + slot * kNK * D;
+    const h16* Kth = Kt + slot * D * kNKP;
+    float* st = qst + warp * 48;
+    const float scale_log2 = scale * kLog2eM;
+    {  // ---- dQ for queries q0 .. q0+15 (rows g and g+8 of the tile) ----
+      AFrag<D> qa, oa;
+      qa.load(Qh, q0, g, t);
+      oa.load(Oh, q0, g, t);
+      float s[4][4], dp[4][4];
+      float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
+        mma_rowsT<D>(s[nt], qa, Kh, nt * 8, g, t);
+        mma_rowsT<D>(dp[nt], oa, Vh, nt * 8, g, t);
+        const int key = nt * 8 + 2 * t;
+        if (key >= T) s[nt][0] = s[nt][2] = -INFINITY;
+        if (key + 1 >= T) s[nt][1] = s[nt][3] = -INFINITY;
+        m0 = fmaxf(m0, fmaxf(s[nt][0], s[nt][1]));
+        m1 = fmaxf(m1, fmaxf(s[nt][2], s[nt][3]));
+      }
+      m0 = quad_max(m0) * scale_log2;
+      m1 = quad_max(m1) * scale_log2;
+      float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        s[nt][0] = exp2f(s[nt][0] * scale_log2 - m0);
+        s[nt][1] = exp2f(s[nt][1] * scale_log2 - m0);
+        s[nt][2] = exp2f(s[nt][2] * scale_log2 - m1);
+        s[nt][3] = exp2f(s[nt][3] * scale_log2 - m1);
+        l0 += s[nt][0] + s[nt][1];
+        l1 += s[nt][2] + s[nt][3];
+      }
+      const float i0 = 1.f / quad_sum(l0), i1 = 1.f / quad_sum(l1);
+      float de0 = 0.f, de1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        s[nt][0] *= i0;
+        s[nt][1] *= i0;
+        s[nt][2] *= i1;
+        s[nt][3] *= i1;
+        de0 += s[nt][0] * dp[nt][0] + s[nt][1] * dp[nt][1];
+        de1 += s[nt][2] * dp[nt][2] + s[nt][3] * dp[nt][3];
+      }
+      de0 = quad_sum(de0);
+      de1 = quad_sum(de1);
+      if (t == 0) {
+        st[g * 3] = m0;
+        st[g * 3 + 1] = i0;
+        st[g * 3 + 2] = de0;
+        st[(g + 8) * 3] = m1;
+        st[(g + 8) * 3 + 1] = i1;
+        st[(g + 8) * 3 + 2] = de1;
+      }
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        s[nt][0] *= (dp[nt][0] - de0) * scale;
+        s[nt][1] *= (dp[nt][1] - de0) * scale;
+        s[nt][2] *= (dp[nt][2] - de1) * scale;
+        s[nt][3] *= (dp[nt][3] - de1) * scale;
+      }
+      float dqa[DC][4];
+#pragma unroll
+      for (int nt = 0; nt < DC; ++nt) dqa[nt][0] = dqa[nt][1] = dqa[nt][2] = dqa[nt][3] = 0.f;
+#pragma unroll
+      for (int kc = 0; kc < 2; ++kc) {
+        uint32_t da[4] = {pack2(s[2 * kc][0], s[2 * kc][1]), pack2(s[2 * kc][2], s[2 * kc][3]),
+                          pack2(s[2 * kc + 1][0], s[2 * kc + 1][1]), pack2(s[2 * kc + 1][2], s[2 * kc + 1][3])};
+#pragma unroll
+        for (int nt = 0; nt < DC; ++nt) mma_T(dqa[nt], da, Kth, kNKP, nt * 8, kc * 16, g, t);
+      }
+      const long long grow = static_cast<long long>(b) * N + q0 + g;
+#pragma unroll
+      for (int nt = 0; nt < DC; ++nt) {
+        if (q0 + g < N)
+          *reinterpret_cast<uint32_t*>(dq + grow * C + h * D + nt * 8 + 2 * t) = pack2(dqa[nt][0] * finv, dqa[nt][1] * finv);
+        if (q0 + g + 8 < N)
+          *reinterpret_cast<uint32_t*>(dq + (grow + 8) * C + h * D + nt * 8 + 2 * t) = pack2(dqa[nt][2] * finv, dqa[nt][3] * finv);
+      }
+    }
+    __syncwarp();
+    // ---- this warp's 16 queries' contribution to dK, dV: transposed roles (keys are the MMA rows) ----
+    float* accs = acc + warp * kNK * 2 * D;     // written by this warp only: plain stores, summed over the head's warps below
+#pragma unroll 1
+    for (int kt = 0; kt < kNK; kt += 16) {
+      AFrag<D> ka, va;
+      ka.load(Kh, kt, g, t);
+      va.load(Vh, kt, g, t);
+      float pt[2][4], ds[2][4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        float dpt[4] = {0.f, 0.f, 0.f, 0.f};
+        pt[i][0] = pt[i][1] = pt[i][2] = pt[i][3] = 0.f;
+        mma_rowsT<D>(pt[i], ka, Qh, q0 + 8 * i, g, t);      // S^T[key kt+g / +8][query q0 + 8i + 2t / +1]
+        mma_rowsT<D>(dpt, va, Oh, q0 + 8 * i, g, t);
+        const float* sa = st + (8 * i + 2 * t) * 3;
+        const float ma = sa[0], ia = sa[1], dea = sa[2], mb = sa[3], ib = sa[4], deb = sa[5];
+        const bool k0ok = kt + g < T, k1ok = kt + g + 8 < T;
+        pt[i][0] = k0ok ? exp2f(pt[i][0] * scale_log2 - ma) * ia : 0.f;
+        pt[i][1] = k0ok ? exp2f(pt[i][1] * scale_log2 - mb) * ib : 0.f;
+        pt[i][2] = k1ok ? exp2f(pt[i][2] * scale_log2 - ma) * ia : 0.f;
+        pt[i][3] = k1ok ? exp2f(pt[i][3] * scale_log2 - mb) * ib : 0.f;
+        ds[i][0] = pt[i][0] * (dpt[0] - dea) * scale;
+        ds[i][1] = pt[i][1] * (dpt[1] - deb) * scale;
+        ds[i][2] = pt[i][2] * (dpt[2] - dea) * scale;
+        ds[i][3] = pt[i][3] * (dpt[3] - deb) * scale;
+      }
+      uint32_t pa[4] = {pack2(pt[0][0], pt[0][1]), pack2(pt[0][2], pt[0][3]), pack2(pt[1][0], pt[1][1]), pack2(pt[1][2], pt[1][3])};
+      uint32_t da[4] = {pack2(ds[0][0], ds[0][1]), pack2(ds[0][2], ds[0][3]), pack2(ds[1][0], ds[1][1]), pack2(ds[1][2], ds[1][3])};
+#pragma unroll
+      for (int nt = 0; nt < DC; ++nt) {
+        float dv[4] = {0.f, 0.f, 0.f, 0.f}, dk[4] = {0.f, 0.f, 0.f, 0.f};
+        mma_T(dv, pa, Oth, NP, nt * 8, q0, g, t);
+        mma_T(dk, da, Qth, NP, nt * 8, q0, g, t);
+        float* r0 = accs + (kt + g) * 2 * D + nt * 8 + 2 * t;
+        float* r1 = r0 + 8 * 2 * D;
+        *reinterpret_cast<float2*>(r0) = make_float2(dk[0], dk[1]);
+        *reinterpret_cast<float2*>(r1) = make_float2(dk[2], dk[3]);
+        *reinterpret_cast<float2*>(r0 + D) = make_float2(dv[0], dv[1]);
+        *reinterpret_cast<float2*>(r1 + D) = make_float2(dv[2], dv[3]);
+      }
+    }
+  }
+  __syncthreads();
+  float* dst = dkv + static_cast<long long>(b) * T * 2 * C;
+  for (int idx = threadIdx.x; idx < G * T * 2 * D; idx += blockDim.x) {
+    const int sl = idx / (T * 2 * D);
+    const int rem = idx - sl * T * 2 * D;
+    const int j = rem / (2 * D), c = rem - j * 2 * D;
+    const int hh = hg * G + sl;
+    float v = 0.f;
+    for (int w = 0; w < qtiles; ++w) v += acc[((sl * qtiles + w) * kNK + j) * 2 * D + c];
+    v *= finv;
+    if (c < D) dst[static_cast<long long>(j) * 2 * C + hh * D + c] = v;
+    else dst[static_cast<long long>(j) * 2 * C + C + hh * D + (c - D)] = v;
+  }
+}
+
+template <int D>
+static int cross_fwd_mma_t(const h16* q, const float* kv, h16* out, int B, int N, int heads, int T, cudaStream_t st) {
+  const int NT = (N + 15) & ~15;
+  const int G = mma_group(NT, heads);
+  const size_t smem = static_cast<size_t>(G) * (NT * D + kNK * D + D * kNKP) * sizeof(h16);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(cross_attn_fwd_mma_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = smem;
+  }
+  const int threads = G * (NT / 16) * 32;
+  launch_k(cross_attn_fwd_mma_kernel<D>, B * (heads / G), threads, smem, st, q, kv, out, N, heads, G, T,
+           rsqrtf(static_cast<float>(D)) * kLog2eM);
+  return static_cast<int>(cudaGetLastError());
+}
+
+template <int D>
+static int cross_bwd_mma_t(const h16* q, const float* kv, const h16* dout, h16* dq, float* dkv, int B, int N, int heads,
+                           int T, cudaStream_t st) {
+  const int NT = (N + 15) & ~15;
+  const int G = mma_group(NT, heads);
+  const int warps = G * (NT / 16);
+  const size_t smem = static_cast<size_t>(G) * (2 * NT * D + 2 * D * (NT + 8) + 2 * kNK * D + D * kNKP) * sizeof(h16) +
+                      (static_cast<size_t>(warps) * kNK * 2 * D + warps * 48) * sizeof(float);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(cross_attn_bwd_mma_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = smem;
+  }
+  launch_k(cross_attn_bwd_mma_kernel<D>, B * (heads / G), warps * 32, smem, st, q, kv, dout, dq, dkv, N, heads, G, T,
+           rsqrtf(static_cast<float>(D)));
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_cross_attn_fwd_mma(const h16* q, const float* kv, h16* out, int B, int N, int heads, int D, int T, cudaStream_t s) {
+  if (!kv || N < 1 || N > 256 || T < 1 || T > kNK) return -1;
+  switch (D) {
+    case 8: return cross_fwd_mma_t<8>(q, kv, out, B, N, heads, T, s);
+    case 16: return cross_fwd_mma_t<16>(q, kv, out, B, N, heads, T, s);
+    case 32: return cross_fwd_mma_t<32>(q, kv, out, B, N, heads, T, s);
+    default: return -1;
+  }
+}
+
+int launch_cross_attn_bwd_mma(const h16* q, const float* kv, const h16* dout, h16* dq, float* dkv, int B, int N, int heads,
+                              int D, int T, cudaStream_t s) {
+  if (!kv || N < 1 || N > 256 || T < 1 || T > kNK) return -1;
+  switch (D) {
+    case 8: return cross_bwd_mma_t<8>(q, kv, dout, dq, dkv, B, N, heads, T, s);
+    case 16: return cross_bwd_mma_t<16>(q, kv, dout, dq, dkv, B, N, heads, T, s);
+    case 32: return cross_bwd_mma_t<32>(q, kv, dout, dq, dkv, B, N, heads, T, s);
+    default: return -1;
+  }
+}
+
 }  // namespace edb

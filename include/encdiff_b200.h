@@ -72,12 +72,16 @@ int encdiff_op_self_attention_bwd(const void* qkv, const void* out, const void* 
 /* CrossAttention.forward with a context of T concept tokens of width Dc, INCLUDING to_k / to_v (attention.py:174-190):
  *   q h16 [B*N, heads*D], ctx fp32 [B, T, Dc], wk / wv fp32 [heads*D, Dc] (reference weight layout), out h16.
  * Backward: dq h16, dwk / dwv / dctx fp32 (accumulated: caller zeroes), scratch fp32 of ..._scratch_bytes().     */
-int encdiff_op_cross_attention(const void* q, const float* ctx, const float* wk, const float* wv, void* out, int B,
-                               int N, int heads, int D, int T, int Dc, void* stream);
+/* kv (optional, may be NULL): K | V [B, T, 2*heads*D] fp32 produced by encdiff_op_cross_kv_project (what the UNet does
+ * once per forward for all its layers); with it the tensor-core path runs and ctx / wk / wv are not read by the forward. */
+int encdiff_op_cross_kv_project(const float* ctx, const float* wk, const float* wv, float* kv, void* table_scratch /*>=64 B*/,
+                                int B, int C, int T, int Dc, void* stream);
+int encdiff_op_cross_attention(const void* q, const float* ctx, const float* wk, const float* wv, const float* kv, void* out,
+                               int B, int N, int heads, int D, int T, int Dc, void* stream);
 long long encdiff_op_cross_attention_bwd_scratch_bytes(int B, int heads, int D, int T);
-int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, const float* wk, const float* wv, const void* dout,
-                                   void* dq, float* dwk, float* dwv, float* dctx, float* scratch, int B, int N,
-                                   int heads, int D, int T, int Dc, void* stream);
+int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, const float* wk, const float* wv, const float* kv,
+                                   const void* dout, void* dq, float* dwk, float* dwv, float* dctx, float* scratch, int B,
+                                   int N, int heads, int D, int T, int Dc, void* stream);
 /* GEGLU (attention.py:37-45): g h16 [M, 2*inner] (value | gate) -> out h16 [M, inner] = value * gelu_erf(gate)  */
 int encdiff_op_geglu(const void* g, void* out, long long M, int inner, void* stream);
 

@@ -63,8 +63,9 @@ def test_self_attention_fwd_bwd(cuda_device, N, D):
         assert rel_err(got, ref) <= 2 * tol16(), name
 
 
+@pytest.mark.parametrize("use_kv", [False, True])       # True: pre-projected K | V -> the tensor-core kernels
 @pytest.mark.parametrize("N,D", [(256, 8), (64, 16), (16, 32), (4, 32)])
-def test_cross_attention_fwd_bwd(cuda_device, N, D):
+def test_cross_attention_fwd_bwd(cuda_device, N, D, use_kv):
     _lib, lib, dt = lib_and_dtype()
     B, heads, T, Dc = 5, 8, 20, 16
     C = heads * D
@@ -81,13 +82,22 @@ def test_cross_attention_fwd_bwd(cuda_device, N, D):
     qd, dd = q16.to(dev).contiguous(), dout.to(dev).contiguous()
     cd, wkd, wvd = ctx.detach().to(dev), wk.detach().to(dev), wv.detach().to(dev)
     out = torch.empty(B, N, C, dtype=dt, device=dev)
-    _lib.check(lib.encdiff_op_cross_attention(qd.data_ptr(), cd.data_ptr(), wkd.data_ptr(), wvd.data_ptr(),
+    kv_ptr = 0
+    if use_kv:
+        kv = torch.empty(B, T, 2 * C, dtype=torch.float32, device=dev)
+        tab = torch.empty(64, dtype=torch.uint8, device=dev)
+        _lib.check(lib.encdiff_op_cross_kv_project(cd.data_ptr(), wkd.data_ptr(), wvd.data_ptr(), kv.data_ptr(),
+                                                   tab.data_ptr(), B, C, T, Dc, _lib.current_stream()))
+        want_kv = torch.cat([ctx.detach() @ wk.detach().t(), ctx.detach() @ wv.detach().t()], -1)
+        assert rel_err(kv, want_kv) <= 1e-5
+        kv_ptr = kv.data_ptr()
+    _lib.check(lib.encdiff_op_cross_attention(qd.data_ptr(), cd.data_ptr(), wkd.data_ptr(), wvd.data_ptr(), kv_ptr,
                                               out.data_ptr(), B, N, heads, D, T, Dc, _lib.current_stream()))
     dq = torch.zeros_like(qd)
     dwk, dwv, dctx = torch.zeros_like(wkd), torch.zeros_like(wvd), torch.zeros_like(cd)
     scratch = torch.empty(lib.encdiff_op_cross_attention_bwd_scratch_bytes(B, heads, D, T) // 4, dtype=torch.float32,
                           device=dev)
-    _lib.check(lib.encdiff_op_cross_attention_bwd(qd.data_ptr(), cd.data_ptr(), wkd.data_ptr(), wvd.data_ptr(),
+    _lib.check(lib.encdiff_op_cross_attention_bwd(qd.data_ptr(), cd.data_ptr(), wkd.data_ptr(), wvd.data_ptr(), kv_ptr,
                                                   dd.data_ptr(), dq.data_ptr(), dwk.data_ptr(), dwv.data_ptr(),
                                                   dctx.data_ptr(), scratch.data_ptr(), B, N, heads, D, T, Dc,
                                                   _lib.current_stream()))
