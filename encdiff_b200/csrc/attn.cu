@@ -712,70 +712,110 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_proj_kernel(const float* _
   }
 }
 
-// All layers' projections in ONE launch (the backward keeps every layer's dK|dV when the weight gradients are deferred):
-// CTA = (chunk of `chunk` samples, layer).  dctx is accumulated with atomics (16 layers add into the same rows); the
-// weight gradient is summed over the CTA's samples in registers first.
+// All layers' projection gradients in ONE launch (the backward keeps every layer's dK | dV).  With R = B*T rows the
+// buffers are plain matrices: dkv [R, 2C], ctx [R, Dc], dctx [R, Dc], and the two products are small GEMMs
+//   dctx[R, Dc]  += dkv[R, 2C] . [wk ; wv][2C, Dc]          dW[2C, Dc] += dkv^T[2C, R] . ctx[R, Dc]
+// run on the TF32 warp MMA (m16n8k8, fp32 accumulate; fp32 operands rounded to tf32).  CTA = (160-row chunk, layer);
+// A fragments come straight from global memory (every element is used by exactly two MMAs), the small B operands
+// ([wk ; wv] and the chunk's context rows) sit in shared memory with a 24-float pitch (conflict-free fragment reads).
+// dctx and dW are accumulated with fp32 atomics (16 layers / 32 chunks add into the same addresses).
+static constexpr int kPRows = 160;      // rows of dkv per CTA (10 m-tiles)
+static constexpr int kPPitch = 24;
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mma_tf32(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
 __global__ void __launch_bounds__(256) cross_attn_bwd_proj_group_kernel(const CrossProjEntry* __restrict__ tab,
                                                                         const float* __restrict__ ctx,
                                                                         float* __restrict__ dctx,
-                                                                        const float* __restrict__ gscale, int B, int T,
-                                                                        int Dc, int chunk) {
+                                                                        const float* __restrict__ gscale, int R) {
   pdl_enter();
   extern __shared__ float sm[];
   const CrossProjEntry en = tab[blockIdx.y];
-  const int C = en.C;
-  float* w_s = sm;                    // [2C][Dc]
-  float* g_s = w_s + 2 * C * Dc;      // [T][2C]
-  float* ctx_s = g_s + T * 2 * C;     // [T][Dc]
+  const int C2 = 2 * en.C;
+  float* w_s = sm;                          // [2C][kPPitch]: wk rows then wv rows, 16 context dims each
+  float* c_s = w_s + C2 * kPPitch;          // [kPRows][kPPitch] context rows of this chunk
   const float ginv = gscale ? gscale[1] : 1.f;
-  for (int i = threadIdx.x; i < C * Dc; i += blockDim.x) {
-    w_s[i] = en.wk[i];
-    w_s[C * Dc + i] = en.wv[i];
+  const int r0 = blockIdx.x * kPRows;
+  for (int i = threadIdx.x; i < C2 * 4; i += blockDim.x) {
+    const int row = i >> 2, q4 = (i & 3) * 4;
+    const float* src = row < en.C ? en.wk + row * 16 : en.wv + (row - en.C) * 16;
+    *reinterpret_cast<float4*>(w_s + row * kPPitch + q4) = *reinterpret_cast<const float4*>(src + q4);
   }
-  constexpr int kRows = 4;
-  float acc[kRows][kMaxDc];
-#pragma unroll
-  for (int r = 0; r < kRows; ++r)
-#pragma unroll
-    for (int e = 0; e < kMaxDc; ++e) acc[r][e] = 0.f;
-  const int b_end = min(B, (static_cast<int>(blockIdx.x) + 1) * chunk);
-  for (int b = blockIdx.x * chunk; b < b_end; ++b) {
-    __syncthreads();
-    const float4* src = reinterpret_cast<const float4*>(en.dkv + static_cast<long long>(b) * T * 2 * C);
-    for (int i = threadIdx.x; i < T * 2 * C / 4; i += blockDim.x) reinterpret_cast<float4*>(g_s)[i] = src[i];
-    for (int i = threadIdx.x; i < T * Dc; i += blockDim.x) ctx_s[i] = ctx[static_cast<long long>(b) * T * Dc + i];
-    __syncthreads();
-    // dctx[b][j][e]: 2C-long dot products, 8 lanes per output (T * Dc * 8 work items over the CTA)
-    for (int o = threadIdx.x >> 3; o < T * Dc; o += blockDim.x >> 3) {
-      const int j = o / Dc, e = o - j * Dc, l8 = threadIdx.x & 7;
-      float a = 0.f;
-      for (int c = l8; c < 2 * C; c += 8) a += g_s[j * 2 * C + c] * w_s[c * Dc + e];
-      a += __shfl_xor_sync(0xffffffffu, a, 1);
-      a += __shfl_xor_sync(0xffffffffu, a, 2);
-      a += __shfl_xor_sync(0xffffffffu, a, 4);
-      if (l8 == 0) atomicAdd(dctx + static_cast<long long>(b) * T * Dc + o, a * ginv);
+  for (int i = threadIdx.x; i < kPRows * 4; i += blockDim.x) {
+    const int row = i >> 2, q4 = (i & 3) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r0 + row < R) v = *reinterpret_cast<const float4*>(ctx + static_cast<long long>(r0 + row) * 16 + q4);
+    *reinterpret_cast<float4*>(c_s + row * kPPitch + q4) = v;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const float* dk = en.dkv;
+  // ---- dctx[r0 + m][e] += sum_c dkv[r0 + m][c] * W[c][e] ----
+  for (int mt = warp; mt < kPRows / 16; mt += 8) {
+    const int ra = r0 + mt * 16 + g, rb = ra + 8;
+    const float* pa = dk + static_cast<long long>(ra) * C2;
+    const float* pb = dk + static_cast<long long>(rb) * C2;
+    const bool oka = ra < R, okb = rb < R;
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 4
+    for (int k0 = 0; k0 < C2; k0 += 8) {
+      uint32_t a[4];
+      a[0] = to_tf32(oka ? pa[k0 + t] : 0.f);
+      a[1] = to_tf32(okb ? pb[k0 + t] : 0.f);
+      a[2] = to_tf32(oka ? pa[k0 + t + 4] : 0.f);
+      a[3] = to_tf32(okb ? pb[k0 + t + 4] : 0.f);
+      const float* wb = w_s + (k0 + t) * kPPitch + g;
+      mma_tf32(acc[0], a, to_tf32(wb[0]), to_tf32(wb[4 * kPPitch]));
+      mma_tf32(acc[1], a, to_tf32(wb[8]), to_tf32(wb[4 * kPPitch + 8]));
     }
 #pragma unroll
-    for (int r = 0; r < kRows; ++r) {
-      const int row = threadIdx.x + r * 256;
-      if (row < 2 * C) {
-        for (int j = 0; j < T; ++j) {
-          const float g = g_s[j * 2 * C + row];
-#pragma unroll
-          for (int e = 0; e < kMaxDc; ++e)
-            if (e < Dc) acc[r][e] += g * ctx_s[j * Dc + e];
-        }
+    for (int nt = 0; nt < 2; ++nt) {
+      if (oka) {
+        atomicAdd(dctx + static_cast<long long>(ra) * 16 + nt * 8 + 2 * t, acc[nt][0] * ginv);
+        atomicAdd(dctx + static_cast<long long>(ra) * 16 + nt * 8 + 2 * t + 1, acc[nt][1] * ginv);
+      }
+      if (okb) {
+        atomicAdd(dctx + static_cast<long long>(rb) * 16 + nt * 8 + 2 * t, acc[nt][2] * ginv);
+        atomicAdd(dctx + static_cast<long long>(rb) * 16 + nt * 8 + 2 * t + 1, acc[nt][3] * ginv);
       }
     }
   }
+  // ---- dW[c][e] += sum_m dkv[r0 + m][c] * ctx[r0 + m][e] ----
+  for (int mt = warp; mt < C2 / 16; mt += 8) {
+    const int ca = mt * 16 + g, cb = ca + 8;
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 4
+    for (int k0 = 0; k0 < kPRows; k0 += 8) {
+      const int ka = r0 + k0 + t, kb = ka + 4;
+      const float* p0 = dk + static_cast<long long>(ka) * C2;
+      const float* p1 = dk + static_cast<long long>(kb) * C2;
+      uint32_t a[4];
+      a[0] = to_tf32(ka < R ? p0[ca] : 0.f);
+      a[1] = to_tf32(ka < R ? p0[cb] : 0.f);
+      a[2] = to_tf32(kb < R ? p1[ca] : 0.f);
+      a[3] = to_tf32(kb < R ? p1[cb] : 0.f);
+      const float* cb_s = c_s + (k0 + t) * kPPitch + g;
+      mma_tf32(acc[0], a, to_tf32(cb_s[0]), to_tf32(cb_s[4 * kPPitch]));
+      mma_tf32(acc[1], a, to_tf32(cb_s[8]), to_tf32(cb_s[4 * kPPitch + 8]));
+    }
+    float* da = ca < en.C ? en.dwk + ca * 16 : en.dwv + (ca - en.C) * 16;
+    float* db = cb < en.C ? en.dwk + cb * 16 : en.dwv + (cb - en.C) * 16;
 #pragma unroll
-  for (int r = 0; r < kRows; ++r) {
-    const int row = threadIdx.x + r * 256;
-    if (row < 2 * C) {
-      float* dst = row < C ? en.dwk + row * Dc : en.dwv + (row - C) * Dc;
-#pragma unroll
-      for (int e = 0; e < kMaxDc; ++e)
-        if (e < Dc) atomicAdd(dst + e, acc[r][e] * ginv);
+    for (int nt = 0; nt < 2; ++nt) {
+      atomicAdd(da + nt * 8 + 2 * t, acc[nt][0] * ginv);
+      atomicAdd(da + nt * 8 + 2 * t + 1, acc[nt][1] * ginv);
+      atomicAdd(db + nt * 8 + 2 * t, acc[nt][2] * ginv);
+      atomicAdd(db + nt * 8 + 2 * t + 1, acc[nt][3] * ginv);
     }
   }
 }
@@ -783,7 +823,8 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_proj_group_kernel(const Cr
 int launch_cross_attn_bwd_proj_group(const CrossProjEntry* tab_dev, int n_layers, int max_C, const float* ctx, float* dctx,
                                      const float* gscale, int B, int T, int Dc, cudaStream_t s) {
   if (n_layers <= 0) return 0;
-  const size_t smem = (2ull * max_C * Dc + 2ull * T * max_C + T * Dc) * sizeof(float);
+  if (Dc != 16 || (max_C % 8) != 0) return static_cast<int>(cudaErrorInvalidValue);   // TF32 tiles: 16 context dims
+  const size_t smem = (2ull * max_C + kPRows) * kPPitch * sizeof(float);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(cross_attn_bwd_proj_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -791,9 +832,9 @@ int launch_cross_attn_bwd_proj_group(const CrossProjEntry* tab_dev, int n_layers
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = smem;
   }
-  const int chunk = 8;
-  launch_k(cross_attn_bwd_proj_group_kernel, dim3((B + chunk - 1) / chunk, n_layers), 256, smem, s, tab_dev, ctx, dctx, gscale, B,
-           T, Dc, chunk);
+  const int R = B * T;
+  launch_k(cross_attn_bwd_proj_group_kernel, dim3((R + kPRows - 1) / kPRows, n_layers), 256, smem, s, tab_dev, ctx, dctx, gscale,
+           R);
   return static_cast<int>(cudaGetLastError());
 }
 

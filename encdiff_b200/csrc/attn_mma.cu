@@ -196,46 +196,19 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
   h16* Qs = reinterpret_cast<h16*>(smraw);   // [G][N][D]
   h16* Ks = Qs + G * N * D;
   h16* Vs = Ks + G * N * D;
-  h16* Os = Vs + G * N * D;                  // f * dO
+  h16* Os = Vs + G * N * D;                  // dO
   h16* Qt = Os + G * N * D;                  // [G][D][NP]
   h16* Kt = Qt + G * D * NP;
-  h16* Ot = Kt + G * D * NP;                 // (f * dO)^T
+  h16* Ot = Kt + G * D * NP;                 // dO^T
   float* Ls = reinterpret_cast<float*>(Ot + G * D * NP);   // [G][N] lse (log2 domain)
-  float* Ds = Ls + G * N;                                  // [G][N] delta = rowsum(f dO * O)
+  float* Ds = Ls + G * N;                                  // [G][N] delta = rowsum(dO * O)
   __shared__ float s_red[16];
-  __shared__ float s_f;
   const int C = heads * D;
   const int groups = heads / G;
   const int b = blockIdx.x / groups, hg = blockIdx.x - b * groups;
   constexpr int DC = D / 8;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // ---- CTA-wide max |dO| -> power-of-two normaliser ------------------------------------------------------------
-  float amax = 0.f;
-  for (int idx = threadIdx.x; idx < G * N * DC; idx += blockDim.x) {
-    const int slot = idx / (N * DC);
-    const int rem = idx - slot * N * DC;
-    const int j = rem / DC, dc = rem - j * DC;
-    float f[8];
-    unpack8(*reinterpret_cast<const uint4*>(dout + (static_cast<long long>(b) * N + j) * C + (hg * G + slot) * D + dc * 8), f);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(f[k]));
-  }
-  amax = warp_max(amax);
-  if (lane == 0) s_red[warp] = amax;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float m = 0.f;
-    for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmaxf(m, s_red[w]);
-    float fsc = 1.f;
-    if (m > 0.f && isfinite(m)) {
-      int e;
-      frexpf(m, &e);
-      fsc = ldexpf(1.f, -e);
-    }
-    s_f = fsc;
-  }
-  __syncthreads();
-  const float fsc = s_f, finv = 1.f / s_f;
+  float amax = 0.f;      // CTA-wide max |dO| (collected while staging) -> power-of-two scale of the fp16 dS fragments
   // ---- stage Q, K, V, f*dO (row-major and the transposes the second MMAs need), lse, delta ---------------------
   for (int idx = threadIdx.x; idx < G * N * DC; idx += blockDim.x) {
     const int slot = idx / (N * DC);
@@ -250,11 +223,13 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
     *reinterpret_cast<uint4*>(Qs + o) = q4;
     *reinterpret_cast<uint4*>(Ks + o) = k4;
     *reinterpret_cast<uint4*>(Vs + o) = *reinterpret_cast<const uint4*>(base + 2 * C);
-    float d8[8];
-    unpack8(*reinterpret_cast<const uint4*>(dout + row * C + h * D + dc * 8), d8);
+    const uint4 o4 = *reinterpret_cast<const uint4*>(dout + row * C + h * D + dc * 8);
+    {
+      float d8[8];
+      unpack8(o4, d8);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) d8[k] *= fsc;
-    const uint4 o4 = pack8(d8);
+      for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(d8[k]));
+    }
     *reinterpret_cast<uint4*>(Os + o) = o4;
     const h16* qe = reinterpret_cast<const h16*>(&q4);
     const h16* ke = reinterpret_cast<const h16*>(&k4);
@@ -280,10 +255,23 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
 #pragma unroll
       for (int k = 0; k < 8; ++k) dl += o[k] * d[k];
     }
-    Ds[idx] = dl * fsc;
+    Ds[idx] = dl;
     Ls[idx] = lse[(static_cast<long long>(b) * heads + h) * N + j];
   }
+  amax = warp_max(amax);
+  if (lane == 0) s_red[warp] = amax;
   __syncthreads();
+  float fsc = 1.f;
+  {
+    float m = 0.f;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmaxf(m, s_red[w]);
+    if (m > 0.f && isfinite(m)) {
+      int e;
+      frexpf(m, &e);
+      fsc = ldexpf(1.f, -e);
+    }
+  }
+  const float finv = 1.f / fsc, sfs = scale * fsc;   // dS is carried multiplied by fsc, dq / dk are multiplied back
   const int g = lane >> 2, t = lane & 3;
   const int qtiles = N >> 4;
   const int slot = warp / qtiles, r0 = (warp - slot * qtiles) << 4;
@@ -315,10 +303,10 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
       for (int i = 0; i < 2; ++i) {
         mma_rowsT<D>(s[i], qa, Kh, kc + 8 * i, g, t);
         mma_rowsT<D>(dp[i], oa, Vh, kc + 8 * i, g, t);
-        s[i][0] = exp2f(s[i][0] * scale_log2 - ls0) * (dp[i][0] - de0) * scale;
-        s[i][1] = exp2f(s[i][1] * scale_log2 - ls0) * (dp[i][1] - de0) * scale;
-        s[i][2] = exp2f(s[i][2] * scale_log2 - ls1) * (dp[i][2] - de1) * scale;
-        s[i][3] = exp2f(s[i][3] * scale_log2 - ls1) * (dp[i][3] - de1) * scale;
+        s[i][0] = exp2f(s[i][0] * scale_log2 - ls0) * (dp[i][0] - de0) * sfs;
+        s[i][1] = exp2f(s[i][1] * scale_log2 - ls0) * (dp[i][1] - de0) * sfs;
+        s[i][2] = exp2f(s[i][2] * scale_log2 - ls1) * (dp[i][2] - de1) * sfs;
+        s[i][3] = exp2f(s[i][3] * scale_log2 - ls1) * (dp[i][3] - de1) * sfs;
       }
       uint32_t da[4] = {pack2(s[0][0], s[0][1]), pack2(s[0][2], s[0][3]), pack2(s[1][0], s[1][1]), pack2(s[1][2], s[1][3])};
 #pragma unroll
@@ -354,10 +342,10 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
         st[i][1] = exp2f(st[i][1] * scale_log2 - lq.y);
         st[i][2] = exp2f(st[i][2] * scale_log2 - lq.x);
         st[i][3] = exp2f(st[i][3] * scale_log2 - lq.y);
-        ds[i][0] = st[i][0] * (dpt[i][0] - dq2.x) * scale;
-        ds[i][1] = st[i][1] * (dpt[i][1] - dq2.y) * scale;
-        ds[i][2] = st[i][2] * (dpt[i][2] - dq2.x) * scale;
-        ds[i][3] = st[i][3] * (dpt[i][3] - dq2.y) * scale;
+        ds[i][0] = st[i][0] * (dpt[i][0] - dq2.x) * sfs;
+        ds[i][1] = st[i][1] * (dpt[i][1] - dq2.y) * sfs;
+        ds[i][2] = st[i][2] * (dpt[i][2] - dq2.x) * sfs;
+        ds[i][3] = st[i][3] * (dpt[i][3] - dq2.y) * sfs;
       }
       uint32_t pa[4] = {pack2(st[0][0], st[0][1]), pack2(st[0][2], st[0][3]), pack2(st[1][0], st[1][1]), pack2(st[1][2], st[1][3])};
       uint32_t da[4] = {pack2(ds[0][0], ds[0][1]), pack2(ds[0][2], ds[0][3]), pack2(ds[1][0], ds[1][1]), pack2(ds[1][2], ds[1][3])};
@@ -373,8 +361,8 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
       h16* p1 = dqkv + (grow + 8) * 3 * C + C + h * D + nt * 8 + 2 * t;
       *reinterpret_cast<uint32_t*>(p0) = pack2(dk[nt][0] * finv, dk[nt][1] * finv);
       *reinterpret_cast<uint32_t*>(p1) = pack2(dk[nt][2] * finv, dk[nt][3] * finv);
-      *reinterpret_cast<uint32_t*>(p0 + C) = pack2(dv[nt][0] * finv, dv[nt][1] * finv);
-      *reinterpret_cast<uint32_t*>(p1 + C) = pack2(dv[nt][2] * finv, dv[nt][3] * finv);
+      *reinterpret_cast<uint32_t*>(p0 + C) = pack2(dv[nt][0], dv[nt][1]);
+      *reinterpret_cast<uint32_t*>(p1 + C) = pack2(dv[nt][2], dv[nt][3]);
     }
   }
 }
@@ -594,7 +582,7 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
   const int NT = (N + 15) & ~15;             // query rows padded to whole tiles: zero rows contribute nothing
   const int NP = NT + 8;
   h16* Qs = reinterpret_cast<h16*>(smraw);   // [G][NT][D]
-  h16* Os = Qs + G * NT * D;                 // f * dO
+  h16* Os = Qs + G * NT * D;                 // dO
   h16* Qt = Os + G * NT * D;                 // [G][D][NP]
   h16* Ot = Qt + G * D * NP;
   h16* Ks = Ot + G * D * NP;                 // [G][kNK][D]
@@ -603,38 +591,12 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
   float* acc = reinterpret_cast<float*>(Kt + G * D * kNKP);   // [warps][kNK][2D] per-warp dK | dV partial sums
   float* qst = acc + (blockDim.x >> 5) * kNK * 2 * D;         // [warps][16][3] row max, 1/l, delta
   __shared__ float s_red[16];
-  __shared__ float s_f;
   const int C = heads * D;
   const int groups = heads / G;
   const int b = blockIdx.x / groups, hg = blockIdx.x - b * groups;
   constexpr int DC = D / 8;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float amax = 0.f;
-  for (int idx = threadIdx.x; idx < G * N * DC; idx += blockDim.x) {
-    const int slot = idx / (N * DC);
-    const int rem = idx - slot * N * DC;
-    const int j = rem / DC, dc = rem - j * DC;
-    float f[8];
-    unpack8(*reinterpret_cast<const uint4*>(dout + (static_cast<long long>(b) * N + j) * C + (hg * G + slot) * D + dc * 8), f);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(f[k]));
-  }
-  amax = warp_max(amax);
-  if (lane == 0) s_red[warp] = amax;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float m = 0.f;
-    for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmaxf(m, s_red[w]);
-    float fsc = 1.f;
-    if (m > 0.f && isfinite(m)) {
-      int e;
-      frexpf(m, &e);
-      fsc = ldexpf(1.f, -e);
-    }
-    s_f = fsc;
-  }
-  __syncthreads();
-  const float fsc = s_f, finv = 1.f / s_f;
+  float amax = 0.f;      // CTA-wide max |dO|, collected while staging
   for (int idx = threadIdx.x; idx < G * NT * DC; idx += blockDim.x) {
     const int slot = idx / (NT * DC);
     const int rem = idx - slot * NT * DC;
@@ -643,11 +605,11 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
     uint4 q4 = make_uint4(0u, 0u, 0u, 0u), o4 = q4;
     if (j < N) {
       q4 = *reinterpret_cast<const uint4*>(q + goff);
+      o4 = *reinterpret_cast<const uint4*>(dout + goff);
       float d8[8];
-      unpack8(*reinterpret_cast<const uint4*>(dout + goff), d8);
+      unpack8(o4, d8);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) d8[k] *= fsc;
-      o4 = pack8(d8);
+      for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(d8[k]));
     }
     const int o = (slot * NT + j) * D + dc * 8;
     *reinterpret_cast<uint4*>(Qs + o) = q4;
@@ -662,7 +624,20 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
     }
   }
   stage_kv<D>(kv + static_cast<long long>(b) * T * 2 * C, T, C, hg, G, Ks, Vs, Kt, nullptr);
+  amax = warp_max(amax);
+  if (lane == 0) s_red[warp] = amax;
   __syncthreads();
+  float fsc = 1.f;
+  {
+    float m = 0.f;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmaxf(m, s_red[w]);
+    if (m > 0.f && isfinite(m)) {
+      int e;
+      frexpf(m, &e);
+      fsc = ldexpf(1.f, -e);
+    }
+  }
+  const float finv = 1.f / fsc, sfs = scale * fsc;   // dS carried multiplied by fsc; dq / dK multiplied back
   const int g = lane >> 2, t = lane & 3;
   const int qtiles = NT >> 4;
   const int slot = warp / qtiles, q0 = (warp - slot * qtiles) << 4;
@@ -730,10 +705,10 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
       }
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) {
-        s[nt][0] *= (dp[nt][0] - de0) * scale;
-        s[nt][1] *= (dp[nt][1] - de0) * scale;
-        s[nt][2] *= (dp[nt][2] - de1) * scale;
-        s[nt][3] *= (dp[nt][3] - de1) * scale;
+        s[nt][0] *= (dp[nt][0] - de0) * sfs;
+        s[nt][1] *= (dp[nt][1] - de0) * sfs;
+        s[nt][2] *= (dp[nt][2] - de1) * sfs;
+        s[nt][3] *= (dp[nt][3] - de1) * sfs;
       }
       float dqa[DC][4];
 #pragma unroll
@@ -776,10 +751,10 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
         pt[i][1] = k0ok ? exp2f(pt[i][1] * scale_log2 - mb) * ib : 0.f;
         pt[i][2] = k1ok ? exp2f(pt[i][2] * scale_log2 - ma) * ia : 0.f;
         pt[i][3] = k1ok ? exp2f(pt[i][3] * scale_log2 - mb) * ib : 0.f;
-        ds[i][0] = pt[i][0] * (dpt[0] - dea) * scale;
-        ds[i][1] = pt[i][1] * (dpt[1] - deb) * scale;
-        ds[i][2] = pt[i][2] * (dpt[2] - dea) * scale;
-        ds[i][3] = pt[i][3] * (dpt[3] - deb) * scale;
+        ds[i][0] = pt[i][0] * (dpt[0] - dea) * sfs;
+        ds[i][1] = pt[i][1] * (dpt[1] - deb) * sfs;
+        ds[i][2] = pt[i][2] * (dpt[2] - dea) * sfs;
+        ds[i][3] = pt[i][3] * (dpt[3] - deb) * sfs;
       }
       uint32_t pa[4] = {pack2(pt[0][0], pt[0][1]), pack2(pt[0][2], pt[0][3]), pack2(pt[1][0], pt[1][1]), pack2(pt[1][2], pt[1][3])};
       uint32_t da[4] = {pack2(ds[0][0], ds[0][1]), pack2(ds[0][2], ds[0][3]), pack2(ds[1][0], ds[1][1]), pack2(ds[1][2], ds[1][3])};
@@ -806,7 +781,7 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
     const int hh = hg * G + sl;
     float v = 0.f;
     for (int w = 0; w < qtiles; ++w) v += acc[((sl * qtiles + w) * kNK + j) * 2 * D + c];
-    v *= finv;
+    if (c < D) v *= finv;      // dK came through the scaled dS; dV = P^T dO did not
     if (c < D) dst[static_cast<long long>(j) * 2 * C + hh * D + c] = v;
     else dst[static_cast<long long>(j) * 2 * C + C + hh * D + (c - D)] = v;
   }
