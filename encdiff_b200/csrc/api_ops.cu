@@ -35,7 +35,7 @@ extern "C" int encdiff_op_sgemm(int nsrc, const void* const* a_ptrs, const int* 
   if (bn <= 0 && !out_fp32 && !out1 && ld0 == N && !old_only) {
     const int sms = device_sm_count();
     const int m_tiles = (B * H * W + 127) / 128;
-    const int bn2 = sgemm2_pick_bn(m_tiles, N, sms);
+    const int bn2 = sgemm2_pick_bn(m_tiles, N, sms, static_cast<int>(K / 64));
     if (bn2) {   // persistent kernel (gemm2.cu)
       Sgemm2Params q;
       memset(&q, 0, sizeof(q));

@@ -109,6 +109,6 @@ int launch_sgemm(const SgemmParams& p, int bn, cudaStream_t stream);
 int launch_wgrad(const WgradParams& p, int bn, int splits, cudaStream_t stream);
 int sgemm_pick_bn(int N);
 int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t stream);
-int sgemm2_pick_bn(int m_tiles, int N, int num_sms);   // 0: shape not supported by the persistent kernel
+int sgemm2_pick_bn(int m_tiles, int N, int num_sms, int nkb);   // nkb = 64-wide k-blocks per tile   // 0: shape not supported by the persistent kernel
 
 }  // namespace edb

@@ -250,12 +250,26 @@ static int launch_sgemm2_t(const Sgemm2Params& p, int num_sms, cudaStream_t stre
   return static_cast<int>(cudaGetLastError());
 }
 
-// N tile: as wide as possible while the tile count still fills the chip
-int sgemm2_pick_bn(int m_tiles, int N, int num_sms) {
+// N tile by a per-SM cost model.  These GEMMs are bound by the L2 -> shared-memory fill of their stages, not by the
+// tensor pipe: a k-block moves 16 KB of A plus BN/4 KB of B per CTA whatever BN is, so a wider tile moves fewer bytes
+// per FLOP but leaves SMs idle when it produces fewer tiles than SMs.  cost = rounds * (k-blocks * stage bytes / fill
+// rate + epilogue panels); constants from the in-graph timings in profiles/ (about 90 GB/s per SM, 0.4 us per panel).
+int sgemm2_pick_bn(int m_tiles, int N, int num_sms, int nkb) {
   if (N % 64 != 0) return 0;
-  if (N >= 256 && N % 256 == 0 && m_tiles * (N / 256) >= num_sms) return 256;
-  if (N >= 128 && m_tiles * ((N + 127) / 128) >= num_sms) return 128;
-  return 64;
+  int best = 64;
+  float best_cost = 1e30f;
+  for (int bn = 64; bn <= 256; bn *= 2) {
+    if (bn > 64 && N % bn != 0) continue;
+    const int tiles = m_tiles * (N / bn);
+    const int rounds = (tiles + num_sms - 1) / num_sms;
+    const float fill_us = static_cast<float>(nkb) * (16.f + bn / 4.f) / 90.f;
+    const float cost = rounds * (fill_us + 0.4f * (bn / 64));
+    if (cost < best_cost * 0.97f) {      // prefer the narrower tile on near-ties (more CTAs in flight)
+      best_cost = cost;
+      best = bn;
+    }
+  }
+  return best;
 }
 
 int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t stream) {

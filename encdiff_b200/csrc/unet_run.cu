@@ -360,7 +360,7 @@ struct Exec {
     p.nsrc = i;
     const int sms = device_sm_count();
     const int m_tiles = (B * H * W + 127) / 128;
-    const int bn2 = (!fp32 && ld == N && !u->force_old_gemm) ? sgemm2_pick_bn(m_tiles, N, sms) : 0;
+    const int bn2 = (!fp32 && ld == N && !u->force_old_gemm) ? sgemm2_pick_bn(m_tiles, N, sms, static_cast<int>(K / 64)) : 0;
     if (bn2) {
       Sgemm2Params q;
       memset(&q, 0, sizeof(q));
