@@ -224,16 +224,24 @@ def run_b200(args):
     ms = timed(step_dev, K, dist_on)
     # ---- (2) host buffers through the public step(): `e2e` (H2D of the batch + D2H of the loss inside the region) --
     host_batches = [synthetic_batch(B, 123 + 7 * rank + i, pin=True) for i in range(nb)]
-    loss_host = torch.zeros(1).pin_memory()
+    loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+    seen = []
 
     def step_host(i):
+        # H2D of the batch (inside trainer.step) -> step -> D2H of the loss, every step.  The host reads each loss one
+        # step late (after its copy event), the way a training loop logs it, so launching step i+1 overlaps step i.
         loss, _ = trainer.step(*host_batches[i % nb])
-        loss_host.copy_(loss, non_blocking=True)
-        torch.cuda.current_stream().synchronize()     # the caller reads the loss every step
+        loss_host[i & 1].copy_(loss, non_blocking=True)
+        loss_ev[i & 1].record()
+        if i > 0:
+            loss_ev[(i - 1) & 1].synchronize()
+            seen.append(float(loss_host[(i - 1) & 1][0]))
 
     for i in range(3):
         step_host(i)
-    ms_e2e = timed(step_host, K, dist_on)
+    torch.cuda.synchronize()
+    ms_e2e = timed(step_host, K, dist_on)       # timed() synchronises at the end: the last loss has landed too
     clk = clocks.stop() if rank == 0 else None
     h2d = sum(v.numel() * v.element_size() for v in host_batches[0])
 

@@ -97,6 +97,7 @@ class DenoiserTrainer:
             self.world = torch.distributed.get_world_size(process_group)
         self.use_cuda_graph = use_cuda_graph
         self._static = None
+        self._bound_once = False
 
     # ---- drop-in p_losses ----------------------------------------------------------------------------------------
     def q_sample(self, x_start, t, noise):
@@ -163,8 +164,12 @@ class DenoiserTrainer:
         st["t"].copy_(t, non_blocking=True)
         st["cond"].copy_(cond, non_blocking=True)
         self.opt.write_hyper(lr)
-        u._bind(need_grads=True)
-        u._prepare_grads()
+        if st.get("g_fb") is None or not self._bound_once:
+            # walks all 734 parameters (Python): only before the graphs exist; afterwards the parameters are views of
+            # the optimiser's flat buffer and cannot move (call invalidate() after replacing a parameter tensor)
+            u._bind(need_grads=True)
+            u._prepare_grads()
+            self._bound_once = True
         if not u._packed_valid:
             u.refresh_weights()
         prev = u.cache_packed_weights
@@ -193,6 +198,11 @@ class DenoiserTrainer:
         finally:
             u.cache_packed_weights = prev
         return st["loss"], st["dcond"]
+
+    def invalidate(self):
+        """Forget the captured graphs and the cached binding (after parameters were replaced or moved)."""
+        self._static = None
+        self._bound_once = False
 
     def _allreduce(self):
         """Sum of the flat fp32 gradient bucket over the data-parallel ranks: ONE NCCL all-reduce over NVLink for all
