@@ -63,11 +63,13 @@ def test_adamw_kernel_matches_torch(cuda_device):
     assert torch.allclose(opt.ema.cpu(), shadow, rtol=1e-5, atol=1e-6)
 
 
-@pytest.mark.parametrize("graph", [False, True])
-def test_fused_step_loss_curve_vs_oracle(cuda_device, graph):
+@pytest.mark.parametrize("graph,steps", [(False, 24), (True, 120)])
+def test_fused_step_loss_curve_vs_oracle(cuda_device, graph, steps):
+    """North-star bar: training loss curve within 2 % of the reference's (here every step of a 120-step run of the tiny
+    configuration, same batches / noise / timesteps on both sides; the fp32 oracle needs ~0.2 s per step on the host)."""
     from encdiff_b200.train import DenoiserTrainer
     cfg = CONFIGS["tiny"]
-    B, steps, lr = 8, 24, 2e-4
+    B, lr = 8, 2e-4
     m, params = make_unet(cfg, cuda_device)
     tr = DenoiserTrainer(m, lr=lr, weight_decay=0.01, use_ema=True, use_cuda_graph=graph)
     # oracle: same batches, torch autograd + torch.optim.AdamW on CPU
