@@ -480,9 +480,9 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
   }
 }
 
-static int gn_threads(int C) {
+static int gn_threads(int C, int max_threads = 512) {
   const int nv = C / 8;
-  int rp = 512 / nv;
+  int rp = max_threads / nv;
   if (rp < 1) rp = 1;
   return nv * rp;
 }
@@ -519,7 +519,8 @@ int launch_gn_bwd(const GnParams& p, int B, cudaStream_t s) {
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = smem;
   }
-  launch_k(gn_bwd_kernel, B, gn_threads(C), smem, s, p);
+  // 256-thread CTAs: at 128 registers a 512-thread CTA owns a whole SM and the B = 256 samples would need two waves
+  launch_k(gn_bwd_kernel, B, gn_threads(C, 256), smem, s, p);
   return static_cast<int>(cudaGetLastError());
 }
 
