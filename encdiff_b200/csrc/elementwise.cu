@@ -399,26 +399,26 @@ __global__ void __launch_bounds__(256) pack_kernel(const PackEntry* __restrict__
     const int nr = min(32, en.rows - r0), nci = min(ci_tile, en.cin - ci0);
     const int w = nci * en.taps;                          // source columns of this tile
     const long long row_len = static_cast<long long>(en.cin) * en.taps;
-    for (int i = threadIdx.x; i < nr * w; i += blockDim.x) {
-      const int rr = i / w, k = i - rr * w;
-      tile[rr][k] = en.src[(r0 + rr) * row_len + static_cast<long long>(ci0) * en.taps + k];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // warps walk rows / (channel, tap) pairs, lanes walk the contiguous index: no per-element integer division
+    for (int rr = warp; rr < nr; rr += 8) {
+      const float* src = en.src + (r0 + rr) * row_len + static_cast<long long>(ci0) * en.taps;
+      for (int k = lane; k < w; k += 32) tile[rr][k] = src[k];
     }
     __syncthreads();
     h16* dst = abf + en.dst_off;
     if (en.kind == 0) {         // dst[row0 + r][col0 + tap * cin_pad + ci]: ci fastest
-      for (int i = threadIdx.x; i < nr * w; i += blockDim.x) {
-        const int rr = i / w, rem = i - rr * w;
-        const int tap = rem / nci, c = rem - tap * nci;
-        dst[static_cast<long long>(en.row0 + r0 + rr) * en.dst_ld + en.col0 + tap * en.cin_pad + ci0 + c] =
-            f2h(tile[rr][c * en.taps + tap]);
+      for (int rr = warp; rr < nr; rr += 8) {
+        h16* drow = dst + static_cast<long long>(en.row0 + r0 + rr) * en.dst_ld + en.col0 + ci0;
+        for (int tap = 0; tap < en.taps; ++tap)
+          for (int c = lane; c < nci; c += 32) drow[tap * en.cin_pad + c] = f2h(tile[rr][c * en.taps + tap]);
       }
     } else {                    // dst[row0 + ci][col0 + tap * rows_pad + r]: r fastest
-      const int per_c = en.taps * nr;
-      for (int i = threadIdx.x; i < nci * per_c; i += blockDim.x) {
-        const int c = i / per_c, rem = i - c * per_c;
-        const int tap = rem / nr, rr = rem - tap * nr;
-        dst[static_cast<long long>(en.row0 + ci0 + c) * en.dst_ld + en.col0 + tap * en.rows_pad + r0 + rr] =
-            f2h(tile[rr][c * en.taps + tap]);
+      const int pairs = nci * en.taps;
+      for (int pr = warp; pr < pairs; pr += 8) {
+        const int c = pr / en.taps, tap = pr - c * en.taps;
+        h16* drow = dst + static_cast<long long>(en.row0 + ci0 + c) * en.dst_ld + en.col0 + tap * en.rows_pad + r0;
+        if (lane < nr) drow[lane] = f2h(tile[lane][pr]);
       }
     }
     return;
