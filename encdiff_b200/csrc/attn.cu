@@ -69,11 +69,11 @@ __global__ void __launch_bounds__(256) self_attn_fwd_kernel(const h16* __restric
       s[k] = a;
     }
     const float mn = fmaxf(m, fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])));
-    const float corr = exp2f(m - mn);
+    const float corr = ex2_approx(m - mn);
     float psum = 0.f;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      s[k] = exp2f(s[k] - mn);
+      s[k] = ex2_approx(s[k] - mn);
       psum += s[k];
     }
     l = l * corr + psum;
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(256) self_attn_bwd_kernel(const h16* __restric
         s += q[d] * Kg[j * D + d];
         dp += dO[d] * Vg[j * D + d];
       }
-      const float ds = exp2f(s - li) * (dp - di) * scale;
+      const float ds = ex2_approx(s - li) * (dp - di) * scale;
 #pragma unroll
       for (int d = 0; d < D; ++d) dq[d] += ds * Kg[j * D + d];
     }
@@ -209,7 +209,7 @@ __global__ void __launch_bounds__(256) self_attn_bwd_kernel(const h16* __restric
         s += k[d] * Qg[j * D + d];
         dp += v[d] * Og[j * D + d];
       }
-      const float p = exp2f(s - Lg[j]);
+      const float p = ex2_approx(s - Lg[j]);
       const float ds = p * (dp - Dg[j]) * scale;
 #pragma unroll
       for (int d = 0; d < D; ++d) {
@@ -466,7 +466,7 @@ __global__ void __launch_bounds__(256) cross_attn_fwd_kernel(const h16* __restri
 #pragma unroll
     for (int j = 0; j < kMaxT; ++j) {
       if (j < T) {
-        s[j] = exp2f(s[j] - m);
+        s[j] = ex2_approx(s[j] - m);
         l += s[j];
       }
     }
@@ -574,7 +574,7 @@ __global__ void __launch_bounds__(256) cross_attn_bwd_kernel(const h16* __restri
 #pragma unroll
     for (int j = 0; j < kMaxT; ++j) {
       if (j < T) {
-        s[j] = exp2f(s[j] - m);
+        s[j] = ex2_approx(s[j] - m);
         l += s[j];
       }
     }

@@ -142,10 +142,10 @@ __global__ void __launch_bounds__(512) self_attn_fwd_mma_kernel(const h16* __res
     mma_rowsT<D>(c[1], qa, Kh, kc + 8, g, t);
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-      c[i][0] = exp2f(c[i][0] * scale_log2 - m0);
-      c[i][1] = exp2f(c[i][1] * scale_log2 - m0);
-      c[i][2] = exp2f(c[i][2] * scale_log2 - m1);
-      c[i][3] = exp2f(c[i][3] * scale_log2 - m1);
+      c[i][0] = ex2_approx(c[i][0] * scale_log2 - m0);
+      c[i][1] = ex2_approx(c[i][1] * scale_log2 - m0);
+      c[i][2] = ex2_approx(c[i][2] * scale_log2 - m1);
+      c[i][3] = ex2_approx(c[i][3] * scale_log2 - m1);
       l0 += c[i][0] + c[i][1];
       l1 += c[i][2] + c[i][3];
     }
@@ -303,10 +303,10 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
       for (int i = 0; i < 2; ++i) {
         mma_rowsT<D>(s[i], qa, Kh, kc + 8 * i, g, t);
         mma_rowsT<D>(dp[i], oa, Vh, kc + 8 * i, g, t);
-        s[i][0] = exp2f(s[i][0] * scale_log2 - ls0) * (dp[i][0] - de0) * sfs;
-        s[i][1] = exp2f(s[i][1] * scale_log2 - ls0) * (dp[i][1] - de0) * sfs;
-        s[i][2] = exp2f(s[i][2] * scale_log2 - ls1) * (dp[i][2] - de1) * sfs;
-        s[i][3] = exp2f(s[i][3] * scale_log2 - ls1) * (dp[i][3] - de1) * sfs;
+        s[i][0] = ex2_approx(s[i][0] * scale_log2 - ls0) * (dp[i][0] - de0) * sfs;
+        s[i][1] = ex2_approx(s[i][1] * scale_log2 - ls0) * (dp[i][1] - de0) * sfs;
+        s[i][2] = ex2_approx(s[i][2] * scale_log2 - ls1) * (dp[i][2] - de1) * sfs;
+        s[i][3] = ex2_approx(s[i][3] * scale_log2 - ls1) * (dp[i][3] - de1) * sfs;
       }
       uint32_t da[4] = {pack2(s[0][0], s[0][1]), pack2(s[0][2], s[0][3]), pack2(s[1][0], s[1][1]), pack2(s[1][2], s[1][3])};
 #pragma unroll
@@ -338,10 +338,10 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
         mma_rowsT<D>(dpt[i], va, Oh, qc + 8 * i, g, t);    // dP^T[key][query]
         const float2 lq = *reinterpret_cast<const float2*>(Lh + qc + 8 * i + 2 * t);   // columns 2t, 2t+1 = queries
         const float2 dq2 = *reinterpret_cast<const float2*>(Dh + qc + 8 * i + 2 * t);
-        st[i][0] = exp2f(st[i][0] * scale_log2 - lq.x);
-        st[i][1] = exp2f(st[i][1] * scale_log2 - lq.y);
-        st[i][2] = exp2f(st[i][2] * scale_log2 - lq.x);
-        st[i][3] = exp2f(st[i][3] * scale_log2 - lq.y);
+        st[i][0] = ex2_approx(st[i][0] * scale_log2 - lq.x);
+        st[i][1] = ex2_approx(st[i][1] * scale_log2 - lq.y);
+        st[i][2] = ex2_approx(st[i][2] * scale_log2 - lq.x);
+        st[i][3] = ex2_approx(st[i][3] * scale_log2 - lq.y);
         ds[i][0] = st[i][0] * (dpt[i][0] - dq2.x) * sfs;
         ds[i][1] = st[i][1] * (dpt[i][1] - dq2.y) * sfs;
         ds[i][2] = st[i][2] * (dpt[i][2] - dq2.x) * sfs;
@@ -541,10 +541,10 @@ __global__ void __launch_bounds__(512) cross_attn_fwd_mma_kernel(const h16* __re
   float l0 = 0.f, l1 = 0.f;
 #pragma unroll
   for (int nt = 0; nt < 4; ++nt) {
-    s[nt][0] = exp2f(s[nt][0] * scale_log2 - m0);
-    s[nt][1] = exp2f(s[nt][1] * scale_log2 - m0);
-    s[nt][2] = exp2f(s[nt][2] * scale_log2 - m1);
-    s[nt][3] = exp2f(s[nt][3] * scale_log2 - m1);
+    s[nt][0] = ex2_approx(s[nt][0] * scale_log2 - m0);
+    s[nt][1] = ex2_approx(s[nt][1] * scale_log2 - m0);
+    s[nt][2] = ex2_approx(s[nt][2] * scale_log2 - m1);
+    s[nt][3] = ex2_approx(s[nt][3] * scale_log2 - m1);
     l0 += s[nt][0] + s[nt][1];
     l1 += s[nt][2] + s[nt][3];
   }
@@ -675,10 +675,10 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
       float l0 = 0.f, l1 = 0.f;
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) {
-        s[nt][0] = exp2f(s[nt][0] * scale_log2 - m0);
-        s[nt][1] = exp2f(s[nt][1] * scale_log2 - m0);
-        s[nt][2] = exp2f(s[nt][2] * scale_log2 - m1);
-        s[nt][3] = exp2f(s[nt][3] * scale_log2 - m1);
+        s[nt][0] = ex2_approx(s[nt][0] * scale_log2 - m0);
+        s[nt][1] = ex2_approx(s[nt][1] * scale_log2 - m0);
+        s[nt][2] = ex2_approx(s[nt][2] * scale_log2 - m1);
+        s[nt][3] = ex2_approx(s[nt][3] * scale_log2 - m1);
         l0 += s[nt][0] + s[nt][1];
         l1 += s[nt][2] + s[nt][3];
       }
@@ -747,10 +747,10 @@ __global__ void __launch_bounds__(512) cross_attn_bwd_mma_kernel(const h16* __re
         const float* sa = st + (8 * i + 2 * t) * 3;
         const float ma = sa[0], ia = sa[1], dea = sa[2], mb = sa[3], ib = sa[4], deb = sa[5];
         const bool k0ok = kt + g < T, k1ok = kt + g + 8 < T;
-        pt[i][0] = k0ok ? exp2f(pt[i][0] * scale_log2 - ma) * ia : 0.f;
-        pt[i][1] = k0ok ? exp2f(pt[i][1] * scale_log2 - mb) * ib : 0.f;
-        pt[i][2] = k1ok ? exp2f(pt[i][2] * scale_log2 - ma) * ia : 0.f;
-        pt[i][3] = k1ok ? exp2f(pt[i][3] * scale_log2 - mb) * ib : 0.f;
+        pt[i][0] = k0ok ? ex2_approx(pt[i][0] * scale_log2 - ma) * ia : 0.f;
+        pt[i][1] = k0ok ? ex2_approx(pt[i][1] * scale_log2 - mb) * ib : 0.f;
+        pt[i][2] = k1ok ? ex2_approx(pt[i][2] * scale_log2 - ma) * ia : 0.f;
+        pt[i][3] = k1ok ? ex2_approx(pt[i][3] * scale_log2 - mb) * ib : 0.f;
         ds[i][0] = pt[i][0] * (dpt[0] - dea) * sfs;
         ds[i][1] = pt[i][1] * (dpt[1] - deb) * sfs;
         ds[i][2] = pt[i][2] * (dpt[2] - dea) * sfs;

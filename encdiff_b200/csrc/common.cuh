@@ -31,6 +31,13 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// 2^x as ONE MUFU.EX2 (exp2f() wraps the same instruction in a denormal-range fix-up: FSETP + 2 FMUL per call, which
+// made the attention loops issue-bound).  Results below 2^-126 flush to zero: irrelevant for softmax weights.
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
 // d/dx [x*sigmoid(x)] = s*(1 + x*(1-s))
 __device__ __forceinline__ float silu_grad_f(float x) {
