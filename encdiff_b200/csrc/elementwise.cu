@@ -53,52 +53,86 @@ int launch_silu_bwd(const float* x, const h16* dy, h16* dx, long long n, cudaStr
 }
 
 // ---- GEGLU (attention.py:37-45) -------------------------------------------------------------------------------------
-__global__ void geglu_fwd_kernel(const h16* __restrict__ g, h16* __restrict__ out, long long M, int inner) {
+// Indexing is 32-bit with a shift when the row width is a power of two (always, for the shipped widths): a 64-bit
+// division per 8 elements cost more instructions than the GELU itself.
+struct RowSplit {
+  unsigned nv;      // 8-element chunks per row
+  int shift;        // log2(nv) or -1
+  __device__ __forceinline__ void split(unsigned idx, unsigned* row, unsigned* chunk) const {
+    if (shift >= 0) {
+      *row = idx >> shift;
+      *chunk = idx & (nv - 1);
+    } else {
+      *row = idx / nv;
+      *chunk = idx - *row * nv;
+    }
+  }
+};
+static RowSplit make_row_split(int nv) {
+  RowSplit r;
+  r.nv = static_cast<unsigned>(nv);
+  r.shift = -1;
+  for (int s = 0; s < 31; ++s)
+    if ((1 << s) == nv) r.shift = s;
+  return r;
+}
+
+__global__ void __launch_bounds__(256) geglu_fwd_kernel(const h16* __restrict__ g, h16* __restrict__ out, unsigned total,
+                                                        int inner, RowSplit rs) {
   pdl_enter();
-  const int nv = inner >> 3;
-  const long long total = M * nv;
-  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long row = idx / nv;
-    const int c = static_cast<int>(idx - row * nv) * 8;
+  for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    unsigned row, ch;
+    rs.split(idx, &row, &ch);
+    const int c = static_cast<int>(ch) * 8;
+    const h16* gr = g + static_cast<long long>(row) * 2 * inner + c;
+    const uint4 rv = *reinterpret_cast<const uint4*>(gr);
+    const uint4 rg = *reinterpret_cast<const uint4*>(gr + inner);
     float v[8], gt[8];
-    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + c), v);
-    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + inner + c), gt);
+    unpack8(rv, v);
+    unpack8(rg, gt);
 #pragma unroll
     for (int k = 0; k < 8; ++k) v[k] *= gelu_erf_f(gt[k]);
-    *reinterpret_cast<uint4*>(out + row * inner + c) = pack8(v);
+    *reinterpret_cast<uint4*>(out + static_cast<long long>(row) * inner + c) = pack8(v);
   }
 }
-__global__ void geglu_bwd_kernel(const h16* __restrict__ g, const h16* __restrict__ dout, h16* __restrict__ dg,
-                                 long long M, int inner) {
+__global__ void __launch_bounds__(256) geglu_bwd_kernel(const h16* __restrict__ g, const h16* __restrict__ dout,
+                                                        h16* __restrict__ dg, unsigned total, int inner, RowSplit rs) {
   pdl_enter();
-  const int nv = inner >> 3;
-  const long long total = M * nv;
-  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long row = idx / nv;
-    const int c = static_cast<int>(idx - row * nv) * 8;
+  for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    unsigned row, ch;
+    rs.split(idx, &row, &ch);
+    const int c = static_cast<int>(ch) * 8;
+    const long long o2 = static_cast<long long>(row) * 2 * inner + c;
+    const uint4 rv = *reinterpret_cast<const uint4*>(g + o2);
+    const uint4 rg = *reinterpret_cast<const uint4*>(g + o2 + inner);
+    const uint4 rd = *reinterpret_cast<const uint4*>(dout + static_cast<long long>(row) * inner + c);
     float v[8], gt[8], d[8], dv[8], dgt[8];
-    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + c), v);
-    unpack8(*reinterpret_cast<const uint4*>(g + row * 2 * inner + inner + c), gt);
-    unpack8(*reinterpret_cast<const uint4*>(dout + row * inner + c), d);
+    unpack8(rv, v);
+    unpack8(rg, gt);
+    unpack8(rd, d);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      dv[k] = d[k] * gelu_erf_f(gt[k]);
-      dgt[k] = d[k] * v[k] * gelu_erf_grad_f(gt[k]);
+      float y, dy;
+      gelu_erf_both_f(gt[k], &y, &dy);
+      dv[k] = d[k] * y;
+      dgt[k] = d[k] * v[k] * dy;
     }
-    *reinterpret_cast<uint4*>(dg + row * 2 * inner + c) = pack8(dv);
-    *reinterpret_cast<uint4*>(dg + row * 2 * inner + inner + c) = pack8(dgt);
+    *reinterpret_cast<uint4*>(dg + o2) = pack8(dv);
+    *reinterpret_cast<uint4*>(dg + o2 + inner) = pack8(dgt);
   }
 }
 int launch_geglu_fwd(const h16* g, h16* out, long long M, int inner, cudaStream_t s) {
-  if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
-  launch_k(geglu_fwd_kernel, grid_for(M * (inner / 8), 256), 256, 0, s, g, out, M, inner);
+  if (inner % 8 || M * (inner / 8) >= (1LL << 31)) return static_cast<int>(cudaErrorInvalidValue);
+  const long long total = M * (inner / 8);
+  launch_k(geglu_fwd_kernel, grid_for(total, 256), 256, 0, s, g, out, static_cast<unsigned>(total), inner,
+           make_row_split(inner / 8));
   return static_cast<int>(cudaGetLastError());
 }
 int launch_geglu_bwd(const h16* g, const h16* dout, h16* dg, long long M, int inner, cudaStream_t s) {
-  if (inner % 8) return static_cast<int>(cudaErrorInvalidValue);
-  launch_k(geglu_bwd_kernel, grid_for(M * (inner / 8), 256), 256, 0, s, g, dout, dg, M, inner);
+  if (inner % 8 || M * (inner / 8) >= (1LL << 31)) return static_cast<int>(cudaErrorInvalidValue);
+  const long long total = M * (inner / 8);
+  launch_k(geglu_bwd_kernel, grid_for(total, 256), 256, 0, s, g, dout, dg, static_cast<unsigned>(total), inner,
+           make_row_split(inner / 8));
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -1,5 +1,7 @@
 // GroupNorm (+FiLM +SiLU +2x resample) and LayerNorm, forward and backward.  HBM-bound kernels: one read of the
 // input slab from HBM (the second pass hits L1/L2), one write of the result.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -93,9 +95,22 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
   float* chsq = sm + C;
   float* cA = sm + 2 * C;
   float* cB = sm + 3 * C;
-  float* gstat = sm + 4 * C;  // [64]
+  float* fS = sm + 4 * C;     // FiLM 1 + scale
+  float* fT = sm + 5 * C;     // FiLM shift
+  float* gstat = sm + 6 * C;  // [64]
   float* part = gstat + 64;   // [rows][2][C] partial sums, rows <= 32
   const bool active = t.prow < t.rp;  // threads beyond nv*rp idle (blockDim is a multiple of nv, so all active)
+  // affine / FiLM parameters are fetched now, under the statistics pass, instead of after it (one dependent global
+  // round trip less on the CTA's critical path); the barriers inside gn_channel_reduce publish them
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    cA[c] = p.gamma[c];
+    cB[c] = p.beta[c];
+    if (p.film) {
+      const float* fr = p.film + static_cast<long long>(b) * p.ldfilm + p.film_off;
+      fS[c] = 1.f + fr[c];
+      fT[c] = fr[C + c];
+    }
+  }
   {
     float s[8], q[8];
 #pragma unroll
@@ -133,9 +148,9 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
       S += chsum[c];
       Q += chsq[c];
     }
-    const float n = static_cast<float>(cpg) * t.HW;
-    const float mean = S / n;
-    const float var = fmaxf(Q / n - mean * mean, 0.f);
+    const float inv_n = 1.0f / (static_cast<float>(cpg) * t.HW);
+    const float mean = S * inv_n;
+    const float var = fmaxf(Q * inv_n - mean * mean, 0.f);
     const float rstd = rsqrtf(var + p.eps);
     gstat[g] = mean;
     gstat[32 + g] = rstd;
@@ -145,13 +160,12 @@ __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const int g = c / cpg;
-    float ga = p.gamma[c] * gstat[32 + g];
-    float be = p.beta[c] - gstat[g] * ga;
+    float ga = cA[c] * gstat[32 + g];
+    float be = cB[c] - gstat[g] * ga;
     if (p.film) {
-      const float* fr = p.film + static_cast<long long>(b) * p.ldfilm + p.film_off;
-      const float sc = 1.f + fr[c];
+      const float sc = fS[c];
       ga *= sc;
-      be = be * sc + fr[C + c];
+      be = be * sc + fT[c];
     }
     cA[c] = ga;
     cB[c] = be;
@@ -282,6 +296,20 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
   int HWo = t.HW;
   if (p.resample == RESAMPLE_DOWN) HWo = t.HW / 4;
   if (p.resample == RESAMPLE_UP) HWo = t.HW * 4;
+  const h16* dact = p.dact + static_cast<long long>(b) * HWo * C + t.c0;
+  // first batch of (x, dact) rows: issued before the parameter staging below so both round trips overlap
+  uint4 rx[4], rd[4];
+  auto load_batch = [&](int pix0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int pix = pix0 + u * t.rp;
+      if (pix < t.HW) {
+        rx[u] = *reinterpret_cast<const uint4*>(t.src + static_cast<long long>(pix) * t.ld + t.cofs);
+        rd[u] = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(pix) * C);
+      }
+    }
+  };
+  if (p.resample == RESAMPLE_NONE) load_batch(t.prow);
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const int g = c / cpg;
     const float mean = p.stats[(b * 32 + g) * 2], rstd = p.stats[(b * 32 + g) * 2 + 1];
@@ -299,7 +327,6 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     cR[c] = rstd;
   }
   __syncthreads();
-  const h16* dact = p.dact + static_cast<long long>(b) * HWo * C + t.c0;
   float a[8], bb[8], mu[8], rs[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
@@ -313,17 +340,9 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
     if (p.resample == RESAMPLE_NONE) {
-      // 4 x (x, dact) loads in flight per thread
+      // 4 x (x, dact) loads in flight per thread; the first batch is already on its way
       for (int pix0 = t.prow; pix0 < t.HW; pix0 += 4 * t.rp) {
-        uint4 rx[4], rd[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int pix = pix0 + u * t.rp;
-          if (pix < t.HW) {
-            rx[u] = *reinterpret_cast<const uint4*>(t.src + static_cast<long long>(pix) * t.ld + t.cofs);
-            rd[u] = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(pix) * C);
-          }
-        }
+        if (pix0 != t.prow) load_batch(pix0);
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           if (pix0 + u * t.rp < t.HW) {
@@ -384,9 +403,9 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
       A += S1[c];
       Bv += S2[c];
     }
-    const float n = static_cast<float>(cpg) * t.HW;
-    gAB[g] = A / n;
-    gAB[32 + g] = Bv / n;
+    const float inv_n = 1.0f / (static_cast<float>(cpg) * t.HW);
+    gAB[g] = A * inv_n;
+    gAB[32 + g] = Bv * inv_n;
   }
   __syncthreads();
   float k1[8], k2[8], k3[8];
@@ -497,8 +516,8 @@ static size_t gn_part_floats(int C) {
 
 int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s) {
   const int C = p.C0 + p.C1;
-  if (C % 32 != 0 || (p.C0 % 8) != 0 || C > 8192) return static_cast<int>(cudaErrorInvalidValue);
-  const size_t smem = (4 * C + 64 + gn_part_floats(C)) * sizeof(float);
+  if (C % 32 != 0 || (p.C0 % 8) != 0 || C > 4096) return static_cast<int>(cudaErrorInvalidValue);
+  const size_t smem = (6 * C + 64 + gn_part_floats(C)) * sizeof(float);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(gn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -509,7 +528,10 @@ int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s) {
   return static_cast<int>(cudaGetLastError());
 }
 
-int launch_gn_bwd(const GnParams& p, int B, cudaStream_t s) {
+int launch_gn_bwd(const GnParams& p_in, int B, cudaStream_t s) {
+  GnParams p = p_in;
+  static const int exp_noatom = getenv("ENCDIFF_EXP_NOATOM") != nullptr;
+  if (exp_noatom) p.dgamma = p.dbeta = nullptr;
   const int C = p.C0 + p.C1;
   if (C % 32 != 0 || (p.C0 % 8) != 0 || C > 4096) return static_cast<int>(cudaErrorInvalidValue);
   const size_t smem = (7 * C + 64 + gn_part_floats(C)) * sizeof(float);
@@ -556,7 +578,8 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const h16* __restrict__ x, 
       for (int k = 0; k < 8; ++k) v[j][k] = 0.f;
     }
   }
-  const float mean = group_sum(s, lpr) / C;
+  const float inv_c = 1.0f / static_cast<float>(C);
+  const float mean = group_sum(s, lpr) * inv_c;
   float q = 0.f;
 #pragma unroll
   for (int j = 0; j < CPL; ++j) {
@@ -569,7 +592,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const h16* __restrict__ x, 
       }
     }
   }
-  const float rstd = rsqrtf(group_sum(q, lpr) / C + eps);
+  const float rstd = rsqrtf(group_sum(q, lpr) * inv_c + eps);
   if (!ok) return;
   if (lane_in_row == 0) {
     stats[row * 2] = mean;
@@ -579,27 +602,35 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const h16* __restrict__ x, 
   for (int j = 0; j < CPL; ++j) {
     const int ch = lane_in_row + j * lpr;
     if (ch < nchunks) {
-      float o[8];
+      float o[8], ga[8], be[8];
+      *reinterpret_cast<float4*>(ga) = __ldg(reinterpret_cast<const float4*>(gamma + ch * 8));
+      *reinterpret_cast<float4*>(ga + 4) = __ldg(reinterpret_cast<const float4*>(gamma + ch * 8 + 4));
+      *reinterpret_cast<float4*>(be) = __ldg(reinterpret_cast<const float4*>(beta + ch * 8));
+      *reinterpret_cast<float4*>(be + 4) = __ldg(reinterpret_cast<const float4*>(beta + ch * 8 + 4));
 #pragma unroll
-      for (int k = 0; k < 8; ++k) o[k] = (v[j][k] - mean) * rstd * __ldg(gamma + ch * 8 + k) + __ldg(beta + ch * 8 + k);
+      for (int k = 0; k < 8; ++k) o[k] = fmaf((v[j][k] - mean) * rstd, ga[k], be[k]);
       *reinterpret_cast<uint4*>(y + row * C + ch * 8) = pack8(o);
     }
   }
 }
 
+// Persistent over rows; the next row's loads are issued before the current row is reduced (two rows in flight per
+// thread).  Parameter gradients: per-thread register sums -> one shared-memory row per row slot (plain stores) -> column
+// sums -> one global atomic per channel and CTA.  (The first version combined the row slots with shared-memory float
+// atomics: ncu showed 44 % of the stall cycles on that CAS loop and the kernel at 1.2 TB/s.)
 template <int CPL>
-__global__ void __launch_bounds__(256, CPL == 1 ? 4 : 1) ln_bwd_kernel(const h16* __restrict__ x, const float* __restrict__ stats,
+__global__ void __launch_bounds__(256, CPL == 1 ? 3 : 1) ln_bwd_kernel(const h16* __restrict__ x, const float* __restrict__ stats,
                                                      const float* __restrict__ gamma, const h16* __restrict__ dy,
                                                      const h16* __restrict__ dres, h16* __restrict__ dx,
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                      const float* __restrict__ gscale, int M, int C, int lpr) {
   pdl_enter();
-  extern __shared__ float sm[];  // [2*C] block partial sums of dgamma / dbeta
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
+  extern __shared__ float sm[];  // [rows_per_block][2*C] partial sums of dgamma | dbeta
   const int nchunks = C >> 3;
   const int rows_per_block = blockDim.x / lpr;
   const int lane_in_row = threadIdx.x % lpr;
+  const int slot = threadIdx.x / lpr;
+  const float inv_c = 1.0f / static_cast<float>(C);
   float ag[CPL][8], ab[CPL][8];
 #pragma unroll
   for (int j = 0; j < CPL; ++j)
@@ -610,32 +641,38 @@ __global__ void __launch_bounds__(256, CPL == 1 ? 4 : 1) ln_bwd_kernel(const h16
 #pragma unroll
   for (int j = 0; j < CPL; ++j) {
     const int ch = lane_in_row + j * lpr;
+    if (ch < nchunks) {
+      *reinterpret_cast<float4*>(&gam[j][0]) = __ldg(reinterpret_cast<const float4*>(gamma + ch * 8));
+      *reinterpret_cast<float4*>(&gam[j][4]) = __ldg(reinterpret_cast<const float4*>(gamma + ch * 8 + 4));
+    } else {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) gam[j][k] = ch < nchunks ? __ldg(gamma + ch * 8 + k) : 0.f;
+      for (int k = 0; k < 8; ++k) gam[j][k] = 0.f;
+    }
   }
-  for (long long row0 = static_cast<long long>(blockIdx.x) * rows_per_block; row0 < M;
-       row0 += static_cast<long long>(gridDim.x) * rows_per_block) {
-    const long long row = row0 + threadIdx.x / lpr;
-    const bool ok = row < M;
-    float xh[CPL][8], g[CPL][8];
-    float s1 = 0.f, s2 = 0.f;
-    float mean = 0.f, rstd = 0.f;
-    // every global load of the row is issued before the first use (x, dy, the residual-branch gradient, the statistics)
-    uint4 rx[CPL], rdy[CPL], rres[CPL];
+  const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
+  long long row = static_cast<long long>(blockIdx.x) * rows_per_block + slot;
+  uint4 rx[CPL], rdy[CPL], rres[CPL];
+  float2 st = make_float2(0.f, 0.f);
+  auto issue = [&](long long r) {
+    if (r < M) {
 #pragma unroll
-    for (int j = 0; j < CPL; ++j) {
-      const int ch = lane_in_row + j * lpr;
-      if (ok && ch < nchunks) {
-        rx[j] = *reinterpret_cast<const uint4*>(x + row * C + ch * 8);
-        rdy[j] = *reinterpret_cast<const uint4*>(dy + row * C + ch * 8);
-        if (dres) rres[j] = *reinterpret_cast<const uint4*>(dres + row * C + ch * 8);
+      for (int j = 0; j < CPL; ++j) {
+        const int ch = lane_in_row + j * lpr;
+        if (ch < nchunks) {
+          rx[j] = *reinterpret_cast<const uint4*>(x + r * C + ch * 8);
+          rdy[j] = *reinterpret_cast<const uint4*>(dy + r * C + ch * 8);
+          if (dres) rres[j] = *reinterpret_cast<const uint4*>(dres + r * C + ch * 8);
+        }
       }
+      st = *reinterpret_cast<const float2*>(stats + r * 2);
     }
-    if (ok) {
-      const float2 st = *reinterpret_cast<const float2*>(stats + row * 2);
-      mean = st.x;
-      rstd = st.y;
-    }
+  };
+  issue(row);
+  for (; row - slot < M; row += stride) {     // uniform trip count over the block (row - slot is the block's first row)
+    const bool ok = row < M;
+    float xh[CPL][8], g[CPL][8], rr[CPL][8];
+    float s1 = 0.f, s2 = 0.f;
+    const float mean = st.x, rstd = st.y;
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
       const int ch = lane_in_row + j * lpr;
@@ -643,22 +680,24 @@ __global__ void __launch_bounds__(256, CPL == 1 ? 4 : 1) ln_bwd_kernel(const h16
         float xv[8], dv[8];
         unpack8(rx[j], xv);
         unpack8(rdy[j], dv);
+        if (dres) unpack8(rres[j], rr[j]);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           xh[j][k] = (xv[k] - mean) * rstd;
-          ag[j][k] += dv[k] * xh[j][k];
+          ag[j][k] = fmaf(dv[k], xh[j][k], ag[j][k]);
           ab[j][k] += dv[k];
           g[j][k] = dv[k] * gam[j][k];
           s1 += g[j][k];
-          s2 += g[j][k] * xh[j][k];
+          s2 = fmaf(g[j][k], xh[j][k], s2);
         }
       } else {
 #pragma unroll
         for (int k = 0; k < 8; ++k) xh[j][k] = g[j][k] = 0.f;
       }
     }
-    s1 = group_sum(s1, lpr) / C;
-    s2 = group_sum(s2, lpr) / C;
+    issue(row + stride);                        // next row's loads fly during the reduction and the store below
+    s1 = group_sum(s1, lpr) * inv_c;
+    s2 = group_sum(s2, lpr) * inv_c;
     if (ok) {
 #pragma unroll
       for (int j = 0; j < CPL; ++j) {
@@ -668,32 +707,39 @@ __global__ void __launch_bounds__(256, CPL == 1 ? 4 : 1) ln_bwd_kernel(const h16
 #pragma unroll
           for (int k = 0; k < 8; ++k) o[k] = rstd * (g[j][k] - s1 - xh[j][k] * s2);
           if (dres) {
-            float r[8];
-            unpack8(rres[j], r);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] += r[k];
+            for (int k = 0; k < 8; ++k) o[k] += rr[j][k];
           }
           *reinterpret_cast<uint4*>(dx + row * C + ch * 8) = pack8(o);
         }
       }
     }
   }
+  if (dgamma == nullptr) return;
+  float* mine = sm + static_cast<size_t>(slot) * 2 * C;
 #pragma unroll
   for (int j = 0; j < CPL; ++j) {
     const int ch = lane_in_row + j * lpr;
     if (ch < nchunks) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        atomicAdd(&sm[ch * 8 + k], ag[j][k]);
-        atomicAdd(&sm[C + ch * 8 + k], ab[j][k]);
-      }
+      *reinterpret_cast<float4*>(mine + ch * 8) = *reinterpret_cast<float4*>(&ag[j][0]);
+      *reinterpret_cast<float4*>(mine + ch * 8 + 4) = *reinterpret_cast<float4*>(&ag[j][4]);
+      *reinterpret_cast<float4*>(mine + C + ch * 8) = *reinterpret_cast<float4*>(&ab[j][0]);
+      *reinterpret_cast<float4*>(mine + C + ch * 8 + 4) = *reinterpret_cast<float4*>(&ab[j][4]);
     }
   }
   __syncthreads();
   const float ginv = gscale ? gscale[1] : 1.f;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    atomicAdd(&dgamma[c], sm[c] * ginv);
-    atomicAdd(&dbeta[c], sm[C + c] * ginv);
+  // columns [0, C) = dgamma, [C, 2C) = dbeta; when 2C < blockDim the row slots are split over blockDim / 2C thread groups
+  const int cols = 2 * C;
+  const int groups = blockDim.x >= cols ? blockDim.x / cols : 1;
+  for (int c0 = 0; c0 < cols; c0 += blockDim.x) {
+    const int c = c0 + static_cast<int>(threadIdx.x) % (groups > 1 ? cols : blockDim.x);
+    const int grp = groups > 1 ? threadIdx.x / cols : 0;
+    if (c < cols && grp < groups) {
+      float a = 0.f;
+      for (int r = grp; r < rows_per_block; r += groups) a += sm[static_cast<size_t>(r) * cols + c];
+      atomicAdd(c < C ? &dgamma[c] : &dbeta[c - C], a * ginv);
+    }
   }
 }
 
@@ -730,8 +776,20 @@ int launch_ln_bwd(const h16* x, const float* stats, const float* gamma, const h1
   ln_shape(C, &lpr, &cpl);
   const int rows_per_block = 256 / lpr;
   int grid = (M + rows_per_block - 1) / rows_per_block;
-  if (grid > 148 * 4) grid = 148 * 4;
-  const size_t smem = 2 * C * sizeof(float);
+  static const int exp_noatom = getenv("ENCDIFF_EXP_NOATOM") != nullptr;
+  static const int exp_cap = getenv("ENCDIFF_EXP_LN_CAP") ? atoi(getenv("ENCDIFF_EXP_LN_CAP")) : 148 * 2;
+  if (exp_noatom) dgamma = dbeta = nullptr;
+  if (grid > exp_cap) grid = exp_cap;
+  const size_t smem = static_cast<size_t>(rows_per_block) * 2 * C * sizeof(float);   // <= 64 KB (C = 1024)
+  if (smem > 48 * 1024) {
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(ln_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(ln_bwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      configured = true;
+    }
+  }
   switch (cpl) {
     case 1: launch_k(ln_bwd_kernel<1>, grid, 256, smem, s, x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
     case 2: launch_k(ln_bwd_kernel<2>, grid, 256, smem, s, x, stats, gamma, dy, dres, dx, dgamma, dbeta, gscale, M, C, lpr); break;
