@@ -36,6 +36,11 @@ SHAPES3D = dict(image_size=16, in_channels=3, out_channels=3, model_channels=64,
                 resblock_updown=True, use_spatial_transformer=True, context_dim=16, latent_unit=20)
 
 
+# BASELINE.json configs[4]: no yaml in the reference tree; synthesised as SURVEY.md section 7 suggests (twice the width)
+CELEBA64 = dict(SHAPES3D, model_channels=128)
+WORKLOADS = {"shapes3d": SHAPES3D, "celeba64": CELEBA64}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -156,12 +161,12 @@ def measured_traffic():
     return d.get("dram_bytes_per_launch"), d.get("algorithmic_bytes_per_launch")
 
 
-def build_model(dev):
+def build_model(dev, workload="shapes3d"):
     """Reference initialisation under seed 23 (main_val.py:173), then every all-zero parameter tensor (zero_module convs,
     norm biases) re-drawn N(0, 0.02^2) from Generator(1) so that outputs and gradients are non-trivial."""
     from encdiff_b200 import UNetModel
     torch.manual_seed(23)
-    m = UNetModel(**SHAPES3D)
+    m = UNetModel(**WORKLOADS[workload])
     g = torch.Generator().manual_seed(1)
     with torch.no_grad():
         for p in m.parameters():
@@ -202,7 +207,7 @@ def run_b200(args):
     from encdiff_b200 import _lib as edb_lib
     act = "bf16" if edb_lib.act_dtype() == torch.bfloat16 else "fp16"      # 16-bit operands, fp32 accumulate / masters
     B, K, W = args.batch, args.steps, args.warmup
-    model = build_model(dev)
+    model = build_model(dev, args.workload)
     trainer = DenoiserTrainer(model, lr=1e-4, use_cuda_graph=not args.no_graph)
     pk = peaks()
 
@@ -263,7 +268,7 @@ def run_b200(args):
     tot_ms = sum(v["ms_per_step"] for v in fam.values())
     sg = fam.get("sgemm", {"ms_per_step": 0.0, "gflop_per_step": 0.0, "launches_per_step": 0})
     achieved = sg["gflop_per_step"] / max(sg["ms_per_step"], 1e-9)        # GFLOP/ms == TFLOP/s
-    traffic, _ = measured_traffic()
+    traffic = measured_traffic()[0] if args.workload == "shapes3d" else None     # the ncu capture is of the Shapes3D step
     alg_bytes = sg.get("gbyte_per_step", 0.0) * 1e9 / max(sg["launches_per_step"], 1)
     roof = {"bound": "tensor", "kernel": "sgemm2_kernel (persistent tcgen05 implicit GEMM: conv3x3/1x1/linear fwd + dgrad)",
             "achieved": achieved, "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
@@ -274,20 +279,25 @@ def run_b200(args):
                          for k, v in sorted(fam.items(), key=lambda kv: -kv[1]["ms_per_step"])}}
 
     # ---- (4) DDIM-50 sampling throughput (configs[2] shape: batch-sharded, no communication) -----------------------
-    ddim = None
+    ddim = swap = None
     if not args.no_ddim:
         ddim = ddim50(model, dev, args.ddim_batch, dist_on, world)
+        swap = swap200(model, dev, args.swap_sources, dist_on, world)
 
     if rank != 0:
         if dist_on:
             torch.distributed.destroy_process_group()
         return
     img_s = world * B * K / (ms / 1e3)
+    wl = f"{args.workload}_train_step_b{B}_per_gpu"
+    # algorithmic work of the step: SURVEY.md's hook count for the Shapes3D UNet, the executor's own per-launch count
+    # (2 M N K of every GEMM it launched) for a synthesised configuration
+    gflop_img = GFLOP_TRAIN if args.workload == "shapes3d" else sum(v["gflop_per_step"] for v in fam.values()) / B
     e2e_img_s = world * B * K / (ms_e2e / 1e3)
     line = {"metric": METRIC, "value": img_s, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": act,
             "data": "synthetic",
-            "config": {"workload": "shapes3d_train_step_b256_per_gpu" if B == 256 else f"shapes3d_train_step_b{B}_per_gpu",
+            "config": {"workload": wl,
                        "global_batch": world * B, "parallelism": f"dp{world}", "cuda_graph": not args.no_graph,
                        "l2": "working set per step (activation workspace %.2f GB) exceeds the 126 MB L2; 4 rotating "
                              "input batches" % (model._lib.encdiff_unet_workspace_bytes(model._h, B, 1) / 1e9),
@@ -298,10 +308,13 @@ def run_b200(args):
             "gpu_launches": int(launches_per_step * K),
             "clocks": clk,
             "roofline": roof,
-            "step_tensor_frac": img_s / world * GFLOP_TRAIN / 1e3 / pk["tf_sustained"],
+            "step_tensor_frac": img_s / world * gflop_img / 1e3 / pk["tf_sustained"],
+            "gflop_per_img": gflop_img,
             "loss_first_last": [losses[0].item(), losses[-1].item()] if losses else None}
     if ddim is not None:
         line["ddim50"] = ddim
+    if swap is not None:
+        line["swap_ddim200"] = swap
     if world == 1 and not args.no_cpu:
         sec, cores = cpu_train_step_time(args.cpu_batch, 5, 1)
         line["cpu_baseline"] = {"value": args.cpu_batch / sec, "unit": UNIT, "cores": cores, "kind": "port",
@@ -330,6 +343,29 @@ def ddim50(model, dev, B, dist_on, world):
             "tensor_frac": img_s / world * 50 * GFLOP_FWD / 1e3 / pk["tf_sustained"]}
 
 
+def swap200(model, dev, n_src, dist_on, world):
+    """configs[3]: concept-token swap generation, DDIM-200, eta 0 (generate_swap_from_ckpt.py:103-105): n_src source images
+    per GPU x 20 swapped units folded into one batch of 20 * n_src samples per GPU; no communication in the loop."""
+    from encdiff_b200 import DDIMSampler
+    from encdiff_b200.diffusion import DenoiserHost
+    from encdiff_b200.swap import sample_swap
+    host = DenoiserHost(model).to(dev)
+    sampler = DDIMSampler(host)
+    L, dctx = model.latent_unit, model.context_dim
+    g = torch.Generator().manual_seed(9)
+    tokens = torch.randn(n_src, L, dctx, generator=g).to(dev)     # stands for warp(encoding(images)): frozen front end
+    model.eval()
+    run = lambda i: sample_swap(sampler, tokens, None, ddim_steps=200, eta=0., shape=(3, 16, 16), shard=False,
+                                reference_rng=False)
+    run(0)                                                         # warm-up: captures the step graph
+    reps = 2
+    ms = timed(run, reps, dist_on)
+    img_s = world * L * n_src * reps / (ms / 1e3)
+    pk = peaks()
+    return {"img_per_s": img_s, "sources_per_gpu": n_src, "folded_batch_per_gpu": L * n_src, "ddim_steps": 200,
+            "ms_per_call": ms / reps, "tensor_frac": img_s / world * 200 * GFLOP_FWD / 1e3 / pk["tf_sustained"]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -339,6 +375,9 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (BASELINE.json configs[1]: 256)")
     ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample of the same workload")
     ap.add_argument("--ddim-batch", type=int, default=128, help="per-GPU DDIM-50 batch (configs[2]: 1024 over 8 GPUs)")
+    ap.add_argument("--swap-sources", type=int, default=8, help="source images per GPU of the swap leg (x 20 units)")
+    ap.add_argument("--workload", default="shapes3d", choices=sorted(WORKLOADS),
+                    help="shapes3d = configs[1] (the headline); celeba64 = the synthesised configs[4] UNet")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-ddim", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

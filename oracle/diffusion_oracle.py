@@ -101,3 +101,17 @@ def ddim_sample(eps_fn: Callable[[torch.Tensor, torch.Tensor], torch.Tensor], x_
             inter['x_inter'].append(img)
             inter['pred_x0'].append(pred_x0)
     return img, inter
+
+
+def swap_conditionings(orc: torch.Tensor, latent_unit: int, warp: Callable[[torch.Tensor], torch.Tensor]):
+    """The conditioning of every run of the swap loop, literally as LatentDiffusion.log_images builds it
+    (ldm/models/diffusion/ddpm_enc.py:1525-1530): one entry per ``cdx``, each [N, latent_unit * context_dim]."""
+    out = []
+    for cdx in range(latent_unit):
+        swapped_c = orc.clone()
+        if len(swapped_c.shape) == 2:
+            swapped_c = torch.stack(swapped_c.chunk(latent_unit, dim=1), dim=1)
+        swapped_c[:, cdx] = swapped_c[0, cdx][None, :].repeat(orc.shape[0], 1)
+        swapped_c = warp(swapped_c)
+        out.append(swapped_c.reshape(orc.shape[0], -1))
+    return out

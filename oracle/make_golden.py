@@ -22,7 +22,11 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 # small architecture with the same block types (down/up ResBlocks, skip-conv ResBlocks, ST at two resolutions)
 TINY = UO.UNetConfig(image_size=8, model_channels=64, channel_mult=(1, 2), num_res_blocks=1,
                      attention_resolutions=(1, 2), latent_unit=20)
-CONFIGS = {"shapes3d": UO.SHAPES3D, "tiny": TINY}
+# BASELINE.json configs[4] (CelebA-64, KL-f4 first stage => 16x16x3 latent, larger UNet): the reference tree ships no yaml
+# for it, so the configuration is synthesised as SURVEY.md suggests: twice the Shapes3D width
+CELEBA64 = UO.UNetConfig(image_size=16, model_channels=128, channel_mult=(1, 2, 4, 4), num_res_blocks=2,
+                         attention_resolutions=(1, 2, 4), latent_unit=20)
+CONFIGS = {"shapes3d": UO.SHAPES3D, "tiny": TINY, "celeba64": CELEBA64}
 
 
 def seeded_inputs(cfg, B, seed):

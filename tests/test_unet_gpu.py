@@ -72,7 +72,7 @@ def test_forward_vs_golden(cuda_device, fixture, cfgname):
     assert err <= TOL.eps
 
 
-@pytest.mark.parametrize("cfgname,B", [("tiny", 5), ("shapes3d", 4)])
+@pytest.mark.parametrize("cfgname,B", [("tiny", 5), ("shapes3d", 4), ("celeba64", 2)])
 def test_forward_backward_vs_oracle(cuda_device, cfgname, B):
     cfg = CONFIGS[cfgname]
     m, params = make_model(cfg, cuda_device)
