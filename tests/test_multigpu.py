@@ -1,0 +1,101 @@
+"""The N > 1 paths on real GPUs (skipped on a single-GPU box; run with `gpurun --gpus 2`): batch-sharded data-parallel
+training step == the single-GPU step on the whole batch (one NCCL all-reduce of the flat gradient bucket), and the
+folded swap generation sharded over two ranks == the unsharded run (no communication inside the loop, one final gather).
+The host-side logic of both is also covered on CPU by tests/test_host_cpu.py::test_data_parallel_gloo_world2."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from oracle import unet_oracle as UO
+from oracle.make_golden import CONFIGS, seeded_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def _need_two():
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _model(cfg, dev):
+    from encdiff_b200 import UNetModel
+    m = UNetModel(image_size=cfg.image_size, in_channels=cfg.in_channels, out_channels=cfg.out_channels,
+                  model_channels=cfg.model_channels, attention_resolutions=list(cfg.attention_resolutions),
+                  num_res_blocks=cfg.num_res_blocks, channel_mult=list(cfg.channel_mult), num_heads=cfg.num_heads,
+                  use_scale_shift_norm=True, resblock_updown=True, use_spatial_transformer=True,
+                  context_dim=cfg.context_dim, latent_unit=cfg.latent_unit)
+    m.load_state_dict(UO.make_params(cfg, seed=1), strict=True)
+    return m.to(dev)
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from encdiff_b200 import DDIMSampler, parallel
+    from encdiff_b200.diffusion import DenoiserHost
+    from encdiff_b200.swap import sample_swap
+    from encdiff_b200.train import DenoiserTrainer
+    r, local, w = parallel.init_from_env("nccl")
+    dev = torch.device("cuda", local)
+    cfg = CONFIGS["tiny"]
+    # ---- training: each rank steps on its half of the batch ------------------------------------------------------
+    B = 8
+    x, t, ctx, noise = seeded_inputs(cfg, B, seed=31)
+    b, e = parallel.shard_range(B, r, w)
+    m = _model(cfg, dev).train()
+    tr = DenoiserTrainer(m, lr=1e-4, use_cuda_graph=False)
+    loss, _ = tr.step(x[b:e].to(dev), ctx[b:e].to(dev), t[b:e].to(dev), noise[b:e].to(dev))
+    grad = (m._gflat / w).cpu()                       # the all-reduced SUM; the optimiser kernel applies 1 / world
+    loss_mean = parallel.allreduce_mean_(loss.clone()).cpu()
+    # ---- swap generation: same codes on every rank, folded batch sharded ---------------------------------------------
+    host = DenoiserHost(_model(cfg, dev).eval()).to(dev)
+    L, N, S = cfg.latent_unit, 2, 6
+    g = torch.Generator().manual_seed(3)
+    tokens = torch.randn(N, L, cfg.context_dim, generator=g).to(dev)
+    xT = torch.randn(L, N, cfg.in_channels, cfg.image_size, cfg.image_size, generator=g).to(dev)
+    shape = (cfg.in_channels, cfg.image_size, cfg.image_size)
+    sharded = sample_swap(DDIMSampler(host), tokens, None, ddim_steps=S, eta=0., shape=shape, x_T=xT,
+                          reference_rng=False)
+    if r == 0:
+        torch.save({"grad": grad, "loss": loss_mean, "swap": sharded.cpu()}, out)
+    torch.distributed.barrier()
+    torch.distributed.destroy_process_group()
+
+
+def test_dp_step_and_sharded_swap_nccl_world2(cuda_device, tmp_path):
+    _need_two()
+    from encdiff_b200 import DDIMSampler
+    from encdiff_b200.diffusion import DenoiserHost
+    from encdiff_b200.swap import sample_swap
+    from encdiff_b200.train import DenoiserTrainer
+    out = str(tmp_path / "mg.pt")
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = torch.load(out)
+    cfg = CONFIGS["tiny"]
+    dev = cuda_device
+    x, t, ctx, noise = seeded_inputs(cfg, 8, seed=31)
+    m = _model(cfg, dev).train()
+    tr = DenoiserTrainer(m, lr=1e-4, use_cuda_graph=False)
+    loss, _ = tr.step(x.to(dev), ctx.to(dev), t.to(dev), noise.to(dev))
+    want = m._gflat.cpu()
+    err = ((got["grad"] - want).abs().max() / want.abs().max()).item()
+    print(f"dp2 vs single-GPU gradient: max rel err {err:.2e}; loss {got['loss'].item():.6f} vs {loss.item():.6f}")
+    assert err < 2e-3                                  # per-rank gradient range scales differ: 16-bit rounding only
+    assert abs(got["loss"].item() - loss.item()) < 1e-5
+    host = DenoiserHost(_model(cfg, dev).eval()).to(dev)
+    L, N, S = cfg.latent_unit, 2, 6
+    g = torch.Generator().manual_seed(3)
+    tokens = torch.randn(N, L, cfg.context_dim, generator=g).to(dev)
+    xT = torch.randn(L, N, cfg.in_channels, cfg.image_size, cfg.image_size, generator=g).to(dev)
+    whole = sample_swap(DDIMSampler(host), tokens, None, ddim_steps=S, eta=0.,
+                        shape=(cfg.in_channels, cfg.image_size, cfg.image_size), x_T=xT, reference_rng=False)
+    assert torch.equal(got["swap"], whole.cpu())       # a sample does not depend on its batch neighbours: bit-identical
