@@ -208,7 +208,8 @@ def run_b200(args):
     act = "bf16" if edb_lib.act_dtype() == torch.bfloat16 else "fp16"      # 16-bit operands, fp32 accumulate / masters
     B, K, W = args.batch, args.steps, args.warmup
     model = build_model(dev, args.workload)
-    trainer = DenoiserTrainer(model, lr=1e-4, use_cuda_graph=not args.no_graph)
+    trainer = DenoiserTrainer(model, lr=1e-4, use_cuda_graph=not args.no_graph,
+                              allreduce_chunks=int(os.environ.get("ENCDIFF_AR_CHUNKS", "1")))
     pk = peaks()
 
     # ---- (1) device-resident inputs: `value` ---------------------------------------------------------------------

@@ -66,10 +66,14 @@ class FlatAdamWEMA:
         h[3] = self.ema_decay()
         self.hyper.copy_(h, non_blocking=True)
 
-    def launch(self, flat_grad: torch.Tensor, grad_scale: float = 1.0):
+    def launch(self, flat_grad: torch.Tensor, grad_scale: float = 1.0, begin: int = 0, end: Optional[int] = None):
+        """AdamW (+EMA) over elements [begin, end) of the flat buffers (default: all of them)."""
         lib = _lib.load()
-        _lib.check(lib.encdiff_adamw_step_dev(self.flat.data_ptr(), flat_grad.data_ptr(), self.m.data_ptr(),
-                                              self.v.data_ptr(), _lib.ptr(self.ema), self.flat.numel(),
+        end = self.flat.numel() if end is None else end
+        off = 4 * begin
+        _lib.check(lib.encdiff_adamw_step_dev(self.flat.data_ptr() + off, flat_grad.data_ptr() + off,
+                                              self.m.data_ptr() + off, self.v.data_ptr() + off,
+                                              (self.ema.data_ptr() + off) if self.ema is not None else 0, end - begin,
                                               self.hyper.data_ptr(), self.betas[0], self.betas[1], self.eps, self.wd,
                                               float(grad_scale), _lib.current_stream()), "adamw_step_dev")
 
@@ -78,7 +82,7 @@ class DenoiserTrainer:
     """p_losses forward/backward + gradient all-reduce + AdamW/EMA for one ``encdiff_b200.UNetModel``."""
 
     def __init__(self, unet: UNetModel, lr=1e-4, weight_decay=0.01, use_ema=True, timesteps=1000,
-                 linear_start=0.0015, linear_end=0.0155, process_group=None, use_cuda_graph=True):
+                 linear_start=0.0015, linear_end=0.0155, process_group=None, use_cuda_graph=True, allreduce_chunks=1):
         self.unet = unet
         dev = next(unet.parameters()).device
         if dev.type != "cuda":
@@ -96,6 +100,11 @@ class DenoiserTrainer:
         if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
             self.world = torch.distributed.get_world_size(process_group)
         self.use_cuda_graph = use_cuda_graph
+        # world > 1: the flat gradient bucket is all-reduced in this many chunks and the optimiser kernel of chunk i runs
+        # while chunk i + 1 is still on the wire (1 = one all-reduce, then one optimiser launch).  Measured on 2 B200s
+        # (profiles/experiments/r01_allreduce_chunks.txt): 1 chunk 10.63 ms, 2: 10.64, 4: 10.69, 8: 10.81 -- the optimiser
+        # kernel and the NCCL kernel compete for the same HBM, so the default stays 1
+        self.allreduce_chunks = max(1, int(allreduce_chunks))
         self._static = None
         self._bound_once = False
 
@@ -126,7 +135,7 @@ class DenoiserTrainer:
               "cond": torch.empty(B, cond_dim, dtype=torch.float32, device=dev),
               "dcond": torch.empty(B, cond_dim, dtype=torch.float32, device=dev),
               "loss": torch.zeros(1, dtype=torch.float32, device=dev),
-              "g_fb": None, "g_opt": None, "key": None}
+              "g_fb": None, "g_opt": None, "g_pack": None, "key": None}
         return st
 
     def _fwd_bwd(self, st):
@@ -150,6 +159,26 @@ class DenoiserTrainer:
     def _opt(self, st):
         self.opt.launch(self.unet._gflat, 1.0 / self.world)
         self.unet.refresh_weights()
+
+    def _chunk_bounds(self):
+        n = self.unet._gflat.numel()
+        k = min(self.allreduce_chunks, max(1, n // (1 << 20)))
+        step = ((n + k - 1) // k + 1023) // 1024 * 1024          # chunk starts stay 4 KB aligned
+        return [(b, min(n, b + step)) for b in range(0, n, step)]
+
+    def _allreduce_and_opt(self, st):
+        """world > 1: NCCL sums chunk i + 1 of the gradient bucket (on NCCL's stream) while AdamW/EMA consumes chunk i;
+        the 16-bit re-pack of the operand arena follows the last chunk (captured graph when graphs are in use)."""
+        g = self.unet._gflat
+        bounds = self._chunk_bounds()
+        works = [torch.distributed.all_reduce(g[b:e], group=self.pg, async_op=True) for b, e in bounds]
+        for (b, e), w in zip(bounds, works):
+            w.wait()                                              # the current stream waits for this chunk only
+            self.opt.launch(g, 1.0 / self.world, b, e)
+        if st.get("g_pack") is not None:
+            st["g_pack"].replay()
+        else:
+            self.unet.refresh_weights()
 
     def step(self, x_start, cond, t, noise, lr: Optional[float] = None):
         """One optimisation step on a batch already on the device (or pinned host memory: the copies into the static
@@ -175,26 +204,41 @@ class DenoiserTrainer:
         prev = u.cache_packed_weights
         u.cache_packed_weights = True       # weights are re-packed right after each optimiser update instead
         try:
+            chunked = self.world > 1 and self.allreduce_chunks > 1
             if not self.use_cuda_graph:
                 self._fwd_bwd(st)
-                self._allreduce()
-                self._opt(st)
-            else:
-                if st["g_fb"] is None or st["key"] != u.plan_key():
-                    self._fwd_bwd(st)                       # eager warm-up (also a real step)
+                if chunked:
+                    self._allreduce_and_opt(st)
+                else:
                     self._allreduce()
                     self._opt(st)
+            else:
+                if st["g_fb"] is None or st["key"] != u.plan_key():
+                    st["g_pack"] = None
+                    self._fwd_bwd(st)                       # eager warm-up (also a real step)
+                    if chunked:
+                        self._allreduce_and_opt(st)
+                    else:
+                        self._allreduce()
+                        self._opt(st)
                     torch.cuda.current_stream().synchronize()
                     g_fb, g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g_fb):
                         self._fwd_bwd(st)
-                    with torch.cuda.graph(g_opt):
-                        self._opt(st)
-                    st["g_fb"], st["g_opt"], st["key"] = g_fb, g_opt, u.plan_key()
+                    with torch.cuda.graph(g_opt):           # chunked mode: only the re-pack (AdamW is launched per chunk)
+                        if chunked:
+                            u.refresh_weights()
+                        else:
+                            self._opt(st)
+                    st["g_fb"], st["key"] = g_fb, u.plan_key()
+                    st["g_opt"], st["g_pack"] = (None, g_opt) if chunked else (g_opt, None)
                 else:
                     st["g_fb"].replay()
-                    self._allreduce()
-                    st["g_opt"].replay()
+                    if chunked:
+                        self._allreduce_and_opt(st)
+                    else:
+                        self._allreduce()
+                        st["g_opt"].replay()
         finally:
             u.cache_packed_weights = prev
         return st["loss"], st["dcond"]
