@@ -275,10 +275,13 @@ int sgemm2_pick_bn(int m_tiles, int N, int num_sms, int nkb) {
 int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t stream) {
   int nkb = 0;
   for (int s = 0; s < p.nsrc; ++s) nkb += p.src_chunks[s] * p.src_taps[s];
-  // short-K GEMMs (1x1 / linear with K <= 256): a tile is 1-4 k-blocks, so a deep smem ring buys nothing; two small
+  // short-K GEMMs (1x1 / linear with K <= 576): a tile is 1-9 k-blocks, so a deep smem ring buys nothing; two small
   // CTAs per SM overlap one CTA's epilogue / fill / drain with the other's loads instead
   static const bool no_occ2 = getenv("ENCDIFF_NO_OCC2") != nullptr;
-  const bool shallow = nkb <= 4 && !no_occ2;
+  // threshold measured on the B = 256 step (k-blocks <= 4 / 9 / 18 / 36 / all: 10.33 / 10.27 / 10.28 / 10.40 / 10.46 ms):
+  // two 3-stage CTAs per SM equal one 6-stage CTA on the deep-K shapes -- the SM's L2 ingest is what is shared
+  static const int shallow_max = getenv("ENCDIFF_SHALLOW_KB") ? atoi(getenv("ENCDIFF_SHALLOW_KB")) : 9;
+  const bool shallow = nkb <= shallow_max && !no_occ2;
   switch (bn) {
     case 64: return shallow ? launch_sgemm2_t<64, 3, 2>(p, num_sms, stream) : launch_sgemm2_t<64, 6, 1>(p, num_sms, stream);
     case 128: return shallow ? launch_sgemm2_t<128, 2, 2>(p, num_sms, stream) : launch_sgemm2_t<128, 5, 1>(p, num_sms, stream);
