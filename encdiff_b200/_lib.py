@@ -40,6 +40,8 @@ PROTOTYPES = {
                                                c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                                c_int, c_int, c_void_p]),
     "encdiff_op_geglu": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p]),
+    "encdiff_concept_mlp_forward": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int, c_void_p]),
+    "encdiff_concept_mlp_backward": (c_int, [c_void_p] * 15 + [c_int, c_int, c_int, c_void_p]),
     "encdiff_unet_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
     "encdiff_unet_destroy": (c_int, [c_void_p]),
     "encdiff_unet_num_params": (c_int, [c_void_p]),

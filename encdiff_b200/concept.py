@@ -1,0 +1,123 @@
+"""The concept-token MLPs of EncDiff's encoder as one CUDA launch (the MLP half of it).
+
+Reference: ``Encoder4`` (ldm/modules/diffusionmodules/openaimodel_enc.py:991-1041) ends in ``latent_unit`` independent
+3-layer MLPs ``Linear(1, 64) - ELU - Linear(64, 128) - ELU - Linear(128, context_dim)`` held in ``self.net`` and run in a
+Python loop, both in ``forward`` (:1024-1031, after the convolutional trunk) and in ``warp`` (:1037-1041, used by the
+swap generation).  ``ConceptMLP`` owns the same parameters stacked over the units (so one kernel can walk them), reads
+and writes the reference's ``state_dict`` keys (``{i}.0.weight`` ... ``{i}.4.bias`` under the module's prefix, i.e.
+``net.{i}...`` when the module is registered as ``net``), and is differentiable w.r.t. codes and parameters.
+
+    enc.net_fast = ConceptMLP.from_reference(enc.net)       # enc: the reference's Encoder4
+    tokens = enc.net_fast(enc.encoding(images))             # == enc(images);   enc.net_fast(codes) == enc.warp(codes)
+
+The convolutional trunk of Encoder4 (4x4 stride-2 convolutions + BatchNorm) stays the reference's PyTorch code.
+No CPU fallback: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from . import _lib
+
+H1, H2 = 64, 128          # hidden widths, fixed by the reference (openaimodel_enc.py:1018-1023)
+
+
+class _ConceptFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, w3, b3):
+        lib = _lib.load()
+        B, L = x.shape
+        Dc = w3.shape[1]
+        y = torch.empty(B, L * Dc, dtype=torch.float32, device=x.device)
+        _lib.check(lib.encdiff_concept_mlp_forward(x.data_ptr(), w1.data_ptr(), b1.data_ptr(), w2.data_ptr(),
+                                                   b2.data_ptr(), w3.data_ptr(), b3.data_ptr(), y.data_ptr(), B, L, Dc,
+                                                   _lib.current_stream()), "concept_mlp_forward")
+        ctx.save_for_backward(x, w1, b1, w2, b2, w3, b3)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w1, b1, w2, b2, w3, b3 = ctx.saved_tensors
+        lib = _lib.load()
+        B, L = x.shape
+        Dc = w3.shape[1]
+        dy = dy.contiguous().float()
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        grads = [torch.zeros_like(t) for t in (w1, b1, w2, b2, w3, b3)]
+        _lib.check(lib.encdiff_concept_mlp_backward(x.data_ptr(), w1.data_ptr(), b1.data_ptr(), w2.data_ptr(),
+                                                    b2.data_ptr(), w3.data_ptr(), b3.data_ptr(), dy.data_ptr(),
+                                                    _lib.ptr(dx), *[g.data_ptr() for g in grads], B, L, Dc,
+                                                    _lib.current_stream()), "concept_mlp_backward")
+        return (dx, *grads)
+
+
+class ConceptMLP(nn.Module):
+    """``latent_unit`` MLPs 1 -> 64 -> 128 -> context_dim with stacked parameters; forward(codes [B, L] or [B, L, 1])
+    returns the tokens [B, L * context_dim] in the reference's ``th.cat(out, dim=1)`` order."""
+
+    def __init__(self, latent_unit: int, context_dim: int):
+        super().__init__()
+        if not 1 <= context_dim <= 32:
+            raise NotImplementedError("encdiff_b200.ConceptMLP: context_dim must be in 1..32")
+        self.latent_unit, self.context_dim = int(latent_unit), int(context_dim)
+        L, Dc = self.latent_unit, self.context_dim
+        # same construction order as the reference's ModuleList => same draws from the global generator
+        w1, b1, w2, b2, w3, b3 = [], [], [], [], [], []
+        for _ in range(L):
+            l0, l2, l4 = nn.Linear(1, H1), nn.Linear(H1, H2), nn.Linear(H2, Dc)
+            w1.append(l0.weight.detach().reshape(H1)); b1.append(l0.bias.detach())
+            w2.append(l2.weight.detach()); b2.append(l2.bias.detach())
+            w3.append(l4.weight.detach()); b3.append(l4.bias.detach())
+        self.w1 = nn.Parameter(torch.stack(w1))            # [L, 64]
+        self.b1 = nn.Parameter(torch.stack(b1))
+        self.w2 = nn.Parameter(torch.stack(w2))            # [L, 128, 64]
+        self.b2 = nn.Parameter(torch.stack(b2))
+        self.w3 = nn.Parameter(torch.stack(w3))            # [L, Dc, 128]
+        self.b3 = nn.Parameter(torch.stack(b3))
+        self._register_state_dict_hook(ConceptMLP._to_reference_keys)
+        self._register_load_state_dict_pre_hook(self._from_reference_keys)
+
+    # ---- the reference's state_dict layout: '{i}.0.weight' [64, 1], '{i}.0.bias', '{i}.2.*', '{i}.4.*' -------------------
+    _MAP = (("w1", "0.weight"), ("b1", "0.bias"), ("w2", "2.weight"), ("b2", "2.bias"), ("w3", "4.weight"),
+            ("b3", "4.bias"))
+
+    @staticmethod
+    def _to_reference_keys(module, state, prefix, local_metadata):
+        for mine, ref in ConceptMLP._MAP:
+            stacked = state.pop(prefix + mine)
+            for i in range(module.latent_unit):
+                t = stacked[i]
+                state[f"{prefix}{i}.{ref}"] = t.reshape(H1, 1) if mine == "w1" else t
+        return state
+
+    def _from_reference_keys(self, state, prefix, local_metadata, strict, missing, unexpected, errors):
+        for mine, ref in ConceptMLP._MAP:
+            keys = [f"{prefix}{i}.{ref}" for i in range(self.latent_unit)]
+            if all(k in state for k in keys):
+                parts = [state.pop(k) for k in keys]
+                if mine == "w1":
+                    parts = [p.reshape(H1) for p in parts]
+                state[prefix + mine] = torch.stack(parts)
+
+    @classmethod
+    def from_reference(cls, net: nn.ModuleList) -> "ConceptMLP":
+        """Build from (and copy the weights of) the reference's ``Encoder4.net`` ModuleList."""
+        m = cls(len(net), net[0][4].out_features)
+        m.load_state_dict(net.state_dict(), strict=True)
+        return m.to(net[0][0].weight.device)
+
+    def forward(self, codes: torch.Tensor) -> torch.Tensor:
+        if codes.dim() == 3:
+            codes = codes.reshape(codes.shape[0], -1)
+        if codes.dim() != 2 or codes.shape[1] != self.latent_unit:
+            raise ValueError(f"ConceptMLP: expected codes [B, {self.latent_unit}], got {tuple(codes.shape)}")
+        if not codes.is_cuda or not self.w1.is_cuda:
+            raise RuntimeError("encdiff_b200.ConceptMLP runs on CUDA tensors only (no CPU fallback)")
+        return _ConceptFn.apply(codes.contiguous().float(), self.w1, self.b1, self.w2, self.b2, self.w3, self.b3)
+
+    def warp(self, x: torch.Tensor) -> torch.Tensor:
+        """Encoder4.warp (openaimodel_enc.py:1037-1041): [B, L, 1] codes give [B, L, context_dim], [B, L] codes give
+        [B, L * context_dim] (what ``x[:, i][:, None]`` and ``th.cat(out, dim=1)`` produce in the reference)."""
+        y = self.forward(x)
+        return y.reshape(x.shape[0], self.latent_unit, self.context_dim) if x.dim() == 3 else y

@@ -197,6 +197,54 @@ extern "C" int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, c
   return EDB_OK;
 }
 
+static ConceptParams concept_params(const float* x, const float* w1, const float* b1, const float* w2, const float* b2,
+                                    const float* w3, const float* b3, int B, int L, int Dc) {
+  ConceptParams p;
+  memset(&p, 0, sizeof(p));
+  p.x = x;
+  p.w1 = w1;
+  p.b1 = b1;
+  p.w2 = w2;
+  p.b2 = b2;
+  p.w3 = w3;
+  p.b3 = b3;
+  p.B = B;
+  p.L = L;
+  p.Dc = Dc;
+  return p;
+}
+
+extern "C" int encdiff_concept_mlp_forward(const float* x, const float* w1, const float* b1, const float* w2,
+                                           const float* b2, const float* w3, const float* b3, float* y, int B, int L,
+                                           int Dc, void* stream) {
+  EDB_REQUIRE(x && w1 && b1 && w2 && b2 && w3 && b3 && y, "concept_mlp_forward: null argument");
+  EDB_REQUIRE(Dc >= 1 && Dc <= 32, "concept_mlp: context_dim must be in 1..32");
+  ConceptParams p = concept_params(x, w1, b1, w2, b2, w3, b3, B, L, Dc);
+  p.y = y;
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_concept_mlp_fwd(p, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
+extern "C" int encdiff_concept_mlp_backward(const float* x, const float* w1, const float* b1, const float* w2,
+                                            const float* b2, const float* w3, const float* b3, const float* dy,
+                                            float* dx, float* dw1, float* db1, float* dw2, float* db2, float* dw3,
+                                            float* db3, int B, int L, int Dc, void* stream) {
+  EDB_REQUIRE(x && w1 && b1 && w2 && b2 && w3 && b3 && dy && dw1 && db1 && dw2 && db2 && dw3 && db3,
+              "concept_mlp_backward: null argument");
+  EDB_REQUIRE(Dc >= 1 && Dc <= 32, "concept_mlp: context_dim must be in 1..32");
+  ConceptParams p = concept_params(x, w1, b1, w2, b2, w3, b3, B, L, Dc);
+  p.dy = dy;
+  p.dx = dx;
+  p.dw1 = dw1;
+  p.db1 = db1;
+  p.dw2 = dw2;
+  p.db2 = db2;
+  p.dw3 = dw3;
+  p.db3 = db3;
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_concept_mlp_bwd(p, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}
+
 extern "C" int encdiff_op_geglu(const void* g, void* out, long long M, int inner, void* stream) {
   EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_geglu_fwd(static_cast<const h16*>(g), static_cast<h16*>(out), M, inner,
                                                            static_cast<cudaStream_t>(stream))));

@@ -131,6 +131,23 @@ int launch_ddim_update_indexed(const float* x, const float* e_t, const float* no
                                const int* idx, float temperature, float* x_prev, float* pred_x0, long long n,
                                cudaStream_t s);
 
+// ---- concept-token MLPs (Encoder4.warp, openaimodel_enc.py:1017-1041): latent_unit independent MLPs 1 -> 64 -> 128 -> Dc ----
+// all fp32; parameters stacked over the units; x [B, L] scalar codes, y [B, L * Dc] tokens (unit-major, the reference's
+// th.cat(out, dim=1)); backward ACCUMULATES into the d* parameter gradients (fp32 atomics) and overwrites dx (may be null)
+struct ConceptParams {
+  const float* x;
+  const float *w1, *b1;      // [L, 64], [L, 64]          (Linear(1, 64).weight squeezed)
+  const float *w2, *b2;      // [L, 128, 64], [L, 128]
+  const float *w3, *b3;      // [L, Dc, 128], [L, Dc]
+  float* y;
+  const float* dy;
+  float* dx;
+  float *dw1, *db1, *dw2, *db2, *dw3, *db3;
+  int B, L, Dc;
+};
+int launch_concept_mlp_fwd(const ConceptParams& p, cudaStream_t s);
+int launch_concept_mlp_bwd(const ConceptParams& p, cudaStream_t s);
+
 // ---- weight packing ---------------------------------------------------------------------------------------------
 struct PackEntry {
   const float* src;      // fp32 parameter, reference layout [rows, cin, taps]

@@ -85,6 +85,18 @@ int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, const float*
 /* GEGLU (attention.py:37-45): g h16 [M, 2*inner] (value | gate) -> out h16 [M, inner] = value * gelu_erf(gate)  */
 int encdiff_op_geglu(const void* g, void* out, long long M, int inner, void* stream);
 
+/* Concept-token MLPs of the encoder: replaces the per-unit Python loop of Encoder4.forward / Encoder4.warp
+ * (ldm/modules/diffusionmodules/openaimodel_enc.py:1024-1041: for i in range(latent_unit): net[i](x[:, i][:, None]);
+ * th.cat(out, dim=1)) with one launch.  All fp32 device pointers; parameters stacked over the L units:
+ * w1/b1 [L,64] (Linear(1,64)), w2 [L,128,64], b2 [L,128], w3 [L,Dc,128], b3 [L,Dc]; x [B,L]; y [B,L*Dc].           */
+int encdiff_concept_mlp_forward(const float* x, const float* w1, const float* b1, const float* w2, const float* b2,
+                                const float* w3, const float* b3, float* y, int B, int L, int Dc, void* stream);
+/* Backward of the above for dy [B,L*Dc]: overwrites dx [B,L] (may be NULL) and ADDS to dw1..db3 (same shapes as the
+ * parameters; the caller zeroes them); the hidden layers are recomputed from x.                                       */
+int encdiff_concept_mlp_backward(const float* x, const float* w1, const float* b1, const float* w2, const float* b2,
+                                 const float* w3, const float* b3, const float* dy, float* dx, float* dw1, float* db1,
+                                 float* dw2, float* db2, float* dw3, float* db3, int B, int L, int Dc, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Model level: the UNet denoiser.
  *   Replaces UNetModel.__init__/forward (ldm/modules/diffusionmodules/openaimodel_enc.py:443-748) and everything
