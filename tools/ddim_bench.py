@@ -1,4 +1,5 @@
-"""DDIM-50 throughput only (the bench.py ddim50 leg).  usage: python tools/ddim_bench.py [B]"""
+"""DDIM-50 throughput only (the `ddim50` leg of bench.py).  usage: python tools/ddim_bench.py [batch]"""
+import json
 import os
 import sys
 
@@ -9,5 +10,4 @@ import bench  # noqa: E402
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 128
 dev = torch.device("cuda:0")
-model = bench.build_model(dev)
-print(B, bench.ddim50(model, dev, B, False, 1))
+print(json.dumps(bench.ddim50(bench.build_model(dev), dev, B, False, 1)))
