@@ -113,11 +113,13 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
             for (int c = 0; c < p.src_chunks[s]; ++c, ++kb, ++it) {
               const int st = it % STAGES;
               const uint32_t ph = (it / STAGES) & 1;
-              mbar_wait(&empty_bar[st], ph ^ 1);
+              if (p.debug & 16) mbar_wait_spin(&empty_bar[st], ph ^ 1);
+              else mbar_wait(&empty_bar[st], ph ^ 1);
               uint8_t* sa = smem + st * STAGE_BYTES;
-              mbar_arrive_expect_tx(&full_bar[st], STAGE_BYTES);
-              tma_load_4d(sa, &p.amap[s], &full_bar[st], c * kChunk2, dx, y0 + dy, b0);
-              tma_load_2d(sa + kABytes2, &p.bmap, &full_bar[st], kb * kChunk2, n_tile * BN);
+              const bool la = !(p.debug & 2), lb = !(p.debug & 4);
+              mbar_arrive_expect_tx(&full_bar[st], (la ? kABytes2 : 0) + (lb ? B_BYTES : 0));
+              if (la) tma_load_4d(sa, &p.amap[s], &full_bar[st], c * kChunk2, dx, y0 + dy, b0);
+              if (lb) tma_load_2d(sa + kABytes2, &p.bmap, &full_bar[st], kb * kChunk2, n_tile * BN);
             }
           }
         }
@@ -135,14 +137,17 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int st = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
-          mbar_wait(&full_bar[st], ph);
+          if (p.debug & 16) mbar_wait_spin(&full_bar[st], ph);
+          else mbar_wait(&full_bar[st], ph);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
           const uint64_t da = make_sdesc(sa, 16, 1024);
           const uint64_t db = make_sdesc(sa + kABytes2, 16, 1024);
 #pragma unroll
-          for (int k = 0; k < kChunk2 / 16; ++k) umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
-          umma_commit(&empty_bar[st]);
+          for (int k = 0; k < kChunk2 / 16; ++k)
+            if (!(p.debug & 1)) umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          if ((p.debug & 64) && (kb & 1) && kb + 1 < nkb) mbar_arrive(&empty_bar[st]);   // pacing experiment: half the commits
+          else umma_commit(&empty_bar[st]);
         }
         umma_commit(&tfull[acc]);
       }
@@ -177,7 +182,7 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
 #pragma unroll 1
       for (int pn = 0; pn < PANELS; ++pn) {
         const int n0 = n_tile * BN + pn * 64;
-        if (n0 >= p.N) break;                    // uniform over the CTA
+        if (n0 >= p.N || (p.debug & 32)) break;  // uniform over the CTA (debug 32: pacing experiment without epilogue work)
         float v[64];
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + pn * 64;
         tmem_ld32(taddr, v);
