@@ -82,7 +82,9 @@ class UNetConfigStruct(C.Structure):
 
 
 def lib_path() -> Path:
-    return _build.LIB_PATH
+    """The in-tree library; ENCDIFF_B200_LIB points at another build of the same ABI (A/B timing of two builds on one box)."""
+    alt = os.environ.get("ENCDIFF_B200_LIB")
+    return Path(alt) if alt else _build.LIB_PATH
 
 
 def load(build_if_missing: bool = True):

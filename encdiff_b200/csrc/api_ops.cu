@@ -58,7 +58,6 @@ extern "C" int encdiff_op_sgemm(int nsrc, const void* const* a_ptrs, const int* 
       q.res = res;
       q.ldres = ldres;
       q.act = act;
-      q.debug = getenv("ENCDIFF_GEMM_DEBUG") ? atoi(getenv("ENCDIFF_GEMM_DEBUG")) : 0;   // tools/exp_gemm_pacing.py
       EDB_CHECK_CUDA(static_cast<cudaError_t>(launch_sgemm2(q, bn2, sms, static_cast<cudaStream_t>(stream))));
       return EDB_OK;
     }

@@ -61,8 +61,6 @@ struct Sgemm2Params {
   const void* res;      // 16-bit [M, ldres] or null
   int ldres;
   int act;
-  int debug;            // tools/exp_gemm_pacing.py only (ENCDIFF_GEMM_DEBUG): 1 skip the MMAs, 2 skip the A loads, 4 skip the B
-                        // loads, 16 spin on mbarrier.test_wait in the producer / MMA threads.  0 in the product.
 };
 
 struct WgradParams {

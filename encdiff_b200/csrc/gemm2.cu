@@ -46,11 +46,14 @@ __device__ __forceinline__ void tile_origin2(const TileGeom& g, int tile, int& b
   }
 }
 
-template <int BN, int STAGES, int OCC>
+// KPS = 64-wide k-blocks per pipeline stage: one full/empty barrier hand-shake and one tcgen05.commit per KPS k-blocks
+// (the hand-shake costs 100-180 ns and does not overlap with the MMAs, profiles/experiments/r01_gemm_pacing.txt)
+template <int BN, int STAGES, int OCC, int KPS = 1>
 __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant__ Sgemm2Params p) {
   pdl_launch_dependents();
   constexpr int B_BYTES = BN * kChunk2 * 2;
-  constexpr int STAGE_BYTES = kABytes2 + B_BYTES;
+  constexpr int SLOT_BYTES = kABytes2 + B_BYTES;        // one k-block: A box + weight box
+  constexpr int STAGE_BYTES = KPS * SLOT_BYTES;
   constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
   constexpr int PANELS = BN / 64;
   extern __shared__ uint8_t smem_raw[];
@@ -96,12 +99,16 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
 
   if (warp == 0) {
     if (lane == 0) {
-      uint32_t it = 0;   // running k-block counter across tiles
+      // The producer and the MMA issuer are single threads whose loop bodies are on the critical path of every k-block
+      // (profiles/experiments/r01_gemm_pacing.txt): the ring position (stage, phase) is carried incrementally -- no
+      // division / modulo by STAGES -- and nothing is done per k-block that can be done per stage or per tile.
+      int st = 0;
+      uint32_t ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int m_tile = t / n_tiles, n_tile = t - m_tile * n_tiles;
         int b0, y0;
         tile_origin2(p.g, m_tile, b0, y0);
-        int kb = 0;
+        int kb = 0, slot = 0, in_stage = 0;
         for (int s = 0; s < p.nsrc; ++s) {
           const int taps = p.src_taps[s];
           for (int tp = 0; tp < taps; ++tp) {
@@ -110,16 +117,23 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
               dy = (tp / 3 - 1) * p.tap_sign;
               dx = (tp % 3 - 1) * p.tap_sign;
             }
-            for (int c = 0; c < p.src_chunks[s]; ++c, ++kb, ++it) {
-              const int st = it % STAGES;
-              const uint32_t ph = (it / STAGES) & 1;
-              if (p.debug & 16) mbar_wait_spin(&empty_bar[st], ph ^ 1);
-              else mbar_wait(&empty_bar[st], ph ^ 1);
-              uint8_t* sa = smem + st * STAGE_BYTES;
-              const bool la = !(p.debug & 2), lb = !(p.debug & 4);
-              mbar_arrive_expect_tx(&full_bar[st], (la ? kABytes2 : 0) + (lb ? B_BYTES : 0));
-              if (la) tma_load_4d(sa, &p.amap[s], &full_bar[st], c * kChunk2, dx, y0 + dy, b0);
-              if (lb) tma_load_2d(sa + kABytes2, &p.bmap, &full_bar[st], kb * kChunk2, n_tile * BN);
+            const int chunks = p.src_chunks[s];
+            for (int c = 0; c < chunks; ++c, ++kb) {
+              if (slot == 0) {      // first k-block of a stage: wait for the slot, announce the bytes of the whole stage
+                mbar_wait(&empty_bar[st], ph ^ 1);
+                in_stage = nkb - kb < KPS ? nkb - kb : KPS;
+                mbar_arrive_expect_tx(&full_bar[st], in_stage * SLOT_BYTES);
+              }
+              uint8_t* sa = smem + st * STAGE_BYTES + slot * SLOT_BYTES;
+              tma_load_4d(sa, &p.amap[s], &full_bar[st], c * kChunk2, dx, y0 + dy, b0);
+              tma_load_2d(sa + kABytes2, &p.bmap, &full_bar[st], kb * kChunk2, n_tile * BN);
+              if (++slot == in_stage) {
+                slot = 0;
+                if (++st == STAGES) {
+                  st = 0;
+                  ph ^= 1;
+                }
+              }
             }
           }
         }
@@ -128,26 +142,35 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(BN, false, false);
-      uint32_t it = 0, lt = 0;
+      uint32_t lt = 0, ph = 0;
+      int st = 0;
+      // shared-memory descriptors of slot 0 of stage 0; a descriptor's address field counts 16-byte units
+      const uint64_t da0 = make_sdesc(smem_u32(smem), 16, 1024);
+      const uint64_t db0 = make_sdesc(smem_u32(smem) + kABytes2, 16, 1024);
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
         const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
         mbar_wait(&tempty[acc], aph ^ 1);   // the epilogue has drained this accumulator stage
         tc_fence_after();
         const uint32_t tacc = tmem_base + acc * BN;
-        for (int kb = 0; kb < nkb; ++kb, ++it) {
-          const int st = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          if (p.debug & 16) mbar_wait_spin(&full_bar[st], ph);
-          else mbar_wait(&full_bar[st], ph);
+        for (int kb = 0; kb < nkb; kb += KPS) {
+          mbar_wait(&full_bar[st], ph);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
-          const uint64_t da = make_sdesc(sa, 16, 1024);
-          const uint64_t db = make_sdesc(sa + kABytes2, 16, 1024);
+          const int nk = nkb - kb < KPS ? nkb - kb : KPS;
+          const uint64_t soff = static_cast<uint64_t>(st * (STAGE_BYTES >> 4));
 #pragma unroll
-          for (int k = 0; k < kChunk2 / 16; ++k)
-            if (!(p.debug & 1)) umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
-          if ((p.debug & 64) && (kb & 1) && kb + 1 < nkb) mbar_arrive(&empty_bar[st]);   // pacing experiment: half the commits
-          else umma_commit(&empty_bar[st]);
+          for (int j = 0; j < KPS; ++j) {
+            if (j < nk) {
+              const uint64_t da = da0 + soff + j * (SLOT_BYTES >> 4);
+              const uint64_t db = db0 + soff + j * (SLOT_BYTES >> 4);
+#pragma unroll
+              for (int k = 0; k < kChunk2 / 16; ++k) umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, ((kb + j) | k) ? 1u : 0u);
+            }
+          }
+          umma_commit(&empty_bar[st]);
+          if (++st == STAGES) {
+            st = 0;
+            ph ^= 1;
+          }
         }
         umma_commit(&tfull[acc]);
       }
@@ -182,7 +205,7 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
 #pragma unroll 1
       for (int pn = 0; pn < PANELS; ++pn) {
         const int n0 = n_tile * BN + pn * 64;
-        if (n0 >= p.N || (p.debug & 32)) break;  // uniform over the CTA (debug 32: pacing experiment without epilogue work)
+        if (n0 >= p.N) break;                    // uniform over the CTA
         float v[64];
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + pn * 64;
         tmem_ld32(taddr, v);
@@ -233,12 +256,12 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
   if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-template <int BN, int STAGES, int OCC>
+template <int BN, int STAGES, int OCC, int KPS = 1>
 static int launch_sgemm2_t(const Sgemm2Params& p, int num_sms, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kABytes2 + BN * kChunk2 * 2) + 2 * kPanelBytes + 2 * BN * 4 + 1024 + 256;
+  constexpr int smem = STAGES * KPS * (kABytes2 + BN * kChunk2 * 2) + 2 * kPanelBytes + 2 * BN * 4 + 1024 + 256;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(sgemm2_kernel<BN, STAGES, OCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(sgemm2_kernel<BN, STAGES, OCC, KPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = true;
   }
@@ -251,7 +274,7 @@ static int launch_sgemm2_t(const Sgemm2Params& p, int num_sms, cudaStream_t stre
     fprintf(stderr, "GEMMLOG sgemm2 M=%d N=%d K=%d taps=%d bn=%d st=%d grid=%d tiles=%d\n", p.M, p.N, kb * 64, p.src_taps[0], BN,
             STAGES, grid, tiles);
   }
-  launch_k(sgemm2_kernel<BN, STAGES, OCC>, grid, 192, smem, stream, p);
+  launch_k(sgemm2_kernel<BN, STAGES, OCC, KPS>, grid, 192, smem, stream, p);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -287,9 +310,19 @@ int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t strea
   // two 3-stage CTAs per SM equal one 6-stage CTA on the deep-K shapes -- the SM's L2 ingest is what is shared
   static const int shallow_max = getenv("ENCDIFF_SHALLOW_KB") ? atoi(getenv("ENCDIFF_SHALLOW_KB")) : 9;
   const bool shallow = nkb <= shallow_max && !no_occ2;
+  static const int kps = getenv("ENCDIFF_KPS") ? atoi(getenv("ENCDIFF_KPS")) : 2;
+  static const int kps128 = getenv("ENCDIFF_KPS128") ? atoi(getenv("ENCDIFF_KPS128")) : 2;
   switch (bn) {
-    case 64: return shallow ? launch_sgemm2_t<64, 3, 2>(p, num_sms, stream) : launch_sgemm2_t<64, 6, 1>(p, num_sms, stream);
-    case 128: return shallow ? launch_sgemm2_t<128, 2, 2>(p, num_sms, stream) : launch_sgemm2_t<128, 5, 1>(p, num_sms, stream);
+    case 64:
+      if (shallow) return launch_sgemm2_t<64, 3, 2>(p, num_sms, stream);
+      if (kps == 3) return launch_sgemm2_t<64, 2, 1, 3>(p, num_sms, stream);
+      if (kps == 2) return launch_sgemm2_t<64, 3, 1, 2>(p, num_sms, stream);
+      return launch_sgemm2_t<64, 6, 1>(p, num_sms, stream);
+    case 128:
+      if (shallow) return launch_sgemm2_t<128, 2, 2>(p, num_sms, stream);
+      if (kps128 == 2) return launch_sgemm2_t<128, 2, 1, 2>(p, num_sms, stream);
+      if (kps128 == 3) return launch_sgemm2_t<128, 2, 1, 3>(p, num_sms, stream);
+      return launch_sgemm2_t<128, 5, 1>(p, num_sms, stream);
     case 256: return launch_sgemm2_t<256, 3, 1>(p, num_sms, stream);
     default: return static_cast<int>(cudaErrorInvalidValue);
   }
