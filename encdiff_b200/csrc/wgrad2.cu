@@ -134,7 +134,10 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
 
   if (warp == 0) {
     if (lane == 0) {
-      uint32_t it = 0;
+      // single-thread loop on the critical path of every reduction step (profiles/experiments/r01_gemm_pacing.txt): ring
+      // position and tile origin are carried incrementally (no division per step)
+      int st = 0;
+      uint32_t ph = 0;
       int cur = 0;
       for (int gi = blockIdx.x; gi < total; gi += gridDim.x) {
         int item;
@@ -149,17 +152,29 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
         }
         const int t_begin = w.split * p.tiles_per_split;
         const int t_end = min(p.m_tiles, t_begin + p.tiles_per_split);
-        for (int t = t_begin; t < t_end; ++t, ++it) {
-          const int st = it % kWStages;
-          const uint32_t ph = (it / kWStages) & 1;
-          int b0, y0;
-          w_tile_origin(g, t, b0, y0);
+        int b0, y0;
+        w_tile_origin(g, t_begin, b0, y0);
+        const int q_col = w.q_tile * kWBN;
+        for (int t = t_begin; t < t_end; ++t) {
           mbar_wait(&empty_bar[st], ph ^ 1);
           uint8_t* sp = smem + st * kWStageBytes;
           mbar_arrive_expect_tx(&full_bar[st], kWStageBytes);
           tma_load_4d(sp, &p.pmap, &full_bar[st], p_col, 0, y0, b0);
           tma_load_4d(sp + kBox, &p.pmap, &full_bar[st], p_col + 64, 0, y0, b0);
-          tma_load_4d(sp + 2 * kBox, &p.qmap, &full_bar[st], w.q_tile * kWBN, dx, y0 + dy, b0);
+          tma_load_4d(sp + 2 * kBox, &p.qmap, &full_bar[st], q_col, dx, y0 + dy, b0);
+          if (g.tiles_per_img > 1) {          // next 128-pixel tile: further down the same image, or the next image(s)
+            y0 += g.box_h;
+            if (y0 >= g.H) {
+              y0 = 0;
+              ++b0;
+            }
+          } else {
+            b0 += g.box_b;
+          }
+          if (++st == kWStages) {
+            st = 0;
+            ph ^= 1;
+          }
         }
       }
     }
@@ -167,8 +182,16 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(kWN, true, true);
       const uint32_t ones_addr = smem_u32(ones);
-      uint32_t it = 0, lt = 0;
+      uint32_t lt = 0, ph = 0;
+      int st = 0;
       int cur = 0;
+      // descriptors of stage 0, reduction step 0.  A (dY): second 64-channel block kBox away.  B (X | ones): the second N
+      // block is the shared ones box, i.e. its leading-dimension offset is (ones - X box) and shrinks by one stage size
+      // per stage; both descriptor fields count 16-byte units, so a stage is a constant added / subtracted.
+      const uint32_t sp0 = smem_u32(smem), sq0 = sp0 + 2 * kBox;
+      const uint64_t da0 = make_sdesc(sp0, kBox, 1024);
+      const uint64_t db0 = make_sdesc(sq0, ones_addr - sq0, 1024);
+      constexpr uint64_t kStageUnits = kWStageBytes >> 4;
       for (int gi = blockIdx.x; gi < total; gi += gridDim.x, ++lt) {
         int item;
         const Wgrad2Params& p = src.at(gi, cur, item);
@@ -179,22 +202,20 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
         mbar_wait(&tempty[acc], aph ^ 1);
         tc_fence_after();
         const uint32_t tacc = tmem_base + acc * 128;
-        for (int i = 0; i < nsteps; ++i, ++it) {
-          const int st = it % kWStages;
-          const uint32_t ph = (it / kWStages) & 1;
+        for (int i = 0; i < nsteps; ++i) {
           mbar_wait(&full_bar[st], ph);
           tc_fence_after();
-          const uint32_t sp = smem_u32(smem + st * kWStageBytes);
-          const uint32_t sq = sp + 2 * kBox;
+          const uint64_t so = static_cast<uint64_t>(st) * kStageUnits;
+          const uint64_t da = da0 + so;
+          const uint64_t db = db0 + so - (so << 16);
 #pragma unroll
-          for (int k = 0; k < kPix / 16; ++k) {
-            // 16 pixels (the reduction) = 16 rows of 128 B = 2048 B per MMA step.  A: second 64-channel block kBox
-            // away.  B: second N block = the shared ones box (same k offset inside it).
-            const uint64_t da = make_sdesc(sp + k * 2048, kBox, 1024);
-            const uint64_t db = make_sdesc(sq + k * 2048, ones_addr - sq, 1024);
-            umma_f16(tacc, da, db, idesc, (i | k) ? 1u : 0u);
-          }
+          for (int k = 0; k < kPix / 16; ++k)   // 16 pixels (the reduction) = 16 rows of 128 B = 2048 B per MMA step
+            umma_f16(tacc, da + k * (2048 >> 4), db + k * (2048 >> 4), idesc, (i | k) ? 1u : 0u);
           umma_commit(&empty_bar[st]);
+          if (++st == kWStages) {
+            st = 0;
+            ph ^= 1;
+          }
         }
         umma_commit(&tfull[acc]);
       }
