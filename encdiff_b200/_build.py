@@ -48,9 +48,14 @@ def _digest(paths) -> str:
     return h.hexdigest()
 
 
+def _headers() -> list[Path]:
+    """Everything a .cu may #include: *.cuh, *.inc (unet_bwd.inc is the whole backward launch sequence) and the ABI."""
+    return list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inc")) + [PKG_DIR.parent / "include" / "encdiff_b200.h"]
+
+
 def is_fresh() -> bool:
     stamp = BUILD_DIR / "stamp"
-    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + [PKG_DIR.parent / "include" / "encdiff_b200.h"]
+    deps = list(CSRC.glob("*.cu")) + _headers()
     return LIB_PATH.exists() and stamp.exists() and stamp.read_text() == _digest(deps)
 
 
@@ -61,7 +66,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     nvcc = _nvcc()
     BUILD_DIR.mkdir(exist_ok=True)
     srcs = sources()
-    headers = list(CSRC.glob("*.cuh")) + [PKG_DIR.parent / "include" / "encdiff_b200.h"]
+    headers = _headers()
     hdig = _digest(headers)
 
     def compile_one(src: Path):

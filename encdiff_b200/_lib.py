@@ -69,6 +69,7 @@ PROTOTYPES = {
                                    C.c_float, C.c_float, C.c_float, c_int, C.c_float, c_void_p]),
     "encdiff_adamw_step_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p, C.c_float,
                                        C.c_float, C.c_float, C.c_float, C.c_float, c_void_p]),
+    "encdiff_adamw_hyper_advance": (c_int, [c_void_p, c_void_p, c_void_p, C.c_float, C.c_float, C.c_float, c_void_p]),
 }
 
 

@@ -242,3 +242,11 @@ extern "C" int encdiff_adamw_step_dev(float* p, const float* g, float* m, float*
                                                            grad_scale, static_cast<cudaStream_t>(stream))));
   return EDB_OK;
 }
+
+extern "C" int encdiff_adamw_hyper_advance(int* step, const float* lr, float* hyper, float beta1, float beta2,
+                                           float ema_decay_max, void* stream) {
+  EDB_REQUIRE(step && lr && hyper, "adamw_hyper_advance: bad argument");
+  EDB_CHECK_CUDA(static_cast<cudaError_t>(
+      launch_adamw_hyper_advance(step, lr, hyper, beta1, beta2, ema_decay_max, static_cast<cudaStream_t>(stream))));
+  return EDB_OK;
+}

@@ -544,6 +544,26 @@ __global__ void adamw_dev_kernel(float* __restrict__ p, const float* __restrict_
     if (ema) ema[i] -= om * (ema[i] - w);
   }
 }
+// Step counter and the step-dependent scalars stay on the device (one thread): a captured optimiser graph advances them
+// itself, so a host that runs many replays ahead of the GPU can neither tear nor pre-date them.
+__global__ void adamw_hyper_advance_kernel(int* __restrict__ step, const float* __restrict__ lr, float* __restrict__ hyper,
+                                           float b1, float b2, float ema_decay_max) {
+  pdl_enter();
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const int t = step[0] + 1;
+  step[0] = t;
+  hyper[0] = lr[0];
+  hyper[1] = static_cast<float>(1.0 - pow(static_cast<double>(b1), static_cast<double>(t)));
+  hyper[2] = static_cast<float>(1.0 - pow(static_cast<double>(b2), static_cast<double>(t)));
+  const float warm = (1.f + t) / (10.f + t);          // LitEma warm-up, ema.py:31-33 (num_updates counted from 1)
+  hyper[3] = warm < ema_decay_max ? warm : ema_decay_max;
+}
+int launch_adamw_hyper_advance(int* step, const float* lr, float* hyper, float beta1, float beta2, float ema_decay_max,
+                               cudaStream_t s) {
+  launch_k(adamw_hyper_advance_kernel, 1, 32, 0, s, step, lr, hyper, beta1, beta2, ema_decay_max);
+  return static_cast<int>(cudaGetLastError());
+}
+
 int launch_adamw_dev(float* p, const float* g, float* m, float* v, float* ema, long long n, const float* hyper,
                      float beta1, float beta2, float eps, float wd, float grad_scale, cudaStream_t s) {
   launch_k(adamw_dev_kernel, grid_for(n, 256, 148 * 16), 256, 0, s, p, g, m, v, ema, n, hyper, beta1, beta2, eps, wd,

@@ -178,5 +178,8 @@ int launch_adamw(float* p, const float* g, float* m, float* v, float* ema, long 
 // all-reduce) before use
 int launch_adamw_dev(float* p, const float* g, float* m, float* v, float* ema, long long n, const float* hyper,
                      float beta1, float beta2, float eps, float wd, float grad_scale, cudaStream_t s);
+// step[0] += 1; hyper = {lr[0], 1-beta1^step, 1-beta2^step, min(ema_decay_max, (1+step)/(10+step))}   (all device)
+int launch_adamw_hyper_advance(int* step, const float* lr, float* hyper, float beta1, float beta2, float ema_decay_max,
+                               cudaStream_t s);
 
 }  // namespace edb

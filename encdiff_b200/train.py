@@ -47,24 +47,40 @@ class FlatAdamWEMA:
         self.ema = self.flat.clone() if use_ema else None
         self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
         self.ema_decay_max = ema_decay
-        self.t = 0
+        self.t = 0                                   # host mirror of the device step counter (information only)
+        # device-resident optimiser clock: {lr, 1-b1^t, 1-b2^t, ema_decay} are derived ON the device from a device step
+        # counter by encdiff_adamw_hyper_advance, which is part of the captured optimiser graph.  A host that runs many
+        # graph replays ahead of the GPU therefore cannot hand step k the scalars of step k + n (or a torn mix).
         self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
-        self._hyper_host = torch.zeros(4, dtype=torch.float32).pin_memory() if dev.type == "cuda" else None
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev)
+        self._lr_on_dev = float(lr)
 
     def ema_decay(self) -> float:
         """LitEma warm-up (ema.py:31-33): min(decay, (1 + n) / (10 + n)) with n counted from 1."""
         n = self.t
         return min(self.ema_decay_max, (1 + n) / (10 + n))
 
+    def set_lr(self, lr: Optional[float] = None):
+        """Stage a new learning rate (LambdaLR of ddpm_enc.py:1630-1637).  The copy comes from pageable host memory: the
+        runtime stages it before returning, so the value a later step sees cannot be overwritten by the host."""
+        lr = self.lr if lr is None else float(lr)
+        if lr != self._lr_on_dev:
+            self.lr_dev.copy_(torch.tensor([lr], dtype=torch.float32))
+            self._lr_on_dev = lr
+
+    def advance(self):
+        """Enqueue the device-side clock tick (graph capturable): step += 1, hyper recomputed from it."""
+        lib = _lib.load()
+        _lib.check(lib.encdiff_adamw_hyper_advance(self.step_dev.data_ptr(), self.lr_dev.data_ptr(), self.hyper.data_ptr(),
+                                                   self.betas[0], self.betas[1], float(self.ema_decay_max),
+                                                   _lib.current_stream()), "adamw_hyper_advance")
+
     def write_hyper(self, lr: Optional[float] = None):
-        """Advance the step counter and stage {lr, 1-b1^t, 1-b2^t, ema_decay} for the device kernel."""
+        """Eager form: stage the learning rate and tick the device clock once (one optimiser step follows)."""
         self.t += 1
-        h = self._hyper_host
-        h[0] = self.lr if lr is None else lr
-        h[1] = 1.0 - self.betas[0] ** self.t
-        h[2] = 1.0 - self.betas[1] ** self.t
-        h[3] = self.ema_decay()
-        self.hyper.copy_(h, non_blocking=True)
+        self.set_lr(lr)
+        self.advance()
 
     def launch(self, flat_grad: torch.Tensor, grad_scale: float = 1.0, begin: int = 0, end: Optional[int] = None):
         """AdamW (+EMA) over elements [begin, end) of the flat buffers (default: all of them)."""
@@ -99,6 +115,14 @@ class DenoiserTrainer:
         self.world = 1
         if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
             self.world = torch.distributed.get_world_size(process_group)
+        if self.world > 1:
+            # what DDP does at construction (main_val.py:656-660): every replica starts from rank 0's parameters; the EMA
+            # shadow is re-cloned from them (LitEma snapshots the model in the constructor, ema.py:16-21)
+            from . import parallel
+            src = torch.distributed.get_global_rank(process_group, 0) if process_group is not None else 0
+            parallel.broadcast_(self.opt.flat, src, process_group)
+            if self.opt.ema is not None:
+                self.opt.ema.copy_(self.opt.flat)
         self.use_cuda_graph = use_cuda_graph
         # world > 1: the flat gradient bucket is all-reduced in this many chunks and the optimiser kernel of chunk i runs
         # while chunk i + 1 is still on the wire (1 = one all-reduce, then one optimiser launch).  Measured on 2 B200s
@@ -157,6 +181,7 @@ class DenoiserTrainer:
                                              st["dcond"].data_ptr(), _lib.current_stream()), "unet_backward")
 
     def _opt(self, st):
+        self.opt.advance()                      # device clock tick: inside the captured optimiser graph
         self.opt.launch(self.unet._gflat, 1.0 / self.world)
         self.unet.refresh_weights()
 
@@ -172,6 +197,7 @@ class DenoiserTrainer:
         g = self.unet._gflat
         bounds = self._chunk_bounds()
         works = [torch.distributed.all_reduce(g[b:e], group=self.pg, async_op=True) for b, e in bounds]
+        self.opt.advance()                      # chunked mode launches the optimiser eagerly: one clock tick per step
         for (b, e), w in zip(bounds, works):
             w.wait()                                              # the current stream waits for this chunk only
             self.opt.launch(g, 1.0 / self.world, b, e)
@@ -192,7 +218,8 @@ class DenoiserTrainer:
         st["noise"].copy_(noise, non_blocking=True)
         st["t"].copy_(t, non_blocking=True)
         st["cond"].copy_(cond, non_blocking=True)
-        self.opt.write_hyper(lr)
+        self.opt.t += 1
+        self.opt.set_lr(lr)
         if st.get("g_fb") is None or not self._bound_once:
             # walks all 734 parameters (Python): only before the graphs exist; afterwards the parameters are views of
             # the optimiser's flat buffer and cannot move (call invalidate() after replacing a parameter tensor)

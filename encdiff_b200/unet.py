@@ -23,17 +23,20 @@ def _as_list(v):
 
 
 class _UNetFn(torch.autograd.Function):
-    """Autograd node over the C-ABI forward/backward.  Parameter gradients are accumulated by the library directly
-    into ``param.grad`` (views of one flat fp32 bucket, see UNetModel._prepare_grads); the ``anchor`` input only makes
-    the output require grad."""
+    """Autograd node over the C-ABI forward/backward.  EVERY parameter is an input of the node and receives its gradient
+    as an output of ``backward`` (views of the flat fp32 bucket the library accumulated into), so each parameter's
+    AccumulateGrad node runs: ``param.grad`` accumulates with torch semantics, gradient hooks fire, and
+    ``torch.nn.parallel.DistributedDataParallel`` (the reference's Lightning 'ddp' strategy, main_val.py:656-660) sees
+    all 734 tensors in its bucket reducer.  The fused trainer (train.DenoiserTrainer) does not come through here."""
 
     @staticmethod
-    def forward(ctx, model, x, t, cond, anchor):
+    def forward(ctx, model, x, t, cond, *params):
         out = model._run_forward(x, t, cond, training=True)
         ctx.model = model
         ctx.fwd_id = model._fwd_id
         ctx.save_for_backward(cond)
         ctx.need_dx = x.requires_grad
+        ctx.need_param = tuple(p.requires_grad for p in params)
         return out
 
     @staticmethod
@@ -44,8 +47,8 @@ class _UNetFn(torch.autograd.Function):
         if ctx.fwd_id != model._fwd_id:
             raise RuntimeError("encdiff_b200.UNetModel: the activation workspace of this forward was overwritten by a "
                                "later forward; run backward before the next forward")
-        dx, dctx = model._run_backward(dout, cond, ctx.need_dx)
-        return None, dx, None, dctx, None
+        dx, dctx, grads = model._run_backward(dout, cond, ctx.need_dx)
+        return (None, dx, None, dctx) + tuple(g if need else None for g, need in zip(grads, ctx.need_param))
 
 
 class UNetModel(nn.Module):
@@ -285,15 +288,23 @@ class UNetModel(nn.Module):
         return out
 
     def _run_backward(self, dout, cond, need_dx: bool):
+        """Backward of the last forward for the autograd node: the library accumulates the parameter gradients into the
+        flat bucket, which is zeroed first; the returned views are handed to autograd, whose AccumulateGrad nodes copy
+        / add them into ``param.grad``."""
         B = dout.shape[0]
-        self._prepare_grads()
+        for p, v in zip(self._params(), self._grad_views):
+            if p.grad is not None and p.grad.data_ptr() == v.data_ptr():
+                p.grad = p.grad.clone()      # a fused-trainer step left param.grad aliasing the bucket: un-alias it
+        self._gflat.zero_()
         dout = dout.contiguous().float()
         dx = torch.empty(B, self.in_channels, self.image_size, self.image_size, dtype=torch.float32,
                          device=dout.device) if need_dx else None
         dctx = torch.empty_like(cond)
         _lib.check(self._lib.encdiff_unet_backward(self._h, B, dout.data_ptr(), cond.data_ptr(), _lib.ptr(dx),
                                                    dctx.data_ptr(), _lib.current_stream()), "unet_backward")
-        return dx, dctx
+        # clones: AccumulateGrad may keep the tensor it is handed as param.grad, and the bucket is reused next backward
+        parts = self._gflat.clone().split([v.numel() for v in self._grad_views])
+        return dx, dctx, tuple(c.view_as(v) for c, v in zip(parts, self._grad_views))
 
     def profile(self, enable: bool):
         """Switch the library's per-launch event timing on/off (bench.py roofline figures)."""
@@ -345,8 +356,7 @@ class UNetModel(nn.Module):
         needs_grad = torch.is_grad_enabled() and (
             xf.requires_grad or cond_f.requires_grad or any(p.requires_grad for p in self.parameters()))
         if needs_grad:
-            anchor = next(self.parameters())
-            out = _UNetFn.apply(self, xf, tf, cond_f, anchor)
+            out = _UNetFn.apply(self, xf, tf, cond_f, *self._params())
         else:
             out = self._run_forward(xf, tf, cond_f, training=False)
         return out.type(x.dtype)

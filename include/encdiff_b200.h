@@ -197,6 +197,13 @@ int encdiff_adamw_step(float* p, const float* g, float* m, float* v, float* ema,
 int encdiff_adamw_step_dev(float* p, const float* g, float* m, float* v, float* ema, long long n, const float* hyper,
                            float beta1, float beta2, float eps, float weight_decay, float grad_scale, void* stream);
 
+/* Device-resident optimiser clock (enqueue-only, graph capturable): step[0] += 1, then hyper = {lr[0], 1-beta1^step,
+ * 1-beta2^step, min(ema_decay_max, (1+step)/(10+step))} -- the bias corrections of torch.optim.AdamW
+ * (ddpm_enc.py:1598-1604) and LitEma's decay warm-up (ldm/modules/ema.py:31-33).  step (int32), lr and hyper are device
+ * pointers. */
+int encdiff_adamw_hyper_advance(int* step, const float* lr, float* hyper, float beta1, float beta2, float ema_decay_max,
+                                void* stream);
+
 #ifdef __cplusplus
 }
 #endif
