@@ -1,10 +1,16 @@
-"""Import shim for the UNMODIFIED reference (only where /root/reference exists: the build container) — TEST
-INFRASTRUCTURE.  Used by oracle/make_golden.py and by the live cross-checks in tests/test_oracle.py.
+"""Import shim for the UNMODIFIED reference -- TEST / BENCH-BASELINE INFRASTRUCTURE (never imported by encdiff_b200/).
 
-The reference needs two harness-side accommodations, neither of which edits the reference:
-  * ``UNetModel.__init__`` imports ``omegaconf.listconfig.ListConfig`` (openaimodel_enc.py:477) — absent here, so a
-    3-line fake module is injected;
-  * ``DDIMSampler.register_buffer`` forces tensors to "cuda" (ddim.py:18-22) — replaced by a CPU-tolerant setter.
+The reference tree is found at /root/reference (the build container) or, on a GPU box, at oracle/_ref/ (a verbatim,
+git-ignored copy of the reference's ``ldm`` package made by oracle/make_ref.py; it travels with the snapshot like the
+built .so).  Used by oracle/make_golden.py, by the live cross-checks in tests/, and by bench.py's reference / comparator
+legs (the reference's own nn.Modules on the host cores and in eager mode on the GPU).
+
+Harness-side accommodations, none of which edits the reference:
+  * ``omegaconf.listconfig.ListConfig`` (openaimodel_enc.py:477), ``pytorch_lightning`` (``LightningModule``,
+    ``utilities.distributed.rank_zero_only``), ``taming.modules.vqvae.quantize.VectorQuantizer2`` and ``main_val.eval_func``
+    are absent from this image: small fake modules are injected into ``sys.modules``;
+  * ``DDIMSampler.register_buffer`` forces tensors to "cuda" (ddim.py:18-22) and ``p_losses`` calls
+    ``self.logvar.cuda()`` (ddpm_enc.py:1200): both are neutralised when the model lives on the CPU.
 """
 from __future__ import annotations
 
@@ -15,11 +21,47 @@ import types
 import numpy as np
 import torch
 
-REFERENCE_ROOT = os.environ.get("ENCDIFF_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _find_root() -> str:
+    for cand in (os.environ.get("ENCDIFF_REFERENCE_ROOT"), "/root/reference", os.path.join(_HERE, "_ref")):
+        if cand and os.path.isdir(os.path.join(cand, "ldm")):
+            return cand
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _find_root()
 
 
 def available() -> bool:
     return os.path.isdir(os.path.join(REFERENCE_ROOT, "ldm"))
+
+
+class _NearestCodeQuantizer(torch.nn.Module):
+    """Stand-in for taming's VectorQuantizer2 (submodule src/taming-transformers pinned 3ba01b24..., empty in the reference
+    checkout; call sites autoencoder.py:49-51,146,342).  Published algorithm: z_q = e[argmin_k ||z - e_k||^2] per spatial
+    position (straight-through estimator in training), returns (z_q, loss, (perplexity, encodings, indices)).  Off the
+    hot path: used only when an image-space decode with quantisation is asked for.  Parity at this boundary: unpinned."""
+
+    def __init__(self, n_e, e_dim, beta=0.25, remap=None, unknown_index="random", sane_index_shape=False, legacy=True):
+        super().__init__()
+        self.n_e, self.e_dim, self.beta = n_e, e_dim, beta
+        self.embedding = torch.nn.Embedding(n_e, e_dim)
+        self.embedding.weight.data.uniform_(-1.0 / n_e, 1.0 / n_e)
+
+    def forward(self, z, temp=None, rescale_logits=False, return_logits=False):
+        zf = z.permute(0, 2, 3, 1).contiguous().view(-1, self.e_dim)
+        e = self.embedding.weight
+        d = (zf ** 2).sum(1, keepdim=True) + (e ** 2).sum(1) - 2.0 * zf @ e.t()
+        idx = torch.argmin(d, dim=1)
+        zq = e[idx].view(z.shape[0], z.shape[2], z.shape[3], self.e_dim).permute(0, 3, 1, 2).contiguous()
+        loss = self.beta * ((zq.detach() - z) ** 2).mean() + ((zq - z.detach()) ** 2).mean()
+        zq = z + (zq - z).detach()
+        return zq, loss, (None, None, idx)
+
+    def embed_code(self, code_b):
+        return self.embedding(code_b)
 
 
 def _install_stubs():
@@ -35,6 +77,52 @@ def _install_stubs():
         om.listconfig = lc
         sys.modules["omegaconf"] = om
         sys.modules["omegaconf.listconfig"] = lc
+    if "pytorch_lightning" not in sys.modules:
+        pl = types.ModuleType("pytorch_lightning")
+
+        class LightningModule(torch.nn.Module):
+            """The slice of pl.LightningModule the reference's model classes touch outside a Trainer."""
+            current_epoch = 0
+            global_step = 0
+            trainer = None
+
+            @property
+            def device(self):
+                for p in self.parameters():
+                    return p.device
+                for b in self.buffers():
+                    return b.device
+                return torch.device("cpu")
+
+            def log(self, *a, **k):
+                pass
+
+            def log_dict(self, *a, **k):
+                pass
+
+        pl.LightningModule = LightningModule
+        util = types.ModuleType("pytorch_lightning.utilities")
+        dist = types.ModuleType("pytorch_lightning.utilities.distributed")
+        dist.rank_zero_only = lambda fn: fn
+        util.distributed = dist
+        pl.utilities = util
+        cb = types.ModuleType("pytorch_lightning.callbacks")
+        pl.callbacks = cb
+        sys.modules.update({"pytorch_lightning": pl, "pytorch_lightning.utilities": util,
+                            "pytorch_lightning.utilities.distributed": dist, "pytorch_lightning.callbacks": cb})
+    if "taming" not in sys.modules:
+        tm = types.ModuleType("taming")
+        tmm = types.ModuleType("taming.modules")
+        tmv = types.ModuleType("taming.modules.vqvae")
+        tmq = types.ModuleType("taming.modules.vqvae.quantize")
+        tmq.VectorQuantizer2 = _NearestCodeQuantizer
+        tm.modules, tmm.vqvae, tmv.quantize = tmm, tmv, tmq
+        sys.modules.update({"taming": tm, "taming.modules": tmm, "taming.modules.vqvae": tmv,
+                            "taming.modules.vqvae.quantize": tmq})
+    if "main_val" not in sys.modules:
+        mv = types.ModuleType("main_val")
+        mv.eval_func = lambda *a, **k: {}
+        sys.modules["main_val"] = mv
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
 
@@ -90,3 +178,68 @@ def reference_ddim_sampler(model):
             setattr(self, name, attr)
 
     return CpuDDIMSampler(model)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the real LatentDiffusion (ddpm_enc.py:484) through the reference's own factory
+# ---------------------------------------------------------------------------------------------------------------------
+REF_UNET_TARGET = "ldm.modules.diffusionmodules.openaimodel_enc.UNetModel"
+
+
+def latent_diffusion_config(cfg, unet_target=REF_UNET_TARGET, resolution=None):
+    """The ``model`` node of configs/latent-diffusion/shapes3d-vq-4-16-encdiff.yaml as a plain dict, for an oracle
+    ``UNetConfig`` (the yaml's own values for cfg = SHAPES3D).  ``unet_target`` is the drop-in seam (ldm/util.py:78-93):
+    ``encdiff_b200.UNetModel`` swaps the denoiser and nothing else.  eval_name is left out (it loads a dataset)."""
+    res = 4 * cfg.image_size if resolution is None else resolution
+    unet = dict(image_size=cfg.image_size, in_channels=cfg.in_channels, out_channels=cfg.out_channels,
+                model_channels=cfg.model_channels, attention_resolutions=list(cfg.attention_resolutions),
+                num_res_blocks=cfg.num_res_blocks, channel_mult=list(cfg.channel_mult), num_heads=cfg.num_heads,
+                use_scale_shift_norm=True, resblock_updown=True, use_spatial_transformer=True,
+                context_dim=cfg.context_dim, latent_unit=cfg.latent_unit)
+    first = dict(embed_dim=3, n_embed=2048, use_disentangled_concat=True, disentangled_dim=cfg.latent_unit,
+                 monitor="train/rec_loss",
+                 ddconfig=dict(double_z=False, z_channels=3, resolution=res, in_channels=3, out_ch=3, ch=32,
+                               ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[], dropout=0.0),
+                 lossconfig=dict(target="torch.nn.Identity"))
+    cond = dict(d=128, context_dim=cfg.context_dim, latent_unit=cfg.latent_unit)
+    return dict(target="ldm.models.diffusion.ddpm_enc.LatentDiffusion",
+                params=dict(linear_start=0.0015, linear_end=0.0155, num_timesteps_cond=1, log_every_t=200, timesteps=1000,
+                            loss_type="l1", first_stage_key="image", cond_stage_key="image", image_size=cfg.image_size,
+                            channels=3, cond_stage_trainable=True, concat_mode=False, scale_by_std=True,
+                            monitor="train/loss_simple", conditioning_key="crossattn",
+                            unet_config=dict(target=unet_target, params=unet),
+                            first_stage_config=dict(target="ldm.models.autoencoder.VQModelInterface", params=first),
+                            cond_stage_config=dict(target="ldm.modules.diffusionmodules.openaimodel_enc.Encoder4",
+                                                   params=cond)))
+
+
+def reference_latent_diffusion(cfg, unet_target=REF_UNET_TARGET, device="cpu", seed=23, unet_params=None):
+    """instantiate_from_config(config.model) as main_val.py:677 does, on ``device``.  With ``unet_params`` the denoiser's
+    parameters are loaded through the wrapper's own prefix (``model.diffusion_model.``) and the EMA shadow is re-synced."""
+    _install_stubs()
+    from ldm.util import instantiate_from_config
+    torch.manual_seed(seed)
+    model = instantiate_from_config(latent_diffusion_config(cfg, unet_target))
+    if unet_params is not None:
+        sd = {"model.diffusion_model." + k: v for k, v in unet_params.items()}
+        missing, unexpected = model.load_state_dict(sd, strict=False)
+        assert not unexpected, unexpected
+        assert not [k for k in missing if k.startswith("model.diffusion_model.")]
+        if getattr(model, "use_ema", False):
+            from ldm.modules.ema import LitEma
+            model.model_ema = LitEma(model.model)
+    model = model.to(device)
+    if torch.device(device).type == "cpu":
+        # ddpm_enc.py:1200 `self.logvar = self.logvar.cuda()`: make the call a no-op on a CPU-only host
+        class _CpuLogvar(torch.Tensor):
+            def cuda(self, *a, **k):
+                return self
+        model.logvar = model.logvar.as_subclass(_CpuLogvar)
+        import ldm.models.diffusion.ddpm_enc as ddpm_enc
+
+        class CpuDDIMSampler(ddpm_enc.DDIMSampler):      # ddim.py:18-22 forces "cuda"
+            def register_buffer(self, name, attr):
+                setattr(self, name, attr)
+        model._cpu_ddim_sampler = CpuDDIMSampler
+        ddpm_enc.DDIMSampler = CpuDDIMSampler            # sample_log resolves the name at call time (ddpm_enc.py:1446)
+    return model
