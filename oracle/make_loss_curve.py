@@ -1,8 +1,9 @@
-"""Generate tests/golden/loss_curve_tiny_1k.npz: the 1 000-step training loss curve of the UNMODIFIED reference UNetModel
-(imported from /root/reference through oracle/ref_shim.py) with torch autograd + torch.optim.AdamW on the CPU, tiny
-configuration, batch 8, the seeded batches of oracle.make_golden.seeded_inputs(seed = 1000 + step).  It pins the north
-star's "1k-step training loss curve within 2 %" bar (tests/test_train_gpu.py::test_loss_curve_1k_vs_reference).
-Run in the build container only (about 5 minutes of CPU):  python -m oracle.make_loss_curve
+"""Generate tests/golden/loss_curve_<config>_<steps>.npz: the training loss curve of the UNMODIFIED reference UNetModel
+(imported from /root/reference through oracle/ref_shim.py) with torch autograd + torch.optim.AdamW on the CPU, batch 8,
+the seeded batches of oracle.make_golden.seeded_inputs(seed = 1000 + step).  It pins the north star's "1k-step training
+loss curve within 2 %" bar (tests/test_train_gpu.py) on the tiny configuration (1 000 steps) and on the Shapes3D
+configuration itself (shapes3d-vq-4-16-encdiff.yaml:33-48; 400 steps -- the fp32 reference needs ~1 s per step here).
+Run in the build container only:  python -m oracle.make_loss_curve [tiny|shapes3d] [steps]
 Test infrastructure: nothing under encdiff_b200/ imports this.
 """
 from __future__ import annotations
@@ -20,16 +21,16 @@ sys.path.insert(0, ROOT)
 from oracle import diffusion_oracle as DO  # noqa: E402
 from oracle import ref_shim  # noqa: E402
 from oracle import unet_oracle as UO  # noqa: E402
-from oracle.make_golden import GOLDEN, TINY, seeded_inputs  # noqa: E402
+from oracle.make_golden import CONFIGS, GOLDEN, seeded_inputs  # noqa: E402
 
 STEPS, BATCH, LR, WD = 1000, 8, 2e-4, 0.01
 
 
-def main():
+def main(name="tiny", steps=STEPS):
     # denormal intermediates (softmax tails) put the CPU on its slow path after a few hundred steps (100x slower);
     # flushing them to zero changes no loss digit that the 2 % bar could see
     torch.set_flush_denormal(True)
-    cfg = TINY
+    cfg = CONFIGS[name]
     params = UO.make_params(cfg, seed=1)
     ref = ref_shim.reference_unet(cfg, params).train()
     for p in ref.parameters():
@@ -39,7 +40,7 @@ def main():
     acp = DO.alphas_cumprod(DO.linear_betas())
     losses = []
     t0 = time.time()
-    for i in range(STEPS):
+    for i in range(steps):
         x, t, ctx, noise = seeded_inputs(cfg, BATCH, seed=1000 + i)
         opt.zero_grad(set_to_none=True)
         eps = ref(DO.q_sample(x, t, noise, acp), t, context=[ctx])
@@ -51,11 +52,11 @@ def main():
             print(i, loss.item(), f"{time.time() - t0:.0f}s", flush=True)
     names = [n for n, _ in ref.named_parameters()]
     delta_norm = np.array([(p.detach() - params[n]).norm().item() for n, p in ref.named_parameters()])
-    np.savez_compressed(os.path.join(GOLDEN, "loss_curve_tiny_1k.npz"), losses=np.array(losses, dtype=np.float64),
-                        steps=STEPS, batch=BATCH, lr=LR, weight_decay=WD, param_names=np.array(names),
+    np.savez_compressed(os.path.join(GOLDEN, f"loss_curve_{name}_{'1k' if steps == 1000 else steps}.npz"), losses=np.array(losses, dtype=np.float64),
+                        steps=steps, batch=BATCH, lr=LR, weight_decay=WD, param_names=np.array(names),
                         param_delta_norm=delta_norm)
     print("final", losses[-1])
 
 
 if __name__ == "__main__":
-    main()
+    main(sys.argv[1] if len(sys.argv) > 1 else "tiny", int(sys.argv[2]) if len(sys.argv) > 2 else STEPS)

@@ -125,3 +125,30 @@ def test_ddim_update_kernel_is_the_reference_arithmetic(cuda_device):
                                        prev.data_ptr(), x0.data_ptr(), xd.numel(), _lib.current_stream()))
     assert torch.allclose(prev.cpu(), want_prev, rtol=1e-5, atol=1e-6)
     assert torch.allclose(x0.cpu(), want_x0, rtol=1e-5, atol=1e-6)
+
+
+def test_ddim50_benched_shape_b128_vs_oracle(cuda_device):
+    """DDIM-50 at the benched shape (BASELINE.json configs[2]: 128 samples per GPU, Shapes3D/MPI3D architecture), graph
+    path, against the fp32 CPU oracle's trajectory.  The samples are independent of their batch neighbours, so the oracle
+    runs the first 8 samples of the same batch (50 CPU forwards of batch 8) and the bar is the north star's PSNR >= 40 dB."""
+    from encdiff_b200 import DDIMSampler
+    cfg = CONFIGS["shapes3d"]
+    host = make_host(cfg, cuda_device)
+    gen = torch.Generator().manual_seed(128)
+    B, n_or = 128, 8
+    x_T = torch.randn(B, cfg.in_channels, cfg.image_size, cfg.image_size, generator=gen)
+    ctx = torch.randn(B, cfg.latent_unit * cfg.context_dim, generator=gen)
+    shape = tuple(x_T.shape[1:])
+    s = DDIMSampler(host, use_cuda_graph=True)
+    out, inter = s.sample(50, B, shape, ctx.to(cuda_device), eta=0., x_T=x_T.to(cuda_device), verbose=False)
+    acp = DO.alphas_cumprod(DO.linear_betas())
+    p = UO.make_params(cfg, seed=1)
+    with torch.no_grad():
+        want, _ = DO.ddim_sample(lambda x, ts: UO.unet_forward(p, cfg, x, ts, [ctx[:n_or]]), x_T[:n_or], acp, 50, 0.0, None)
+    ps = psnr(out[:n_or], want)
+    print(f"DDIM-50 B=128 (graph) vs oracle on samples 0..{n_or - 1}: PSNR {ps:.1f} dB")
+    assert torch.isfinite(out).all()
+    assert ps >= PSNR_MIN
+    # a second call is bit-identical (eta = 0 is deterministic given x_T)
+    out2, _ = s.sample(50, B, shape, ctx.to(cuda_device), eta=0., x_T=x_T.to(cuda_device), verbose=False)
+    assert torch.equal(out, out2)
