@@ -1,0 +1,147 @@
+"""The drop-in boundary exercised through the REFERENCE'S OWN seam: the real ``LatentDiffusion``
+(ldm/models/diffusion/ddpm_enc.py:484) is built by the reference's ``instantiate_from_config`` (ldm/util.py:78-93) from
+the Shapes3D yaml values with ``unet_config.target: encdiff_b200.UNetModel``, and driven through the reference's own
+``forward`` / ``p_losses`` / ``sample_log`` / ``log_images`` code.  The comparator is the same ``LatentDiffusion`` with
+the reference's ``UNetModel`` in fp32 eager mode on the same GPU.  The reference package is imported from /root/reference
+(build container) or oracle/_ref (GPU box, oracle/make_ref.py); those tests are skipped when neither exists."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_shim
+from oracle import unet_oracle as UO
+from oracle.make_golden import CONFIGS
+
+pytestmark = pytest.mark.gpu
+needs_ref = pytest.mark.skipif(not ref_shim.available(), reason="no reference tree (/root/reference or oracle/_ref)")
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def psnr(a, b):
+    a, b = torch.as_tensor(a).double().cpu(), torch.as_tensor(b).double().cpu()
+    peak = (b.max() - b.min()).item()
+    mse = ((a - b) ** 2).mean().item()
+    return float("inf") if mse == 0 else 10.0 * np.log10(peak * peak / mse)
+
+
+@pytest.fixture(scope="module")
+def pair(cuda_device):
+    """(reference LatentDiffusion, the same with encdiff_b200.UNetModel as unet_config.target), identical weights."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    cfg = CONFIGS["shapes3d"]
+    params = UO.make_params(cfg, seed=1)
+    ref = ref_shim.reference_latent_diffusion(cfg, device=cuda_device, unet_params=params)
+    mine = ref_shim.reference_latent_diffusion(cfg, unet_target="encdiff_b200.UNetModel", device=cuda_device,
+                                               unet_params=params)
+    # everything outside the denoiser (first stage, Encoder4, EMA shadow) comes from the reference-side model through
+    # the plain state_dict: this is also the check that the keys under `model.diffusion_model.` are the reference's
+    missing, unexpected = mine.load_state_dict(ref.state_dict(), strict=True)
+    assert not missing and not unexpected
+    return cfg, ref, mine
+
+
+@needs_ref
+def test_instantiate_from_config_builds_the_dropin(pair):
+    import encdiff_b200
+    cfg, ref, mine = pair
+    assert type(mine.model.diffusion_model) is encdiff_b200.UNetModel
+    assert type(mine).__name__ == "LatentDiffusion" and type(mine.model).__name__ == "DiffusionWrapper"
+    assert list(mine.state_dict().keys()) == list(ref.state_dict().keys())
+    assert mine.model.diffusion_model.latent_unit == cfg.latent_unit          # read by log_images, ddpm_enc.py:1525
+    assert len(list(mine.model_ema.buffers())) == len(list(ref.model_ema.buffers()))      # LitEma snapshot, ema.py:16-21
+
+
+@needs_ref
+def test_instantiate_from_config_p_losses_forward_backward(pair, cuda_device):
+    """LatentDiffusion.forward -> Encoder4 -> p_losses -> apply_model -> DiffusionWrapper -> UNet (ddpm_enc.py:1040-1213)
+    and loss.backward(): loss, the gradient reaching the trainable concept encoder through d context, and the UNet's own
+    parameter gradients, against the reference UNet in fp32 on the same GPU."""
+    cfg, ref, mine = pair
+    g = torch.Generator().manual_seed(23)
+    batch = {"image": (torch.rand(8, 64, 64, 3, generator=g) * 2 - 1).to(cuda_device)}
+    out = {}
+    for name, model in (("ref", ref), ("mine", mine)):
+        model.train()
+        model.zero_grad(set_to_none=True)
+        x, c = model.get_input(batch, "image")
+        torch.manual_seed(77)                       # t = randint(...), noise = randn_like(...) inside forward / p_losses
+        loss, loss_dict = model(x, c)
+        loss.backward()
+        out[name] = (loss.item(), loss_dict,
+                     {k: p.grad.detach().clone() for k, p in model.cond_stage_model.named_parameters() if p.grad is not None},
+                     {k: p.grad.detach().clone() for k, p in model.model.diffusion_model.named_parameters()})
+    l_ref, l_mine = out["ref"][0], out["mine"][0]
+    print(f"LatentDiffusion.forward loss: reference {l_ref:.6f}, drop-in {l_mine:.6f}")
+    assert abs(l_ref - l_mine) <= 2e-3 * abs(l_ref)
+    assert set(out["ref"][1]) == set(out["mine"][1])
+
+    # L1's gradient is sign(eps - noise): a few signs flip between two precisions, so the bars are on direction
+    def cos(da, db):
+        a = torch.cat([da[k].flatten().double() for k in db])
+        b = torch.cat([db[k].flatten().double() for k in db])
+        return (torch.dot(a, b) / (a.norm() * b.norm())).item()
+    assert set(out["mine"][2]) == set(out["ref"][2]) and len(out["ref"][2]) > 0
+    c_enc, c_unet = cos(out["mine"][2], out["ref"][2]), cos(out["mine"][3], out["ref"][3])
+    print(f"gradient cosine: concept encoder {c_enc:.5f}, UNet {c_unet:.5f}")
+    assert c_enc > 0.99 and c_unet > 0.99
+
+
+@needs_ref
+def test_sample_log_after_install(pair, cuda_device):
+    """``sampler.install()`` rebinds the name LatentDiffusion.sample_log resolves (ddpm_enc.py:1442-1455); the reference's
+    own sample_log then runs the graph-replayed CUDA sampler.  Same x_T, eta 0: PSNR >= 40 dB against the reference
+    DDIMSampler around the reference UNet."""
+    import ldm.models.diffusion.ddpm_enc as ddpm_enc
+    from encdiff_b200 import sampler as edb_sampler
+    cfg, ref, mine = pair
+    g = torch.Generator().manual_seed(3)
+    B, S = 4, 20
+    cond = torch.randn(B, cfg.latent_unit * cfg.context_dim, generator=g).to(cuda_device)
+    x_T = torch.randn(B, 3, cfg.image_size, cfg.image_size, generator=g).to(cuda_device)
+    ref.eval(), mine.eval()
+    want, _ = ref.sample_log(cond=cond, batch_size=B, ddim=True, ddim_steps=S, eta=0., x_T=x_T)
+    prev = edb_sampler.install(ddpm_enc)
+    try:
+        got, inter = mine.sample_log(cond=cond, batch_size=B, ddim=True, ddim_steps=S, eta=0., x_T=x_T)
+    finally:
+        ddpm_enc.DDIMSampler = prev
+    p = psnr(got, want)
+    print(f"sample_log (DDIM-{S}, installed sampler) vs reference: PSNR {p:.1f} dB")
+    assert got.shape == want.shape and set(inter) == {"x_inter", "pred_x0"}
+    assert p >= 40.0
+
+
+def test_swap_vs_reference_log_images_golden(cuda_device):
+    """SURVEY.md section 8 row a17 pinned on the reference side: tests/golden/swap_shapes3d_n2_s10.npz holds what the
+    UNMODIFIED reference's ``log_images(sample_swap=True, ddim_steps=10, ddim_eta=0)`` produced
+    (oracle/make_swap_golden.py): codes, Encoder4.net weights, the start noise of its 20 sequential runs and the 40
+    latents it decoded.  The folded CUDA run (one batch of 20 x N samples) must reproduce those latents."""
+    from encdiff_b200 import ConceptMLP, DDIMSampler, UNetModel
+    from encdiff_b200.diffusion import DenoiserHost
+    from encdiff_b200.swap import sample_swap
+    fx = np.load(os.path.join(GOLDEN, "swap_shapes3d_n2_s10.npz"))
+    cfg = CONFIGS["shapes3d"]
+    m = UNetModel(image_size=cfg.image_size, in_channels=cfg.in_channels, out_channels=cfg.out_channels,
+                  model_channels=cfg.model_channels, attention_resolutions=list(cfg.attention_resolutions),
+                  num_res_blocks=cfg.num_res_blocks, channel_mult=list(cfg.channel_mult), num_heads=cfg.num_heads,
+                  use_scale_shift_norm=True, resblock_updown=True, use_spatial_transformer=True,
+                  context_dim=cfg.context_dim, latent_unit=cfg.latent_unit)
+    m.load_state_dict(UO.make_params(cfg, seed=1), strict=True)
+    host = DenoiserHost(m.eval()).to(cuda_device)
+    net = ConceptMLP(cfg.latent_unit, cfg.context_dim)
+    net.load_state_dict({k[len("net::"):]: torch.tensor(fx[k]) for k in fx.files if k.startswith("net::")}, strict=True)
+    net = net.to(cuda_device)
+    S, N = int(fx["S"]), int(fx["N"])
+    orc = torch.tensor(fx["orc"]).to(cuda_device)
+    x_T = torch.tensor(fx["x_T"]).to(cuda_device)                    # [20, N, 3, 16, 16], run-major
+    got = sample_swap(DDIMSampler(host), orc, net.warp, ddim_steps=S, eta=0., shape=(3, cfg.image_size, cfg.image_size),
+                      x_T=x_T)
+    want = torch.tensor(fx["samples"])
+    assert got.shape == want.shape == (cfg.latent_unit * N, 3, cfg.image_size, cfg.image_size)
+    p = psnr(got, want)
+    per_run = min(psnr(got[i * N:(i + 1) * N], want[i * N:(i + 1) * N]) for i in range(cfg.latent_unit))
+    print(f"swap generation vs the reference's log_images: PSNR {p:.1f} dB (worst run {per_run:.1f} dB)")
+    assert p >= 40.0 and per_run >= 40.0
