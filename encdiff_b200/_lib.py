@@ -39,6 +39,9 @@ PROTOTYPES = {
     "encdiff_op_cross_attention_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                                c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                                c_int, c_int, c_void_p]),
+    "encdiff_op_cross_attention_bwd_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                       c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                                       c_int, c_int, c_void_p]),
     "encdiff_op_geglu": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p]),
     "encdiff_concept_mlp_forward": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int, c_void_p]),
     "encdiff_concept_mlp_backward": (c_int, [c_void_p] * 15 + [c_int, c_int, c_int, c_void_p]),

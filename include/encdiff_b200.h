@@ -82,6 +82,17 @@ long long encdiff_op_cross_attention_bwd_scratch_bytes(int B, int heads, int D, 
 int encdiff_op_cross_attention_bwd(const void* q, const float* ctx, const float* wk, const float* wv, const float* kv,
                                    const void* dout, void* dq, float* dwk, float* dwv, float* dctx, float* scratch, int B,
                                    int N, int heads, int D, int T, int Dc, void* stream);
+/* Allocation-free variant of encdiff_op_cross_attention_bwd.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and arithmetic, but the fp32 dK | dV scratch lives in a static device array of
+ * ENCDIFF_NOALLOC_SCRATCH_BYTES inside the library (held by every GPU that loads it until exit); the call performs no
+ * cudaMalloc / cudaFree / allocating library routine.  B*T*2*heads*D*4 bytes must fit, otherwise the call returns a
+ * non-zero status and encdiff_last_error() names both sizes.  All calls on a device share the one array: calls that
+ * overlap on the GPU (different streams) race -- serialise them, or use the caller-scratch entry point. */
+#define ENCDIFF_NOALLOC_SCRATCH_BYTES (16u << 20)
+int encdiff_op_cross_attention_bwd_noalloc(const void* q, const float* ctx, const float* wk, const float* wv,
+                                           const float* kv, const void* dout, void* dq, float* dwk, float* dwv,
+                                           float* dctx, int B, int N, int heads, int D, int T, int Dc, void* stream);
 /* GEGLU (attention.py:37-45): g h16 [M, 2*inner] (value | gate) -> out h16 [M, inner] = value * gelu_erf(gate)  */
 int encdiff_op_geglu(const void* g, void* out, long long M, int inner, void* stream);
 
