@@ -148,3 +148,37 @@ def test_loss_curve_1k_vs_reference(cuda_device):
     assert rel.max() <= 1e-1
     assert rel_sm.max() <= 2e-2
     assert got[-50:].mean() < 0.75 * got[0]               # it trains
+
+
+def test_loss_curve_shapes3d_vs_reference(cuda_device):
+    """The north star's loss-curve bar on the Shapes3D configuration itself (16x16x3 latents of 64x64x3 images, the UNet
+    of shapes3d-vq-4-16-encdiff.yaml:33-48): tests/golden/loss_curve_shapes3d_400.npz is the UNMODIFIED reference UNetModel
+    trained for 400 AdamW steps on the CPU in fp32 (oracle/make_loss_curve.py shapes3d 400, same seeded batches of 8).
+    CUDA side: the graph-captured fused step.  Bars: the curve (20-step moving mean) within 2 % over the whole run, every
+    step of the first 100 within 2 %."""
+    import os
+    from encdiff_b200.train import DenoiserTrainer
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_curve_shapes3d_400.npz"))
+    want = fx["losses"]
+    steps, B, lr, wd = int(fx["steps"]), int(fx["batch"]), float(fx["lr"]), float(fx["weight_decay"])
+    cfg = CONFIGS["shapes3d"]
+    m, params = make_unet(cfg, cuda_device)
+    tr = DenoiserTrainer(m, lr=lr, weight_decay=wd, use_ema=True, use_cuda_graph=True)
+    got = []
+    for i in range(steps):
+        x, t, ctx, noise = seeded_inputs(cfg, B, seed=1000 + i)
+        loss, _ = tr.step(x.to(cuda_device), ctx.to(cuda_device), t.to(cuda_device), noise.to(cuda_device))
+        got.append(loss.detach().clone())
+    got = torch.stack([g.reshape(()) for g in got]).cpu().double().numpy()
+    rel = np.abs(got - want) / want
+    k = np.ones(20) / 20
+    sm_got, sm_want = np.convolve(got, k, mode="valid"), np.convolve(want, k, mode="valid")
+    rel_sm = np.abs(sm_got - sm_want) / sm_want
+    print(f"shapes3d {steps} steps: reference {want[0]:.4f} -> {want[-20:].mean():.4f}, cuda {got[0]:.4f} -> "
+          f"{got[-20:].mean():.4f}; per-step rel diff max {rel.max():.2e} (first 100: {rel[:100].max():.2e}); 20-step mean "
+          f"rel diff max {rel_sm.max():.2e}")
+    assert np.isfinite(got).all()
+    assert rel[:100].max() <= 2e-2
+    assert rel_sm.max() <= 2e-2
+    assert rel.max() <= 1e-1
+    assert got[-50:].mean() < 0.6 * got[0]
