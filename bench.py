@@ -108,7 +108,14 @@ class ClockSampler:
 # CPU arm: the reference algorithm (oracle port of the reference's torch modules) on the host cores
 # ---------------------------------------------------------------------------------------------------------------------
 def cpu_train_step_time(B, steps, warmup):
-    """Seconds per p_losses forward+backward+AdamW step of the CPU oracle at batch B (all host threads)."""
+    """(seconds per step, host threads, kind) of the reference's training step on the host cores at batch B.
+    kind "reference": the UNMODIFIED reference modules (LatentDiffusion.p_losses -> DiffusionWrapper -> UNetModel, autograd,
+    torch.optim.AdamW, LitEma) imported from /root/reference or oracle/_ref (oracle/ref_bench.py).
+    kind "port": the oracle's functional port of the same step, only when no reference tree travelled to this box."""
+    from oracle import ref_bench
+    if ref_bench.available():
+        sec, cores, _ = ref_bench.train_step_time(B, steps, warmup, "cpu")
+        return sec, cores, "reference"
     from oracle import diffusion_oracle as DO
     from oracle import unet_oracle as UO
     torch.set_num_threads(os.cpu_count() or 1)
@@ -127,22 +134,26 @@ def cpu_train_step_time(B, steps, warmup):
         opt.step()
         if i >= warmup:
             times.append(time.perf_counter() - t0)
-    return statistics.median(times), torch.get_num_threads()
+    return statistics.median(times), torch.get_num_threads(), "port"
 
 
 def run_reference(args):
+    """The reference arm: the reference's own CPU implementation of the step at the SAME per-GPU batch as the CUDA arm
+    (BASELINE.json configs[1]: 256), all host threads.  One process, whatever --gpus says (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    B = args.cpu_batch
-    sec, cores = cpu_train_step_time(B, args.steps, args.warmup)
+    B = args.batch
+    sec, cores, kind = cpu_train_step_time(B, args.steps, args.warmup)
     v = B / sec
-    sample = f"{args.steps} timed steps of batch {B} (of the per-GPU batch {args.batch}), median"
+    sample = (f"{args.steps} timed steps (median) of the full per-GPU batch {B}: LatentDiffusion.p_losses fwd + bwd + "
+              f"AdamW + LitEma of the {'unmodified reference modules' if kind == 'reference' else 'oracle port'}, fp32")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": "shapes3d_train_step_b256_per_gpu", "sample_batch": B},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "config": {"workload": f"{args.workload}_train_step_b{B}_per_gpu", "global_batch": B, "parallelism": "cpu",
+                       "step": "q_sample+UNet fwd+L1+UNet bwd+AdamW/EMA"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -317,13 +328,71 @@ def run_b200(args):
     if swap is not None:
         line["swap_ddim200"] = swap
     if world == 1 and not args.no_cpu:
-        sec, cores = cpu_train_step_time(args.cpu_batch, 5, 1)
-        line["cpu_baseline"] = {"value": args.cpu_batch / sec, "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": f"5 timed steps of batch {args.cpu_batch} (of {B}), median, fp32 torch oracle "
-                                          "(p_losses fwd+bwd+AdamW), all host threads"}
+        sec, cores, kind = cpu_train_step_time(B, 3, 1)
+        line["cpu_baseline"] = {"value": B / sec, "unit": UNIT, "cores": cores, "kind": kind,
+                                "sample": f"3 timed steps (median, 1 warm-up) of the full batch {B}, fp32, all host threads: "
+                                          + ("the unmodified reference LatentDiffusion.p_losses fwd+bwd+AdamW+LitEma "
+                                             "(oracle/_ref)" if kind == "reference" else "oracle port of p_losses fwd+bwd+AdamW")}
+    if world == 1 and not args.no_comparators:
+        line["comparators"] = gpu_comparators(model, dev, B, args.ddim_batch)
     print(json.dumps(line), flush=True)
     if dist_on:
         torch.distributed.destroy_process_group()
+
+
+def gpu_comparators(model, dev, B, ddim_B):
+    """Same-GPU context for the headline, each a few steps after warm-up:
+      ref_eager_gpu_tf32 / ref_eager_gpu_bf16: the UNMODIFIED reference modules (oracle/_ref) in PyTorch eager mode on this
+        B200 -- TF32 matmul/conv as the reference ships (main_val.py:524-525) and under bf16 autocast -- training step at
+        the benched batch and DDIM-50 at the benched sampling batch;
+      dropin_autograd: what a reference user gets from the documented drop-in seam without the fused trainer:
+        encdiff_b200.UNetModel.forward + loss.backward() through torch autograd + torch.optim.AdamW."""
+    import gc
+    out = {}
+    try:
+        from oracle import ref_bench
+        if ref_bench.available():
+            ref = ref_bench.build(dev)
+            for name, kw in (("ref_eager_gpu_tf32", dict(tf32=True)),
+                             ("ref_eager_gpu_bf16", dict(tf32=True, autocast_dtype=torch.bfloat16))):
+                sec, _, _ = ref_bench.train_step_time(B, 5, 2, dev, model=ref, **kw)
+                dsec = ref_bench.ddim_time(ddim_B, 50, 2, dev, model=ref, **kw)
+                out[name] = {"train_img_per_s": B / sec, "train_ms_per_step": sec * 1e3, "batch": B,
+                             "ddim50_img_per_s": ddim_B / dsec, "ddim50_batch": ddim_B}
+            del ref
+            gc.collect()
+            torch.cuda.empty_cache()
+        else:
+            out["ref_eager_gpu"] = "unavailable: no reference tree on this box (oracle/_ref missing)"
+    except Exception as e:           # a comparator must never take the headline down with it
+        out["ref_eager_gpu_error"] = repr(e)[:300]
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        x0, cond, t, noise = synthetic_batch(B, 23, device=dev)
+        model.train()
+        model.cache_packed_weights = False
+        opt = torch.optim.AdamW(list(model.parameters()), lr=1e-4)
+        for p in model.parameters():
+            p.grad = None
+        times = []
+        for i in range(2 + 5):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            opt.zero_grad(set_to_none=True)
+            c = cond.clone().requires_grad_(True)
+            eps = model(x0, t, context=[c])
+            (eps - noise).abs().mean().backward()
+            opt.step()
+            torch.cuda.synchronize()
+            if i >= 2:
+                times.append(time.perf_counter() - t0)
+        sec = statistics.median(times)
+        out["dropin_autograd"] = {"train_img_per_s": B / sec, "train_ms_per_step": sec * 1e3, "batch": B,
+                                  "path": "encdiff_b200.UNetModel.forward + loss.backward() + torch.optim.AdamW (eager)"}
+    except Exception as e:
+        out["dropin_autograd_error"] = repr(e)[:300]
+    return out
 
 
 def ddim50(model, dev, B, dist_on, world):
@@ -374,7 +443,6 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (BASELINE.json configs[1]: 256)")
-    ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample of the same workload")
     ap.add_argument("--ddim-batch", type=int, default=128, help="per-GPU DDIM-50 batch (configs[2]: 1024 over 8 GPUs)")
     ap.add_argument("--swap-sources", type=int, default=8, help="source images per GPU of the swap leg (x 20 units)")
     ap.add_argument("--workload", default="shapes3d", choices=sorted(WORKLOADS),
@@ -382,6 +450,8 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-ddim", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-comparators", action="store_true",
+                    help="skip the same-GPU comparators (reference modules in eager mode, drop-in autograd path)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
