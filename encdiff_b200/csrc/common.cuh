@@ -160,14 +160,16 @@ __device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
     }
   }
 }
-// Bounded wait: a pipeline bug must become a trap (reported CUDA error), never a hung GPU.
+// Bounded wait: a pipeline bug must become a trap (reported CUDA error), never a hung GPU.  The bound is a retry count
+// (try_wait suspends the thread for a hardware-defined time slice per attempt), not clock64(): the single-thread producer /
+// MMA loops run through here once per pipeline stage and a clock read per retry sat on their critical path.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  long long t0 = clock64();
+  unsigned n = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) {  // ~2 s at 2 GHz
-      printf("encdiff_b200: mbarrier wait timeout (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y,
-             blockIdx.z, threadIdx.x);
+    if (++n > (1u << 26)) {
+      printf("encdiff_b200: mbarrier wait timeout (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y, blockIdx.z,
+             threadIdx.x);
       __trap();
     }
   }

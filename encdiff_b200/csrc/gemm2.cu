@@ -98,7 +98,12 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    // The whole warp walks the loop with warp-uniform values (ring position, tile origin, descriptors live in uniform
+    // registers) and ONE elected lane issues the asynchronous instructions.  With the loop inside `if (lane == 0)` ptxas
+    // had to wrap every UTMALDG / UTCHMMA in an ELECT + R2UR.BROADCAST + BRA.U.ANY uniformisation loop (~35 cycles per
+    // instruction on the single issuing thread, which is what paces a k-block at the narrow N tiles of this network).
+    const bool leader = elect_one();
+    {
       // The producer and the MMA issuer are single threads whose loop bodies are on the critical path of every k-block
       // (profiles/experiments/r01_gemm_pacing.txt): the ring position (stage, phase) is carried incrementally -- no
       // division / modulo by STAGES -- and nothing is done per k-block that can be done per stage or per tile.
@@ -122,11 +127,13 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
               if (slot == 0) {      // first k-block of a stage: wait for the slot, announce the bytes of the whole stage
                 mbar_wait(&empty_bar[st], ph ^ 1);
                 in_stage = nkb - kb < KPS ? nkb - kb : KPS;
-                mbar_arrive_expect_tx(&full_bar[st], in_stage * SLOT_BYTES);
+                if (leader) mbar_arrive_expect_tx(&full_bar[st], in_stage * SLOT_BYTES);
               }
               uint8_t* sa = smem + st * STAGE_BYTES + slot * SLOT_BYTES;
-              tma_load_4d(sa, &p.amap[s], &full_bar[st], c * kChunk2, dx, y0 + dy, b0);
-              tma_load_2d(sa + kABytes2, &p.bmap, &full_bar[st], kb * kChunk2, n_tile * BN);
+              if (leader) {
+                tma_load_4d(sa, &p.amap[s], &full_bar[st], c * kChunk2, dx, y0 + dy, b0);
+                tma_load_2d(sa + kABytes2, &p.bmap, &full_bar[st], kb * kChunk2, n_tile * BN);
+              }
               if (++slot == in_stage) {
                 slot = 0;
                 if (++st == STAGES) {
@@ -140,7 +147,8 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    const bool leader = elect_one();
+    {
       constexpr uint32_t idesc = make_idesc(BN, false, false);
       uint32_t lt = 0, ph = 0;
       int st = 0;
@@ -162,17 +170,19 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
             if (j < nk) {
               const uint64_t da = da0 + soff + j * (SLOT_BYTES >> 4);
               const uint64_t db = db0 + soff + j * (SLOT_BYTES >> 4);
+              if (leader) {
 #pragma unroll
-              for (int k = 0; k < kChunk2 / 16; ++k) umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, ((kb + j) | k) ? 1u : 0u);
+                for (int k = 0; k < kChunk2 / 16; ++k) umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, ((kb + j) | k) ? 1u : 0u);
+              }
             }
           }
-          umma_commit(&empty_bar[st]);
+          if (leader) umma_commit(&empty_bar[st]);
           if (++st == STAGES) {
             st = 0;
             ph ^= 1;
           }
         }
-        umma_commit(&tfull[acc]);
+        if (leader) umma_commit(&tfull[acc]);
       }
     }
   } else {

@@ -133,7 +133,8 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    const bool leader = elect_one();   // whole warp walks the loop (uniform registers), one elected lane issues: see gemm2.cu
+    {
       // single-thread loop on the critical path of every reduction step (profiles/experiments/r01_gemm_pacing.txt): ring
       // position and tile origin are carried incrementally (no division per step)
       int st = 0;
@@ -158,10 +159,12 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
         for (int t = t_begin; t < t_end; ++t) {
           mbar_wait(&empty_bar[st], ph ^ 1);
           uint8_t* sp = smem + st * kWStageBytes;
-          mbar_arrive_expect_tx(&full_bar[st], kWStageBytes);
-          tma_load_4d(sp, &p.pmap, &full_bar[st], p_col, 0, y0, b0);
-          tma_load_4d(sp + kBox, &p.pmap, &full_bar[st], p_col + 64, 0, y0, b0);
-          tma_load_4d(sp + 2 * kBox, &p.qmap, &full_bar[st], q_col, dx, y0 + dy, b0);
+          if (leader) {
+            mbar_arrive_expect_tx(&full_bar[st], kWStageBytes);
+            tma_load_4d(sp, &p.pmap, &full_bar[st], p_col, 0, y0, b0);
+            tma_load_4d(sp + kBox, &p.pmap, &full_bar[st], p_col + 64, 0, y0, b0);
+            tma_load_4d(sp + 2 * kBox, &p.qmap, &full_bar[st], q_col, dx, y0 + dy, b0);
+          }
           if (g.tiles_per_img > 1) {          // next 128-pixel tile: further down the same image, or the next image(s)
             y0 += g.box_h;
             if (y0 >= g.H) {
@@ -179,7 +182,8 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    const bool leader = elect_one();
+    {
       constexpr uint32_t idesc = make_idesc(kWN, true, true);
       const uint32_t ones_addr = smem_u32(ones);
       uint32_t lt = 0, ph = 0;
@@ -208,16 +212,18 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
           const uint64_t so = static_cast<uint64_t>(st) * kStageUnits;
           const uint64_t da = da0 + so;
           const uint64_t db = db0 + so - (so << 16);
+          if (leader) {
 #pragma unroll
-          for (int k = 0; k < kPix / 16; ++k)   // 16 pixels (the reduction) = 16 rows of 128 B = 2048 B per MMA step
-            umma_f16(tacc, da + k * (2048 >> 4), db + k * (2048 >> 4), idesc, (i | k) ? 1u : 0u);
-          umma_commit(&empty_bar[st]);
+            for (int k = 0; k < kPix / 16; ++k)   // 16 pixels (the reduction) = 16 rows of 128 B = 2048 B per MMA step
+              umma_f16(tacc, da + k * (2048 >> 4), db + k * (2048 >> 4), idesc, (i | k) ? 1u : 0u);
+            umma_commit(&empty_bar[st]);
+          }
           if (++st == kWStages) {
             st = 0;
             ph ^= 1;
           }
         }
-        umma_commit(&tfull[acc]);
+        if (leader) umma_commit(&tfull[acc]);
       }
     }
   } else {
