@@ -289,10 +289,15 @@ __device__ __forceinline__ void pdl_enter() {
 }
 
 bool pdl_enabled();   // host.cu: false when ENCDIFF_NO_PDL is set
+// Measurement aid (host.cu, tools/exp_ablate.py): true when ENCDIFF_DEBUG_SKIP_KERNELS holds a comma-separated list of
+// substrings and the (mangled) name of `func` contains one of them.  launch_k then enqueues nothing, so the marginal
+// in-graph cost of a kernel family is the step-time difference; results are garbage by construction.  Unset: no effect.
+bool debug_skip_kernel(const void* func);
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                             Args&&... args) {
+  if (debug_skip_kernel(reinterpret_cast<const void*>(kernel))) return cudaSuccess;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = grid;

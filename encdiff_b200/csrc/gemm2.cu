@@ -313,26 +313,19 @@ int sgemm2_pick_bn(int m_tiles, int N, int num_sms, int nkb) {
 int launch_sgemm2(const Sgemm2Params& p, int bn, int num_sms, cudaStream_t stream) {
   int nkb = 0;
   for (int s = 0; s < p.nsrc; ++s) nkb += p.src_chunks[s] * p.src_taps[s];
-  // short-K GEMMs (1x1 / linear with K <= 576): a tile is 1-9 k-blocks, so a deep smem ring buys nothing; two small
-  // CTAs per SM overlap one CTA's epilogue / fill / drain with the other's loads instead
-  static const bool no_occ2 = getenv("ENCDIFF_NO_OCC2") != nullptr;
-  // threshold measured on the B = 256 step (k-blocks <= 4 / 9 / 18 / 36 / all: 10.33 / 10.27 / 10.28 / 10.40 / 10.46 ms):
-  // two 3-stage CTAs per SM equal one 6-stage CTA on the deep-K shapes -- the SM's L2 ingest is what is shared
-  static const int shallow_max = getenv("ENCDIFF_SHALLOW_KB") ? atoi(getenv("ENCDIFF_SHALLOW_KB")) : 9;
-  const bool shallow = nkb <= shallow_max && !no_occ2;
-  static const int kps = getenv("ENCDIFF_KPS") ? atoi(getenv("ENCDIFF_KPS")) : 2;
-  static const int kps128 = getenv("ENCDIFF_KPS128") ? atoi(getenv("ENCDIFF_KPS128")) : 2;
+  // short-K GEMMs (1x1 / linear with K <= 576 = 9 k-blocks): a tile is 1-9 k-blocks, so a deep smem ring buys nothing;
+  // two small CTAs per SM overlap one CTA's epilogue / fill / drain with the other's loads instead.  Threshold and the
+  // k-blocks per stage of the deep variants (2) were measured on the B = 256 step: k-blocks <= 4 / 9 / 18 / 36 / all gave
+  // 10.33 / 10.27 / 10.28 / 10.40 / 10.46 ms, KPS 1 / 2 / 3 gave 10.27 / 10.11 / 10.25 ms
+  // (profiles/experiments/r01_gemm_kps_sweep.txt).  Constants, not environment tunables.
+  const bool shallow = nkb <= 9;
   switch (bn) {
     case 64:
       if (shallow) return launch_sgemm2_t<64, 3, 2>(p, num_sms, stream);
-      if (kps == 3) return launch_sgemm2_t<64, 2, 1, 3>(p, num_sms, stream);
-      if (kps == 2) return launch_sgemm2_t<64, 3, 1, 2>(p, num_sms, stream);
-      return launch_sgemm2_t<64, 6, 1>(p, num_sms, stream);
+      return launch_sgemm2_t<64, 3, 1, 2>(p, num_sms, stream);
     case 128:
       if (shallow) return launch_sgemm2_t<128, 2, 2>(p, num_sms, stream);
-      if (kps128 == 2) return launch_sgemm2_t<128, 2, 1, 2>(p, num_sms, stream);
-      if (kps128 == 3) return launch_sgemm2_t<128, 2, 1, 3>(p, num_sms, stream);
-      return launch_sgemm2_t<128, 5, 1>(p, num_sms, stream);
+      return launch_sgemm2_t<128, 2, 1, 2>(p, num_sms, stream);
     case 256: return launch_sgemm2_t<256, 3, 1>(p, num_sms, stream);
     default: return static_cast<int>(cudaErrorInvalidValue);
   }

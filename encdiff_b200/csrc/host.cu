@@ -159,4 +159,25 @@ bool pdl_enabled() {
   return on;
 }
 
+bool debug_skip_kernel(const void* func) {
+  const char* pat = getenv("ENCDIFF_DEBUG_SKIP_KERNELS");   // read per launch: launches happen at capture time only
+  if (!pat || !*pat) return false;
+  const char* name = nullptr;
+  if (cudaFuncGetName(&name, func) != cudaSuccess || !name) return false;
+  const char* p = pat;
+  while (*p) {
+    const char* e = strchr(p, ',');
+    const size_t n = e ? static_cast<size_t>(e - p) : strlen(p);
+    if (n > 0 && n < 200) {
+      char buf[200];
+      memcpy(buf, p, n);
+      buf[n] = 0;
+      if (strstr(name, buf)) return true;
+    }
+    if (!e) break;
+    p = e + 1;
+  }
+  return false;
+}
+
 }  // namespace edb

@@ -2,8 +2,7 @@
 replayed graph, L2-hot): the micro-benchmark behind profiles/experiments/r01_gemm_pacing.txt.  The ENCDIFF_GEMM_DEBUG
 bits that experiment used (drop the loads / the MMAs / the epilogue work) lived in sgemm2_kernel only for that study
 (commit "sgemm2 pacing experiment", removed afterwards because every instruction in the single-thread producer / MMA
-loops costs step time); what remains tunable: ENCDIFF_KPS / ENCDIFF_KPS128 (k-blocks per pipeline stage) and
-ENCDIFF_SHALLOW_KB.  usage: ENCDIFF_KPS=2 python tools/exp_gemm_pacing.py"""
+loops costs step time).  usage: python tools/exp_gemm_pacing.py"""
 import os
 import sys
 
@@ -20,7 +19,7 @@ SHAPES = [  # (B, H, W, Cin, Cout, taps)
 def main():
     dev = torch.device("cuda:0")
     dt = _lib.act_dtype()
-    dbg = os.environ.get("ENCDIFF_KPS", "-")
+    dbg = os.environ.get("ENCDIFF_TAG", "-")
     for (B, H, W, ci, co, taps) in SHAPES:
         x = torch.randn(B, H, W, ci, device=dev).to(dt)
         if taps == 9:
@@ -46,7 +45,7 @@ def main():
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) / 100 * 1e3
         M, K = B * H * W, ci * taps
-        print(f"kps={dbg} M={M} N={co} K={K} taps={taps}: {us:7.2f} us  {2.0 * M * co * K / us / 1e6:7.1f} TF/s",
+        print(f"{dbg} M={M} N={co} K={K} taps={taps}: {us:7.2f} us  {2.0 * M * co * K / us / 1e6:7.1f} TF/s",
               flush=True)
 
 
