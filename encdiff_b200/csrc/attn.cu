@@ -880,8 +880,10 @@ int launch_cross_attn_fwd(const h16* q, const float* ctx, const float* wk, const
                           int heads, int D, int T, int Dc, cudaStream_t s, const float* kv) {
   if (T < 1 || T > kMaxT || Dc < 1 || Dc > kMaxDc) return static_cast<int>(cudaErrorInvalidValue);
   static const bool cuda_core_only = getenv("ENCDIFF_ATTN_CUDA_CORE") != nullptr;
+  static const bool staged_only = getenv("ENCDIFF_ATTN_STAGED") != nullptr;   // tests: keep the attn_mma.cu kernels covered
   if (kv && !cuda_core_only) {
-    const int rc = launch_cross_attn_fwd_mma(q, kv, out, B, N, heads, D, T, s);
+    int rc = staged_only ? -1 : launch_cross_attn_fwd_reg(q, kv, out, B, N, heads, D, T, s);
+    if (rc == -1) rc = launch_cross_attn_fwd_mma(q, kv, out, B, N, heads, D, T, s);
     if (rc != -1) return rc;
   }
   switch (D) {
@@ -904,7 +906,9 @@ int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const
   const int C = heads * D;
   static const bool cuda_core_only = getenv("ENCDIFF_ATTN_CUDA_CORE") != nullptr;
   int rc = -1;
-  if (kv && !cuda_core_only) rc = launch_cross_attn_bwd_mma(q, kv, dout, dq, dkv_scratch, B, N, heads, D, T, s);
+  static const bool staged_only = getenv("ENCDIFF_ATTN_STAGED") != nullptr;
+  if (kv && !cuda_core_only && !staged_only) rc = launch_cross_attn_bwd_reg(q, kv, dout, dq, dkv_scratch, B, N, heads, D, T, s);
+  if (kv && !cuda_core_only && rc == -1) rc = launch_cross_attn_bwd_mma(q, kv, dout, dq, dkv_scratch, B, N, heads, D, T, s);
   cudaError_t e = cudaSuccess;
   if (rc == -1) {
   e = cudaMemsetAsync(dkv_scratch, 0, cross_attn_bwd_scratch_bytes(B, heads, D, T), s);

@@ -73,6 +73,10 @@ int launch_cross_attn_bwd(const h16* q, const float* ctx, const float* wk, const
                           const float* kv = nullptr);
 // tensor-core (mma.sync) variants over pre-projected K | V, attn_mma.cu; -1 when the shape is not handled
 int launch_cross_attn_fwd_mma(const h16* q, const float* kv, h16* out, int B, int N, int heads, int D, int T, cudaStream_t s);
+// register-resident variants (attn_reg.cu); -1 = shape not covered
+int launch_cross_attn_fwd_reg(const h16* q, const float* kv, h16* out, int B, int N, int heads, int D, int T, cudaStream_t s);
+int launch_cross_attn_bwd_reg(const h16* q, const float* kv, const h16* dout, h16* dq, float* dkv, int B, int N, int heads,
+                              int D, int T, cudaStream_t s);
 int launch_cross_attn_bwd_mma(const h16* q, const float* kv, const h16* dout, h16* dq, float* dkv, int B, int N, int heads,
                               int D, int T, cudaStream_t s);
 // deferred form of the projection half (d to_k, d to_v, d context) for all layers at once: dkv of every layer must still

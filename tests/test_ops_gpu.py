@@ -63,11 +63,17 @@ def test_self_attention_fwd_bwd(cuda_device, N, D):
         assert rel_err(got, ref) <= 2 * tol16(), name
 
 
-@pytest.mark.parametrize("use_kv", [False, True])       # True: pre-projected K | V -> the tensor-core kernels
-@pytest.mark.parametrize("N,D", [(256, 8), (64, 16), (16, 32), (4, 32)])
-def test_cross_attention_fwd_bwd(cuda_device, N, D, use_kv):
+# use_kv True: pre-projected K | V -> the tensor-core kernels.  The step's four shapes and (256, 16) (the synthesised
+# CelebA-64 widths) run the register-resident kernels of attn_reg.cu, T = 20 with three key tiles and T = 27 with four;
+# (32, 16) and (128, 8) have no register-resident variant and keep the staged kernels of attn_mma.cu covered; use_kv
+# False is the CUDA-core path that projects K | V itself.
+@pytest.mark.parametrize("N,D,T,use_kv", [(256, 8, 20, True), (64, 16, 20, True), (16, 32, 20, True), (4, 32, 20, True),
+                                          (256, 16, 20, True), (256, 8, 27, True), (64, 16, 32, True), (16, 32, 9, True),
+                                          (32, 16, 20, True), (128, 8, 20, True),
+                                          (256, 8, 20, False), (64, 16, 20, False), (16, 32, 20, False), (4, 32, 20, False)])
+def test_cross_attention_fwd_bwd(cuda_device, N, D, T, use_kv):
     _lib, lib, dt = lib_and_dtype()
-    B, heads, T, Dc = 5, 8, 20, 16
+    B, heads, Dc = 5, 8, 16
     C = heads * D
     gen = torch.Generator().manual_seed(7 * N + D)
     q16 = torch.randn(B, N, C, generator=gen).to(dt)
