@@ -57,6 +57,8 @@ PROTOTYPES = {
     "encdiff_unet_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_void_p]),
     "encdiff_unet_backward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "encdiff_unet_fp32_workspace_bytes": (c_ll, [c_void_p, c_int]),
+    "encdiff_unet_forward_fp32": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "encdiff_unet_profile": (c_int, [c_void_p, c_int]),
     "encdiff_unet_profile_read": (c_ll, [c_void_p, C.c_char_p, c_ll]),
     "encdiff_unet_debug_block": (c_int, [c_void_p, c_int, c_int, C.POINTER(c_void_p), C.POINTER(c_int),

@@ -111,6 +111,19 @@ extern "C" int encdiff_unet_plan(encdiff_unet* h, int batch, void* workspace, in
   return unet_plan(&h->u, batch, static_cast<char*>(workspace), training != 0);
 }
 
+extern "C" long long encdiff_unet_fp32_workspace_bytes(encdiff_unet* h, int batch) {
+  if (!h || batch <= 0) return -1;
+  return static_cast<long long>(unet_fp32_workspace_floats(&h->u, batch) * sizeof(float));
+}
+
+extern "C" int encdiff_unet_forward_fp32(encdiff_unet* h, int batch, const float* x, const float* t, const float* ctx,
+                                         float* out, void* workspace, long long workspace_bytes, void* stream) {
+  EDB_REQUIRE(h && x && t && ctx && out && workspace && batch > 0, "unet_forward_fp32: bad argument");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "unet_forward_fp32: workspace must be 256-byte aligned");
+  return unet_forward_fp32(&h->u, batch, x, t, ctx, out, static_cast<float*>(workspace),
+                           static_cast<size_t>(workspace_bytes) / sizeof(float), static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int encdiff_unet_forward(encdiff_unet* h, int batch, const float* x, const float* noise, const float* sqrt_acp,
                                     const float* sqrt_1macp, const float* t, const float* ctx, float* out, float* x_t,
                                     void* stream) {

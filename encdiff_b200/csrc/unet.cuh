@@ -167,5 +167,9 @@ size_t unet_workspace_bytes(UNet* u, int B, bool training);
 int unet_forward(UNet* u, int B, const float* x, const float* noise, const float* sa, const float* sb, const float* t,
                  const float* ctx, float* out, float* xt, cudaStream_t s);
 int unet_backward(UNet* u, int B, const float* dout, const float* ctx, float* dx, float* dctx, cudaStream_t s);
+// fp32 validation forward (fp32_ref.cu): fp32 tensors, CUDA-core FMA contractions, reference-layout master parameters
+size_t unet_fp32_workspace_floats(UNet* u, int B);
+int unet_forward_fp32(UNet* u, int B, const float* x, const float* t, const float* ctx, float* out, float* ws,
+                      size_t ws_floats, cudaStream_t s);
 
 }  // namespace edb

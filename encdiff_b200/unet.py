@@ -306,6 +306,31 @@ class UNetModel(nn.Module):
         parts = self._gflat.clone().split([v.numel() for v in self._grad_views])
         return dx, dctx, tuple(c.view_as(v) for c, v in zip(parts, self._grad_views))
 
+    @torch.no_grad()
+    def forward_fp32(self, x, timesteps, context):
+        """The library's fp32 VALIDATION forward (csrc/fp32_ref.cu, ``encdiff_unet_forward_fp32``): fp32 tensors and
+        CUDA-core FMA contractions over the fp32 master parameters -- the north star's "fp32 validation build"
+        (eps max relative error <= 1e-4).  A checker for tests at shapes the CPU oracle cannot reach; not a product path
+        (no autograd, ~100x slower than ``forward``)."""
+        cond = context[0] if isinstance(context, (list, tuple)) else context
+        if x.device.type != "cuda":
+            raise RuntimeError("encdiff_b200.UNetModel.forward_fp32 runs on CUDA only")
+        B = x.shape[0]
+        x = x.contiguous().float()
+        t = timesteps.to(device=x.device, dtype=torch.float32).contiguous()
+        cond = cond.reshape(B, -1).contiguous().float()
+        self._bind(need_grads=False)
+        nbytes = self._lib.encdiff_unet_fp32_workspace_bytes(self._h, B)
+        if nbytes < 0:
+            raise RuntimeError("encdiff_b200: fp32_workspace_bytes failed")
+        ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=x.device)
+        ws_ptr = (ws.data_ptr() + 255) // 256 * 256
+        out = torch.empty(B, self.out_channels, x.shape[2], x.shape[3], dtype=torch.float32, device=x.device)
+        _lib.check(self._lib.encdiff_unet_forward_fp32(self._h, B, x.data_ptr(), t.data_ptr(), cond.data_ptr(),
+                                                       out.data_ptr(), ws_ptr, nbytes, _lib.current_stream()),
+                   "unet_forward_fp32")
+        return out
+
     def profile(self, enable: bool):
         """Switch the library's per-launch event timing on/off (bench.py roofline figures)."""
         _lib.check(self._lib.encdiff_unet_profile(self._h, int(enable)), "unet_profile")

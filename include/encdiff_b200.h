@@ -160,6 +160,15 @@ int encdiff_unet_plan(encdiff_unet* h, int batch, void* workspace, int training)
 int encdiff_unet_forward(encdiff_unet* h, int batch, const float* x, const float* noise, const float* sqrt_acp,
                          const float* sqrt_1macp, const float* t, const float* ctx, float* out, float* x_t_out,
                          void* stream);
+/* fp32 VALIDATION forward (the north star's "fp32 validation build", eps max relative error <= 1e-4 against the
+ * reference's fp32 result): the same UNetModel.forward (openaimodel_enc.py:712-748) with fp32 tensors, fp32 FMA
+ * contractions on the CUDA cores and the bound fp32 master parameters read in the reference's layouts -- no 16-bit
+ * operands, no tensor cores, slow by design.  A checker that runs on the GPU at any batch (tests compare the 16-bit
+ * product path with it at B = 256); needs bind() only, not plan().  workspace: 256-byte aligned,
+ * >= encdiff_unet_fp32_workspace_bytes(h, batch). */
+long long encdiff_unet_fp32_workspace_bytes(encdiff_unet* h, int batch);
+int encdiff_unet_forward_fp32(encdiff_unet* h, int batch, const float* x, const float* t, const float* ctx, float* out,
+                              void* workspace, long long workspace_bytes, void* stream);
 /* Backward of the last forward on this handle (training plan).  dout [B,Cout,S,S] fp32; writes dx (may be NULL) and
  * dctx [B, latent_unit*context_dim] fp32 (overwritten); parameter gradients are accumulated into the bound tensors. */
 int encdiff_unet_backward(encdiff_unet* h, int batch, const float* dout, const float* ctx, float* dx, float* dctx,
