@@ -132,7 +132,11 @@ __global__ void __launch_bounds__(512) self_attn_fwd_mma_kernel(const h16* __res
   m0 = quad_max(m0) * scale_log2;
   m1 = quad_max(m1) * scale_log2;
   // pass 2: p = 2^(s*scale_log2 - m), l = sum p, O = P V
-  float l0 = 0.f, l1 = 0.f;
+  // The row sums l ride on the tensor pipe: one extra MMA per 16-key block against an all-ones B fragment (every
+  // column of `ls` is the row sum of the SAME 16-bit P that feeds P V, so normalisation and numerator agree) instead of
+  // 8 FADDs + a quad reduction -- the loop is instruction-issue bound (ncu: 60 % issue-active, 37 instructions per block).
+  float ls[4] = {0.f, 0.f, 0.f, 0.f};
+  const uint32_t ones = pack2(1.f, 1.f);
   float o[DC][4];
 #pragma unroll
   for (int nt = 0; nt < DC; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
@@ -146,18 +150,16 @@ __global__ void __launch_bounds__(512) self_attn_fwd_mma_kernel(const h16* __res
       c[i][1] = ex2_approx(c[i][1] * scale_log2 - m0);
       c[i][2] = ex2_approx(c[i][2] * scale_log2 - m1);
       c[i][3] = ex2_approx(c[i][3] * scale_log2 - m1);
-      l0 += c[i][0] + c[i][1];
-      l1 += c[i][2] + c[i][3];
     }
     uint32_t pa[4] = {pack2(c[0][0], c[0][1]), pack2(c[0][2], c[0][3]), pack2(c[1][0], c[1][1]), pack2(c[1][2], c[1][3])};
+    mma_k16(ls, pa, ones, ones);
 #pragma unroll
     for (int nt = 0; nt < DC; ++nt) {
       const h16* vp = Vh + (nt * 8 + g) * NP + kc + 2 * t;
       mma_k16(o[nt], pa, lds32(vp), lds32(vp + 8));
     }
   }
-  l0 = quad_sum(l0);
-  l1 = quad_sum(l1);
+  const float l0 = ls[0], l1 = ls[2];
   const float i0 = 1.f / l0, i1 = 1.f / l1;
   const long long row0 = static_cast<long long>(b) * N + q0 + g;
 #pragma unroll
@@ -292,7 +294,9 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
     AFrag<D> qa, oa;
     qa.load(Qh, r0, g, t);
     oa.load(Oh, r0, g, t);
-    const float ls0 = Lh[r0 + g], ls1 = Lh[r0 + g + 8], de0 = Dh[r0 + g], de1 = Dh[r0 + g + 8];
+    // sfs = scale * fsc is folded into the exponent (P * sfs = 2^(x - lse + log2 sfs)): one multiply less per score
+    const float lsf = log2f(sfs);
+    const float ls0 = Lh[r0 + g] - lsf, ls1 = Lh[r0 + g + 8] - lsf, de0 = Dh[r0 + g], de1 = Dh[r0 + g + 8];
     float dq[DC][4];
 #pragma unroll
     for (int nt = 0; nt < DC; ++nt) dq[nt][0] = dq[nt][1] = dq[nt][2] = dq[nt][3] = 0.f;
@@ -303,10 +307,10 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
       for (int i = 0; i < 2; ++i) {
         mma_rowsT<D>(s[i], qa, Kh, kc + 8 * i, g, t);
         mma_rowsT<D>(dp[i], oa, Vh, kc + 8 * i, g, t);
-        s[i][0] = ex2_approx(s[i][0] * scale_log2 - ls0) * (dp[i][0] - de0) * sfs;
-        s[i][1] = ex2_approx(s[i][1] * scale_log2 - ls0) * (dp[i][1] - de0) * sfs;
-        s[i][2] = ex2_approx(s[i][2] * scale_log2 - ls1) * (dp[i][2] - de1) * sfs;
-        s[i][3] = ex2_approx(s[i][3] * scale_log2 - ls1) * (dp[i][3] - de1) * sfs;
+        s[i][0] = ex2_approx(s[i][0] * scale_log2 - ls0) * (dp[i][0] - de0);
+        s[i][1] = ex2_approx(s[i][1] * scale_log2 - ls0) * (dp[i][1] - de0);
+        s[i][2] = ex2_approx(s[i][2] * scale_log2 - ls1) * (dp[i][2] - de1);
+        s[i][3] = ex2_approx(s[i][3] * scale_log2 - ls1) * (dp[i][3] - de1);
       }
       uint32_t da[4] = {pack2(s[0][0], s[0][1]), pack2(s[0][2], s[0][3]), pack2(s[1][0], s[1][1]), pack2(s[1][2], s[1][3])};
 #pragma unroll
@@ -337,15 +341,17 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
         mma_rowsT<D>(st[i], ka, Qh, qc + 8 * i, g, t);     // S^T[key][query]
         mma_rowsT<D>(dpt[i], va, Oh, qc + 8 * i, g, t);    // dP^T[key][query]
         const float2 lq = *reinterpret_cast<const float2*>(Lh + qc + 8 * i + 2 * t);   // columns 2t, 2t+1 = queries
-        const float2 dq2 = *reinterpret_cast<const float2*>(Dh + qc + 8 * i + 2 * t);
+        float2 dq2 = *reinterpret_cast<const float2*>(Dh + qc + 8 * i + 2 * t);
+        dq2.x *= -sfs;       // ds = P * fma(dP, sfs, -delta * sfs)
+        dq2.y *= -sfs;
         st[i][0] = ex2_approx(st[i][0] * scale_log2 - lq.x);
         st[i][1] = ex2_approx(st[i][1] * scale_log2 - lq.y);
         st[i][2] = ex2_approx(st[i][2] * scale_log2 - lq.x);
         st[i][3] = ex2_approx(st[i][3] * scale_log2 - lq.y);
-        ds[i][0] = st[i][0] * (dpt[i][0] - dq2.x) * sfs;
-        ds[i][1] = st[i][1] * (dpt[i][1] - dq2.y) * sfs;
-        ds[i][2] = st[i][2] * (dpt[i][2] - dq2.x) * sfs;
-        ds[i][3] = st[i][3] * (dpt[i][3] - dq2.y) * sfs;
+        ds[i][0] = st[i][0] * fmaf(dpt[i][0], sfs, dq2.x);
+        ds[i][1] = st[i][1] * fmaf(dpt[i][1], sfs, dq2.y);
+        ds[i][2] = st[i][2] * fmaf(dpt[i][2], sfs, dq2.x);
+        ds[i][3] = st[i][3] * fmaf(dpt[i][3], sfs, dq2.y);
       }
       uint32_t pa[4] = {pack2(st[0][0], st[0][1]), pack2(st[0][2], st[0][3]), pack2(st[1][0], st[1][1]), pack2(st[1][2], st[1][3])};
       uint32_t da[4] = {pack2(ds[0][0], ds[0][1]), pack2(ds[0][2], ds[0][3]), pack2(ds[1][0], ds[1][1]), pack2(ds[1][2], ds[1][3])};
