@@ -33,6 +33,7 @@ struct GnParams {
   float* dgamma; float* dbeta; // fp32 atomics
   h16* dfilm; int lddfilm;    // grad of film (same column layout), plain store
   const float* gscale;         // device {scale, 1/scale} of the activation gradients (null = 1): fp32 outputs are unscaled
+  int stash_off;               // backward, set by the launcher: float offset of the per-thread dy' stash in shared memory (0 = none)
 };
 int launch_gn_fwd(const GnParams& p, int B, cudaStream_t s);
 int launch_gn_bwd(const GnParams& p, int B, cudaStream_t s);
