@@ -545,7 +545,8 @@ int launch_gn_bwd(const GnParams& p_in, int B, cudaStream_t s) {
   // dy' stash of the un-resampled SiLU path: one 16-byte slot per (thread, vector of the thread); used when the sample's
   // 16-bit slab fits next to the reduction scratch with two CTAs per SM (up to 96 KB: 16x16x192 is the largest level-0 slab)
   p.stash_off = 0;
-  if (p.resample == RESAMPLE_NONE && p.silu) {
+  static const bool no_stash = getenv("ENCDIFF_GN_NO_STASH") != nullptr;   // A/B switch (parity experiments)
+  if (p.resample == RESAMPLE_NONE && p.silu && !no_stash) {
     const int threads = gn_threads(C, 256), nv = C / 8, rp = threads / nv;
     const size_t vecs = static_cast<size_t>((p.H * p.W + rp - 1) / rp + 3) * threads;   // + the 4-deep batch rounding
     const size_t off = (smem + 15) & ~size_t(15);

@@ -179,8 +179,11 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
 }
 
 size_t unet_workspace_bytes(UNet* u, int B, bool training) {
-  unet_plan(u, B, nullptr, training);
-  return u->ws_bytes_persist + u->ws_bytes_scratch + 1024;
+  // sizing runs the planner on a COPY: a live plan (layer pointers, tensor maps, device-table state) stays valid when a
+  // caller merely asks for a size (bench.py does, between a trainer step and an autograd-path forward)
+  UNet tmp = *u;
+  unet_plan(&tmp, B, nullptr, training);
+  return tmp.ws_bytes_persist + tmp.ws_bytes_scratch + 1024;
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -31,7 +31,7 @@ class _UNetFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, model, x, t, cond, *params):
-        out = model._run_forward(x, t, cond, training=True)
+        out = model._auto_forward(x, t, cond)
         ctx.model = model
         ctx.fwd_id = model._fwd_id
         ctx.save_for_backward(cond)
@@ -47,7 +47,7 @@ class _UNetFn(torch.autograd.Function):
         if ctx.fwd_id != model._fwd_id:
             raise RuntimeError("encdiff_b200.UNetModel: the activation workspace of this forward was overwritten by a "
                                "later forward; run backward before the next forward")
-        dx, dctx, grads = model._run_backward(dout, cond, ctx.need_dx)
+        dx, dctx, grads = model._auto_backward(dout, cond, ctx.need_dx)
         return (None, dx, None, dctx) + tuple(g if need else None for g, need in zip(grads, ctx.need_param))
 
 
@@ -168,6 +168,13 @@ class UNetModel(nn.Module):
         self._fwd_id = 0
         self._planned = None
         self.cache_packed_weights = False   # set by the sampler: parameters do not change inside its loop
+        # The autograd path (forward() under grad mode + loss.backward(): what a reference training loop drives) replays
+        # captured CUDA graphs of the library's forward / backward launch sequences from the third call of a shape on
+        # (call 1 runs eagerly and lets the library build its device tables, call 2 captures).  ~330 / ~430 launches
+        # become one graph launch each.  Set False to run every call eagerly.
+        self.graph_autograd = True
+        self._auto = {}
+        self._prof_on = False
         self._packed_valid = False
 
     # ------------------------------------------------------------------------------------------------------------
@@ -331,8 +338,79 @@ class UNetModel(nn.Module):
                    "unet_forward_fp32")
         return out
 
+    # ---- graph replay of the autograd path -------------------------------------------------------------------------
+    def _graph_ok(self):
+        # cache_packed_weights (sampler loops) skips the re-pack: such calls stay eager so that every captured forward
+        # contains the pack kernel and always sees the current master weights
+        return (self.graph_autograd and not self._prof_on and not self.cache_packed_weights
+                and not torch.cuda.is_current_stream_capturing())
+
+    def _auto_forward(self, x, t, cond):
+        if not self._graph_ok():
+            return self._run_forward(x, t, cond, training=True)
+        st = self._auto.setdefault(("fwd", x.shape[0]), {})
+        if st.get("plan") is None or st["plan"] != self.plan_key():
+            out = self._run_forward(x, t, cond, training=True)       # eager: the library builds its tables for this plan
+            st.clear()
+            st["plan"] = self.plan_key()
+            return out
+        if st.get("g") is None:
+            sx, stt, sc = x.clone(), t.clone(), cond.clone()
+            torch.cuda.current_stream().synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                so = self._run_forward(sx, stt, sc, training=True)
+            if st["plan"] != self.plan_key():                        # the capture itself must not have re-planned
+                raise RuntimeError("encdiff_b200.UNetModel: plan changed during graph capture")
+            st.update(g=g, x=sx, t=stt, c=sc, out=so)
+        else:
+            st["x"].copy_(x)
+            st["t"].copy_(t)
+            st["c"].copy_(cond)
+        st["g"].replay()
+        self._fwd_id += 1
+        return st["out"].clone()
+
+    def _auto_backward(self, dout, cond, need_dx):
+        if not self._graph_ok():
+            return self._run_backward(dout, cond, need_dx)
+        st = self._auto.setdefault(("bwd", dout.shape[0], bool(need_dx)), {})
+        if st.get("plan") is None or st["plan"] != self.plan_key():
+            res = self._run_backward(dout, cond, need_dx)            # eager: builds the weight-gradient tables
+            st.clear()
+            st["plan"] = self.plan_key()
+            return res
+        dout = dout.contiguous().float()
+        if st.get("g") is None:
+            for p, v in zip(self._params(), self._grad_views):
+                if p.grad is not None and p.grad.data_ptr() == v.data_ptr():
+                    p.grad = p.grad.clone()
+            sd, sc = dout.clone(), cond.clone()
+            B = dout.shape[0]
+            dx = torch.empty(B, self.in_channels, self.image_size, self.image_size, dtype=torch.float32,
+                             device=dout.device) if need_dx else None
+            dctx = torch.empty_like(sc)
+            torch.cuda.current_stream().synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._gflat.zero_()
+                _lib.check(self._lib.encdiff_unet_backward(self._h, B, sd.data_ptr(), sc.data_ptr(), _lib.ptr(dx),
+                                                           dctx.data_ptr(), _lib.current_stream()), "unet_backward")
+            st.update(g=g, d=sd, c=sc, dx=dx, dctx=dctx)
+        else:
+            for p, v in zip(self._params(), self._grad_views):
+                if p.grad is not None and p.grad.data_ptr() == v.data_ptr():
+                    p.grad = p.grad.clone()
+            st["d"].copy_(dout)
+            st["c"].copy_(cond)
+        st["g"].replay()
+        parts = self._gflat.clone().split([v.numel() for v in self._grad_views])
+        dx = st["dx"].clone() if need_dx else None
+        return dx, st["dctx"].clone(), tuple(c.view_as(v) for c, v in zip(parts, self._grad_views))
+
     def profile(self, enable: bool):
         """Switch the library's per-launch event timing on/off (bench.py roofline figures)."""
+        self._prof_on = bool(enable)
         _lib.check(self._lib.encdiff_unet_profile(self._h, int(enable)), "unet_profile")
 
     def profile_read(self):

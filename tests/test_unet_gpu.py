@@ -185,3 +185,32 @@ def test_benched_shape_b256_forward_backward_vs_oracle(cuda_device):
     # per-sample check: no sample of the batch is an outlier (a wrong tile would hit a few samples only)
     per_sample = ((eps.detach().cpu() - eps_o).abs().amax(dim=(1, 2, 3)) / eps_o.abs().max()).max().item()
     assert per_sample <= TOL.eps
+
+
+def test_autograd_path_graph_replay_matches_eager(cuda_device):
+    """The documented drop-in training path (UNetModel.forward under grad mode + loss.backward()) replays captured graphs
+    of the library's launch sequences from the third call on (unet.py:_auto_forward / _auto_backward).  Four successive
+    calls on different inputs: call 1 eager, call 2 captures, calls 3-4 replay; every call is compared with the same call on
+    an eager-only twin (graph_autograd = False).  Weight gradients go through TMA reduce-adds whose order varies from run
+    to run, hence a tolerance instead of bit equality."""
+    cfg = CONFIGS["tiny"]
+    m1, params = make_model(cfg, cuda_device)
+    m2, _ = make_model(cfg, cuda_device)
+    m2.graph_autograd = False
+    for it in range(4):
+        x, t, ctx, noise = seeded_inputs(cfg, 6, seed=500 + it)
+        outs = []
+        for m in (m1, m2):
+            for p in m.parameters():
+                p.grad = None
+            xd = x.to(cuda_device).requires_grad_(True)
+            cd = ctx.to(cuda_device).requires_grad_(True)
+            eps = m(xd, t.to(cuda_device), context=[cd])
+            (eps - noise.to(cuda_device)).abs().mean().backward()
+            outs.append((eps.detach(), xd.grad, cd.grad, [p.grad.clone() for p in m.parameters()]))
+        (e1, dx1, dc1, g1), (e2, dx2, dc2, g2) = outs
+        assert torch.equal(e1, e2), it                      # the forward is deterministic
+        assert rel_err(dx1, dx2) <= 1e-3 and rel_err(dc1, dc2) <= 1e-3, it
+        worst = max(rel_err(a, b) for a, b in zip(g1, g2))
+        assert worst <= 2e-3, (it, worst)
+    assert m1._auto[("fwd", 6)].get("g") is not None and m1._auto[("bwd", 6, True)].get("g") is not None
