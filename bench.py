@@ -420,7 +420,7 @@ def gpu_comparators(model, dev, B, ddim_B):
                 times.append(time.perf_counter() - t0)
         sec = statistics.median(times)
         out["dropin_autograd"] = {"train_img_per_s": B / sec, "train_ms_per_step": sec * 1e3, "batch": B,
-                                  "path": "encdiff_b200.UNetModel.forward + loss.backward() + torch.optim.AdamW (eager)"}
+                                  "path": "encdiff_b200.UNetModel.forward + loss.backward() through torch autograd (the library replays captured graphs of its forward / backward launch sequences) + torch.optim.AdamW"}
     except Exception as e:
         out["dropin_autograd_error"] = repr(e)[:300]
     return out

@@ -61,7 +61,14 @@ def train_step_time(B, steps, warmup, device="cpu", autocast_dtype=None, tf32=Fa
         ctx = torch.autocast("cuda", dtype=autocast_dtype) if autocast_dtype is not None else contextlib.nullcontext()
         with ctx:
             loss, _ = model.p_losses(x0, cond, t, noise=noise)
-        loss.backward()
+            if autocast_dtype is not None:
+                # the reference's CheckpointFunction.backward (diffusionmodules/util.py:147-176) re-runs the block forward
+                # WITHOUT restoring the autocast state, so under autocast its recompute mixes bf16 saved inputs with fp32
+                # weights and raises; keeping backward() inside the autocast region is the only way the unmodified
+                # reference trains in bf16 at all
+                loss.backward()
+        if autocast_dtype is None:
+            loss.backward()
         opt.step()
         if model.use_ema:
             model.model_ema(model.model)
