@@ -57,6 +57,9 @@ PROTOTYPES = {
     "encdiff_unet_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_void_p]),
     "encdiff_unet_backward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "encdiff_vqenc_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
+    "encdiff_vqenc_workspace_bytes": (c_ll, [c_void_p, c_int]),
+    "encdiff_vqenc_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "encdiff_unet_fp32_workspace_bytes": (c_ll, [c_void_p, c_int]),
     "encdiff_unet_forward_fp32": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "encdiff_unet_profile": (c_int, [c_void_p, c_int]),
@@ -85,6 +88,12 @@ class UNetConfigStruct(C.Structure):
                 ("n_channel_mult", c_int), ("channel_mult", c_int * 8), ("num_heads", c_int), ("context_dim", c_int),
                 ("latent_unit", c_int), ("transformer_depth", c_int), ("use_scale_shift_norm", c_int),
                 ("resblock_updown", c_int)]
+
+
+class VQEncConfigStruct(C.Structure):
+    """Mirror of ``encdiff_vqenc_config`` (include/encdiff_b200.h)."""
+    _fields_ = [("ch", c_int), ("n_ch_mult", c_int), ("ch_mult", c_int * 4), ("num_res_blocks", c_int),
+                ("in_channels", c_int), ("resolution", c_int), ("z_channels", c_int), ("embed_dim", c_int)]
 
 
 def lib_path() -> Path:

@@ -111,6 +111,30 @@ extern "C" int encdiff_unet_plan(encdiff_unet* h, int batch, void* workspace, in
   return unet_plan(&h->u, batch, static_cast<char*>(workspace), training != 0);
 }
 
+extern "C" int encdiff_vqenc_create(const encdiff_vqenc_config* cfg, encdiff_unet** out) {
+  EDB_REQUIRE(cfg && out, "vqenc_create: null argument");
+  encdiff_unet* h = new (std::nothrow) encdiff_unet();
+  EDB_REQUIRE(h, "vqenc_create: out of host memory");
+  int rc = vqenc_build(&h->u, cfg);
+  if (rc) {
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return EDB_OK;
+}
+
+extern "C" long long encdiff_vqenc_workspace_bytes(encdiff_unet* h, int batch) {
+  if (!h || batch <= 0 || h->u.model_kind != 1) return -1;
+  return static_cast<long long>(vqenc_workspace_bytes(&h->u, batch));
+}
+
+extern "C" int encdiff_vqenc_forward(encdiff_unet* h, int batch, const float* x, float* z, void* workspace, void* stream) {
+  EDB_REQUIRE(h && x && z && workspace && batch > 0, "vqenc_forward: bad argument");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, "vqenc_forward: workspace must be 1 KB aligned");
+  return vqenc_forward(&h->u, batch, x, z, static_cast<char*>(workspace), static_cast<cudaStream_t>(stream));
+}
+
 extern "C" long long encdiff_unet_fp32_workspace_bytes(encdiff_unet* h, int batch) {
   if (!h || batch <= 0) return -1;
   return static_cast<long long>(unet_fp32_workspace_floats(&h->u, batch) * sizeof(float));

@@ -187,4 +187,12 @@ int launch_adamw_dev(float* p, const float* g, float* m, float* v, float* ema, l
 int launch_adamw_hyper_advance(int* step, const float* lr, float* hyper, float beta1, float beta2, float ema_decay_max,
                                cudaStream_t s);
 
+// ---- first-stage VQ encoder (vq_kernels.cu) ----------------------------------------------------------------------
+// Downsample-with-conv im2col: x NHWC [B, H, H, C] -> cols [B*(H/2)^2, 9 * ceil64(C)] tap-major (pad right / bottom)
+int launch_vq_down_im2col(const h16* x, h16* cols, int B, int H, int C, cudaStream_t s);
+// single-head attention of AttnBlock: qkv [B*N, 3D] -> out [B*N, D], D in {64, 128}, N <= 256 multiple of 16
+int launch_vq_attn(const h16* qkv, h16* out, int B, int N, int D, cudaStream_t s);
+// quant_conv (1x1, zc -> ed) + NHWC fp32 -> NCHW fp32
+int launch_vq_tail(const float* h, const float* wq, const float* bq, float* z, int B, int HW, int zc, int ed, cudaStream_t s);
+
 }  // namespace edb

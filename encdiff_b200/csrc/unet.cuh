@@ -67,6 +67,16 @@ struct StLayer {
   float* kv = nullptr;    // [B, T, 2C] to_k | to_v of the context, projected once per forward for all layers
 };
 
+// first-stage VQ encoder layers (vq_enc.inc): the same UNet object carries their parameters / packed operands
+struct VqLayer {
+  int kind = 0;            // 1 ResnetBlock, 2 Downsample (3x3 stride 2, pad right/bottom), 3 AttnBlock
+  int cin = 0, cout = 0, H = 0;     // H = input spatial size (square)
+  int n1w = -1, n1b = -1, c1w = -1, c1b = -1, n2w = -1, n2b = -1, c2w = -1, c2b = -1, sw = -1, sb = -1;   // res / down (c1*) / attn
+  int qw = -1, qb = -1, kw = -1, kb = -1, vw = -1, vb = -1, pw = -1, pb = -1;
+  Packed w1, w2;           // res: conv1, conv2 (+ nin_shortcut slab); down: conv; attn: qkv, proj_out
+  long long bias_off = -1; // fp32 arena: res with shortcut: conv2.bias + nin.bias; attn: q|k|v biases
+};
+
 struct Layer {
   int kind;   // 0 stem conv, 1 res, 2 st
   int idx;    // index into res / st vectors
@@ -156,6 +166,12 @@ struct UNet {
   static constexpr int kWgCap = 640;   // problems per backward (the Shapes3D plan records 273)
   size_t scratch_total = 0;
   bool force_old_gemm = false;   // parity A/B switch: route every GEMM through the one-tile-per-CTA kernel
+  // first-stage VQ encoder (model_kind 1): config, layer list, stem / head operands live in stemf / headf
+  int model_kind = 0;
+  encdiff_vqenc_config vqcfg;
+  std::vector<VqLayer> vq;
+  int vq_in_w = -1, vq_in_b = -1, vq_no_w = -1, vq_no_b = -1, vq_co_w = -1, vq_co_b = -1, vq_qc_w = -1, vq_qc_b = -1;
+  int vq_out_res = 0, vq_out_ch = 0;
 
   h16* pbf() const { return reinterpret_cast<h16*>(packed + table_bytes); }
   float* pf32() const { return reinterpret_cast<float*>(packed + table_bytes + h16_bytes); }
@@ -168,6 +184,9 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
                  const float* ctx, float* out, float* xt, cudaStream_t s);
 int unet_backward(UNet* u, int B, const float* dout, const float* ctx, float* dx, float* dctx, cudaStream_t s);
 // fp32 validation forward (fp32_ref.cu): fp32 tensors, CUDA-core FMA contractions, reference-layout master parameters
+int vqenc_build(UNet* u, const encdiff_vqenc_config* cfg);
+size_t vqenc_workspace_bytes(UNet* u, int B);
+int vqenc_forward(UNet* u, int B, const float* x, float* z, char* ws, cudaStream_t s);
 size_t unet_fp32_workspace_floats(UNet* u, int B);
 int unet_forward_fp32(UNet* u, int B, const float* x, const float* t, const float* ctx, float* out, float* ws,
                       size_t ws_floats, cudaStream_t s);

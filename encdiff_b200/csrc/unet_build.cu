@@ -317,4 +317,118 @@ int unet_build(UNet* u, const encdiff_unet_config* c) {
   return EDB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// First-stage VQ-f4 encoder (ldm/modules/diffusionmodules/model.py:368-459 + quant_conv, autoencoder.py:49,313-316):
+// parameter inventory in the reference's registration order and forward-layout operands only (frozen, inference).
+// ---------------------------------------------------------------------------------------------------------------
+int vqenc_build(UNet* u, const encdiff_vqenc_config* c) {
+  u->model_kind = 1;
+  u->vqcfg = *c;
+  memset(&u->cfg, 0, sizeof(u->cfg));
+  EDB_REQUIRE(c->ch >= 32 && c->ch % 32 == 0, "vqenc: ch must be a multiple of 32 (GroupNorm 32)");
+  EDB_REQUIRE(c->n_ch_mult >= 1 && c->n_ch_mult <= 4 && c->num_res_blocks >= 1, "vqenc: bad ch_mult / num_res_blocks");
+  EDB_REQUIRE(c->in_channels * 9 <= 64, "vqenc: in_channels*9 must fit one 64-wide K chunk");
+  EDB_REQUIRE(c->z_channels >= 1 && c->z_channels <= 8 && c->embed_dim >= 1 && c->embed_dim <= 8, "vqenc: z_channels / embed_dim <= 8");
+  int R = c->resolution;
+  EDB_REQUIRE(R >= 8 && R <= 128 && (R & (R - 1)) == 0, "vqenc: resolution must be a power of two in 8..128");
+  Builder b;
+  b.u = u;
+  auto conv_params = [&](const std::string& n, int co, int ci, int k, int& w, int& bi) {
+    w = b.add_param(n + ".weight", {co, ci, k, k});
+    bi = b.add_param(n + ".bias", {co});
+  };
+  auto norm_params = [&](const std::string& n, int ch, int& w, int& bi) {
+    w = b.add_param(n + ".weight", {ch});
+    bi = b.add_param(n + ".bias", {ch});
+  };
+  auto add_res = [&](const std::string& n, int ci, int co, int H) {
+    VqLayer l;
+    l.kind = 1;
+    l.cin = ci;
+    l.cout = co;
+    l.H = H;
+    norm_params(n + ".norm1", ci, l.n1w, l.n1b);
+    conv_params(n + ".conv1", co, ci, 3, l.c1w, l.c1b);
+    norm_params(n + ".norm2", co, l.n2w, l.n2b);
+    conv_params(n + ".conv2", co, co, 3, l.c2w, l.c2b);
+    if (ci != co) conv_params(n + ".nin_shortcut", co, ci, 1, l.sw, l.sb);
+    const long long ci64 = ceil_to(ci, 64), co64 = ceil_to(co, 64);
+    l.w1 = b.alloc(co, 9 * ci64);
+    b.pack_fwd(l.w1, l.c1w, co, ci, 9, 0, 0);
+    l.w2 = b.alloc(co, 9 * co64 + (l.sw >= 0 ? ci64 : 0));
+    b.pack_fwd(l.w2, l.c2w, co, co, 9, 0, 0);
+    if (l.sw >= 0) {
+      b.pack_fwd(l.w2, l.sw, co, ci, 1, 0, static_cast<int>(9 * co64));
+      l.bias_off = b.f32_off;
+      b.f32_off += ceil_to(co, 64);
+      b.entry(3, l.c2b, l.sb, l.bias_off, co, 1, 1, 0, 0, 0, 0, 0);
+    }
+    u->vq.push_back(l);
+  };
+  conv_params("encoder.conv_in", c->ch, c->in_channels, 3, u->vq_in_w, u->vq_in_b);
+  int block_in = c->ch;
+  for (int lvl = 0; lvl < c->n_ch_mult; ++lvl) {
+    block_in = c->ch * (lvl == 0 ? 1 : c->ch_mult[lvl - 1]);
+    const int block_out = c->ch * c->ch_mult[lvl];
+    EDB_REQUIRE(block_out % 32 == 0, "vqenc: channel counts must be multiples of 32");
+    for (int i = 0; i < c->num_res_blocks; ++i) {
+      add_res("encoder.down." + std::to_string(lvl) + ".block." + std::to_string(i), block_in, block_out, R);
+      block_in = block_out;
+    }
+    if (lvl != c->n_ch_mult - 1) {
+      VqLayer l;
+      l.kind = 2;
+      l.cin = l.cout = block_in;
+      l.H = R;
+      conv_params("encoder.down." + std::to_string(lvl) + ".downsample.conv", block_in, block_in, 3, l.c1w, l.c1b);
+      l.w1 = b.alloc(block_in, 9 * ceil_to(block_in, 64));
+      b.pack_fwd(l.w1, l.c1w, block_in, block_in, 9, 0, 0);
+      u->vq.push_back(l);
+      R /= 2;
+    }
+  }
+  EDB_REQUIRE(R >= 4 && R * R <= 256 && block_in <= 128 && block_in % 64 == 0,
+              "vqenc: the mid attention kernel handles <= 256 tokens of 64 or 128 channels");
+  add_res("encoder.mid.block_1", block_in, block_in, R);
+  {
+    VqLayer l;
+    l.kind = 3;
+    l.cin = l.cout = block_in;
+    l.H = R;
+    const std::string n = "encoder.mid.attn_1";
+    norm_params(n + ".norm", block_in, l.n1w, l.n1b);
+    conv_params(n + ".q", block_in, block_in, 1, l.qw, l.qb);
+    conv_params(n + ".k", block_in, block_in, 1, l.kw, l.kb);
+    conv_params(n + ".v", block_in, block_in, 1, l.vw, l.vb);
+    conv_params(n + ".proj_out", block_in, block_in, 1, l.pw, l.pb);
+    const int C = block_in;
+    l.w1 = b.alloc(3 * C, ceil_to(C, 64));
+    const int src[3] = {l.qw, l.kw, l.vw}, bsrc[3] = {l.qb, l.kb, l.vb};
+    l.bias_off = b.f32_off;
+    b.f32_off += ceil_to(3 * C, 64);
+    for (int i = 0; i < 3; ++i) {
+      b.pack_fwd(l.w1, src[i], C, C, 1, i * C, 0);
+      b.entry(2, bsrc[i], -1, l.bias_off, C, 1, 1, 0, 0, 0, 0, i * C);
+    }
+    l.w2 = b.alloc(C, ceil_to(C, 64));
+    b.pack_fwd(l.w2, l.pw, C, C, 1, 0, 0);
+    u->vq.push_back(l);
+  }
+  add_res("encoder.mid.block_2", block_in, block_in, R);
+  norm_params("encoder.norm_out", block_in, u->vq_no_w, u->vq_no_b);
+  conv_params("encoder.conv_out", c->z_channels, block_in, 3, u->vq_co_w, u->vq_co_b);
+  conv_params("quant_conv", c->embed_dim, c->z_channels, 1, u->vq_qc_w, u->vq_qc_b);
+  u->vq_out_res = R;
+  u->vq_out_ch = block_in;
+  // conv_in: reference-order flat K (ci*9 + tap) in one 64-wide chunk, like the UNet stem
+  u->stemf = b.alloc(c->ch, 64);
+  b.entry(4, u->vq_in_w, -1, u->stemf.off, c->ch, c->in_channels, 9, 0, 0, 64, 0, 0);
+  u->headf = b.alloc(c->z_channels, 9 * ceil_to(block_in, 64));
+  b.pack_fwd(u->headf, u->vq_co_w, c->z_channels, block_in, 9, 0, 0);
+  u->table_bytes = static_cast<size_t>(ceil_to(static_cast<long long>(u->table.size() * sizeof(PackEntry)), 1024));
+  u->h16_bytes = static_cast<size_t>(ceil_to(b.bf_off * 2, 1024));
+  u->f32_bytes = static_cast<size_t>(ceil_to(b.f32_off * 4, 1024));
+  return EDB_OK;
+}
+
 }  // namespace edb

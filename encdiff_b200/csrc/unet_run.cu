@@ -696,3 +696,4 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
 }  // namespace edb
 
 #include "unet_bwd.inc"
+#include "vq_enc.inc"

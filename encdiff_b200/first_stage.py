@@ -1,0 +1,175 @@
+"""Host side of the first-stage VQ-f4 ENCODE path: ``z = quant_conv(encoder(x))`` as sm_100a kernels behind the C ABI
+(``encdiff_vqenc_*``, include/encdiff_b200.h).  Mirrors, for the encode direction, the reference's
+``VQModelInterface`` (ldm/models/autoencoder.py:308-316) built from ``Encoder`` (ldm/modules/diffusionmodules/model.py:
+368-459): same ``ddconfig`` keywords, same parameter names (``encoder.*``, ``quant_conv.*``) in the same registration
+order, so ``load_state_dict`` takes the first-stage entries of a reference checkpoint as they are.  The first stage is
+frozen in EncDiff (ddpm_enc.py instantiate_first_stage: eval, requires_grad False), hence inference only; the decoder and
+the quantiser stay the reference's PyTorch modules.  No CPU fallback."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+def _norm(c):
+    return nn.GroupNorm(num_groups=32, num_channels=c, eps=1e-6, affine=True)      # Normalize(), model.py:37-38
+
+
+class _ResnetBlock(nn.Module):          # parameter holder; registration order of model.py:82-119 (temb_channels = 0)
+    def __init__(self, cin, cout):
+        super().__init__()
+        self.norm1 = _norm(cin)
+        self.conv1 = nn.Conv2d(cin, cout, 3, 1, 1)
+        self.norm2 = _norm(cout)
+        self.conv2 = nn.Conv2d(cout, cout, 3, 1, 1)
+        if cin != cout:
+            self.nin_shortcut = nn.Conv2d(cin, cout, 1, 1, 0)
+
+
+class _AttnBlock(nn.Module):            # model.py:153-176
+    def __init__(self, c):
+        super().__init__()
+        self.norm = _norm(c)
+        self.q = nn.Conv2d(c, c, 1)
+        self.k = nn.Conv2d(c, c, 1)
+        self.v = nn.Conv2d(c, c, 1)
+        self.proj_out = nn.Conv2d(c, c, 1)
+
+
+class _Downsample(nn.Module):           # model.py:63-71 (with_conv)
+    def __init__(self, c):
+        super().__init__()
+        self.conv = nn.Conv2d(c, c, 3, 2, 0)
+
+
+class _Encoder(nn.Module):              # model.py:368-435
+    def __init__(self, ch, ch_mult, num_res_blocks, in_channels, z_channels, double_z):
+        super().__init__()
+        self.conv_in = nn.Conv2d(in_channels, ch, 3, 1, 1)
+        in_mult = (1,) + tuple(ch_mult)
+        self.down = nn.ModuleList()
+        block_in = ch
+        for lvl in range(len(ch_mult)):
+            block_in, block_out = ch * in_mult[lvl], ch * ch_mult[lvl]
+            down = nn.Module()
+            down.block = nn.ModuleList()
+            down.attn = nn.ModuleList()
+            for _ in range(num_res_blocks):
+                down.block.append(_ResnetBlock(block_in, block_out))
+                block_in = block_out
+            if lvl != len(ch_mult) - 1:
+                down.downsample = _Downsample(block_in)
+            self.down.append(down)
+        self.mid = nn.Module()
+        self.mid.block_1 = _ResnetBlock(block_in, block_in)
+        self.mid.attn_1 = _AttnBlock(block_in)
+        self.mid.block_2 = _ResnetBlock(block_in, block_in)
+        self.norm_out = _norm(block_in)
+        self.conv_out = nn.Conv2d(block_in, 2 * z_channels if double_z else z_channels, 3, 1, 1)
+
+
+class VQEncoder(nn.Module):
+    """``VQEncoder(embed_dim=3, ddconfig={...})`` — the encode half of the reference's ``VQModelInterface``; ``encode(x)`` /
+    ``forward(x)``: images [B, 3, R, R] in [-1, 1] -> latents [B, embed_dim, R/4, R/4] (f4)."""
+
+    def __init__(self, embed_dim, ddconfig=None, **ddkw):
+        super().__init__()
+        dd = dict(ddconfig or {})
+        dd.update(ddkw)
+        ch, ch_mult = int(dd["ch"]), tuple(int(v) for v in dd.get("ch_mult", (1, 2, 4, 8)))
+        nrb, in_ch = int(dd["num_res_blocks"]), int(dd.get("in_channels", 3))
+        res, zc = int(dd["resolution"]), int(dd["z_channels"])
+        if list(dd.get("attn_resolutions", [])):
+            raise NotImplementedError("encdiff_b200.VQEncoder: attn_resolutions must be empty (the shipped first stages)")
+        if dd.get("double_z", True):
+            raise NotImplementedError("encdiff_b200.VQEncoder: double_z=True (KL first stage) is not implemented")
+        if float(dd.get("dropout", 0.0)) != 0.0 or dd.get("use_linear_attn", False) or dd.get("attn_type", "vanilla") != "vanilla":
+            raise NotImplementedError("encdiff_b200.VQEncoder: dropout / linear attention are not implemented")
+        if not dd.get("resamp_with_conv", True):
+            raise NotImplementedError("encdiff_b200.VQEncoder: resamp_with_conv=False is not implemented")
+        self.embed_dim, self.resolution, self.in_channels = int(embed_dim), res, in_ch
+        self.encoder = _Encoder(ch, ch_mult, nrb, in_ch, zc, False)
+        self.quant_conv = nn.Conv2d(zc, int(embed_dim), 1)
+        self.out_res = res // (2 ** (len(ch_mult) - 1))
+        self._lib = _lib.load()
+        cfg = _lib.VQEncConfigStruct()
+        cfg.ch, cfg.n_ch_mult = ch, len(ch_mult)
+        for i, v in enumerate(ch_mult):
+            cfg.ch_mult[i] = v
+        cfg.num_res_blocks, cfg.in_channels, cfg.resolution, cfg.z_channels, cfg.embed_dim = nrb, in_ch, res, zc, int(embed_dim)
+        h = C.c_void_p()
+        _lib.check(self._lib.encdiff_vqenc_create(C.byref(cfg), C.byref(h)), "vqenc_create")
+        self._h = h
+        n = self._lib.encdiff_unet_num_params(self._h)
+        mine = list(self.named_parameters())
+        if n != len(mine):
+            raise RuntimeError(f"encdiff_b200.VQEncoder: library expects {n} parameter tensors, module has {len(mine)}")
+        buf, shape, nd = C.create_string_buffer(256), (C.c_longlong * 4)(), C.c_int()
+        for i, (name, p) in enumerate(mine):
+            _lib.check(self._lib.encdiff_unet_param_info(self._h, i, buf, 256, shape, C.byref(nd)), "param_info")
+            if buf.value.decode() != name or tuple(shape[k] for k in range(nd.value)) != tuple(p.shape):
+                raise RuntimeError(f"encdiff_b200.VQEncoder: parameter {i} mismatch: module {name}{tuple(p.shape)} vs library "
+                                   f"{buf.value.decode()}{tuple(shape[k] for k in range(nd.value))}")
+        self._bound_key = None
+        self._packed = None
+        self._ws = None
+        for p in self.parameters():
+            p.requires_grad_(False)          # frozen first stage (ddpm_enc.py instantiate_first_stage)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.encdiff_unet_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def refresh_weights(self):
+        """(Re-)bind the parameter tensors and pack them into 16-bit GEMM operands; automatic on the first call and
+        whenever a parameter tensor moved (``.to()``, ``load_state_dict`` keeps storage and needs an explicit call)."""
+        params = [p for _, p in self.named_parameters()]
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("encdiff_b200.VQEncoder runs on CUDA only (sm_100a kernels, no CPU fallback)")
+        for p in params:
+            if p.dtype != torch.float32 or not p.is_contiguous():
+                raise RuntimeError("encdiff_b200.VQEncoder keeps fp32 contiguous parameters")
+        if self._packed is None or self._packed.device != dev:
+            self._packed = torch.empty(self._lib.encdiff_unet_packed_bytes(self._h) + 1024, dtype=torch.uint8, device=dev)
+        ptr = (self._packed.data_ptr() + 1023) // 1024 * 1024
+        pp = (C.c_void_p * len(params))(*[p.data_ptr() for p in params])
+        _lib.check(self._lib.encdiff_unet_bind(self._h, pp, None, ptr, _lib.current_stream()), "vqenc bind")
+        _lib.check(self._lib.encdiff_unet_pack_weights(self._h, _lib.current_stream()), "vqenc pack")
+        self._bound_key = tuple(p.data_ptr() for p in params)
+
+    def load_state_dict(self, *a, **k):
+        out = super().load_state_dict(*a, **k)
+        self._bound_key = None
+        return out
+
+    @torch.no_grad()
+    def encode(self, x):
+        """VQModelInterface.encode (autoencoder.py:313-316)."""
+        if not x.is_cuda:
+            raise RuntimeError("encdiff_b200.VQEncoder.encode needs CUDA tensors (no CPU fallback)")
+        B = x.shape[0]
+        if tuple(x.shape[1:]) != (self.in_channels, self.resolution, self.resolution):
+            raise RuntimeError(f"encdiff_b200.VQEncoder: expected (B,{self.in_channels},{self.resolution},{self.resolution}), "
+                               f"got {tuple(x.shape)}")
+        if self._bound_key is None or self._bound_key[0] != next(self.parameters()).data_ptr():
+            self.refresh_weights()
+        xf = x.contiguous().float()
+        nbytes = self._lib.encdiff_vqenc_workspace_bytes(self._h, B)
+        if self._ws is None or self._ws.numel() < nbytes + 1024 or self._ws.device != x.device:
+            self._ws = torch.empty(nbytes + 1024, dtype=torch.uint8, device=x.device)
+        ws_ptr = (self._ws.data_ptr() + 1023) // 1024 * 1024
+        z = torch.empty(B, self.embed_dim, self.out_res, self.out_res, dtype=torch.float32, device=x.device)
+        _lib.check(self._lib.encdiff_vqenc_forward(self._h, B, xf.data_ptr(), z.data_ptr(), ws_ptr, _lib.current_stream()),
+                   "vqenc_forward")
+        return z.type(x.dtype)
+
+    forward = encode

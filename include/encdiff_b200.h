@@ -224,6 +224,26 @@ int encdiff_adamw_step_dev(float* p, const float* g, float* m, float* v, float* 
 int encdiff_adamw_hyper_advance(int* step, const float* lr, float* hyper, float beta1, float beta2, float ema_decay_max,
                                 void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * First-stage VQ-f4 ENCODE path: z = quant_conv(Encoder(x)), the frozen front end of every
+ * training step.  Replaces VQModelInterface.encode (ldm/models/autoencoder.py:313-316) = Encoder.forward
+ * (ldm/modules/diffusionmodules/model.py:437-459: conv_in, ResnetBlock :121-143, Downsample :72-79, mid AttnBlock
+ * :178-204, norm_out / swish / conv_out) followed by the 1x1 quant_conv.  Inference only (the first stage is frozen,
+ * ddpm_enc.py instantiate_first_stage).  The handle is an encdiff_unet: num_params / param_info (names = state_dict keys
+ * `encoder.*`, `quant_conv.*`, reference registration order) / packed_bytes / bind (grads NULL) / pack_weights / destroy
+ * are the calls above.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct encdiff_vqenc_config {   /* first_stage_config.params of shapes3d-vq-4-16-encdiff.yaml:52-75 */
+  int ch, n_ch_mult;
+  int ch_mult[4];
+  int num_res_blocks, in_channels, resolution, z_channels, embed_dim;
+} encdiff_vqenc_config;
+int encdiff_vqenc_create(const encdiff_vqenc_config* cfg /*host*/, encdiff_unet** out /*host*/);
+long long encdiff_vqenc_workspace_bytes(encdiff_unet* h, int batch);
+/* x [B, in_channels, R, R] fp32 NCHW in [-1, 1] -> z [B, embed_dim, R/2^(levels-1), R/2^(levels-1)] fp32 NCHW.
+ * workspace: 1 KB aligned, >= encdiff_vqenc_workspace_bytes(h, batch).  Enqueue-only. */
+int encdiff_vqenc_forward(encdiff_unet* h, int batch, const float* x, float* z, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
