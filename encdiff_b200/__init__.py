@@ -2,7 +2,7 @@
 
 Drop-in classes (select with ``target: encdiff_b200.UNetModel`` in the reference's unet_config):
 ``UNetModel``, ``SpatialTransformer``, ``CrossAttention``, ``DDIMSampler``; ``ConceptMLP`` replaces the per-unit MLP loop
-of the reference's ``Encoder4`` (``net`` / ``warp``); ``VQEncoder`` is the encode half of the frozen VQ-f4 first stage.
+of the reference's ``Encoder4`` (``net`` / ``warp``); ``VQEncoder`` / ``VQDecoder`` are the encode / decode halves of the frozen VQ-f4 first stage.
 """
 __version__ = "0.1.0"
 
@@ -10,4 +10,4 @@ from .modules import CrossAttention, SpatialTransformer  # noqa: F401
 from .unet import UNetModel  # noqa: F401
 from .sampler import DDIMSampler  # noqa: F401
 from .concept import ConceptMLP  # noqa: F401
-from .first_stage import VQEncoder  # noqa: F401
+from .first_stage import VQDecoder, VQEncoder  # noqa: F401

@@ -60,6 +60,9 @@ PROTOTYPES = {
     "encdiff_vqenc_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
     "encdiff_vqenc_workspace_bytes": (c_ll, [c_void_p, c_int]),
     "encdiff_vqenc_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "encdiff_vqdec_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
+    "encdiff_vqdec_workspace_bytes": (c_ll, [c_void_p, c_int]),
+    "encdiff_vqdec_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "encdiff_unet_fp32_workspace_bytes": (c_ll, [c_void_p, c_int]),
     "encdiff_unet_forward_fp32": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "encdiff_unet_profile": (c_int, [c_void_p, c_int]),
@@ -94,6 +97,11 @@ class VQEncConfigStruct(C.Structure):
     """Mirror of ``encdiff_vqenc_config`` (include/encdiff_b200.h)."""
     _fields_ = [("ch", c_int), ("n_ch_mult", c_int), ("ch_mult", c_int * 4), ("num_res_blocks", c_int),
                 ("in_channels", c_int), ("resolution", c_int), ("z_channels", c_int), ("embed_dim", c_int)]
+
+
+class VQDecConfigStruct(C.Structure):
+    """Mirror of ``encdiff_vqdec_config`` (include/encdiff_b200.h)."""
+    _fields_ = [("dd", VQEncConfigStruct), ("out_ch", c_int), ("n_embed", c_int), ("disentangled_dim", c_int)]
 
 
 def lib_path() -> Path:

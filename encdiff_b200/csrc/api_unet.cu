@@ -135,6 +135,32 @@ extern "C" int encdiff_vqenc_forward(encdiff_unet* h, int batch, const float* x,
   return vqenc_forward(&h->u, batch, x, z, static_cast<char*>(workspace), static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int encdiff_vqdec_create(const encdiff_vqdec_config* cfg, encdiff_unet** out) {
+  EDB_REQUIRE(cfg && out, "vqdec_create: null argument");
+  encdiff_unet* h = new (std::nothrow) encdiff_unet();
+  EDB_REQUIRE(h, "vqdec_create: out of host memory");
+  int rc = vqdec_build(&h->u, cfg);
+  if (rc) {
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return EDB_OK;
+}
+
+extern "C" long long encdiff_vqdec_workspace_bytes(encdiff_unet* h, int batch) {
+  if (!h || batch <= 0 || h->u.model_kind != 2) return -1;
+  return static_cast<long long>(vqdec_workspace_bytes(&h->u, batch));
+}
+
+extern "C" int encdiff_vqdec_forward(encdiff_unet* h, int batch, const float* latent, const float* s, int quantize,
+                                     float* img, void* workspace, void* stream) {
+  EDB_REQUIRE(h && latent && img && workspace && batch > 0, "vqdec_forward: bad argument");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, "vqdec_forward: workspace must be 1 KB aligned");
+  return vqdec_forward(&h->u, batch, latent, s, quantize, img, static_cast<char*>(workspace),
+                       static_cast<cudaStream_t>(stream));
+}
+
 extern "C" long long encdiff_unet_fp32_workspace_bytes(encdiff_unet* h, int batch) {
   if (!h || batch <= 0) return -1;
   return static_cast<long long>(unet_fp32_workspace_floats(&h->u, batch) * sizeof(float));

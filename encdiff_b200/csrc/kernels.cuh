@@ -192,6 +192,10 @@ int launch_adamw_hyper_advance(int* step, const float* lr, float* hyper, float b
 int launch_vq_down_im2col(const h16* x, h16* cols, int B, int H, int C, cudaStream_t s);
 // single-head attention of AttnBlock: qkv [B*N, 3D] -> out [B*N, D], D in {64, 128}, N <= 256 multiple of 16
 int launch_vq_attn(const h16* qkv, h16* out, int B, int N, int D, cudaStream_t s);
+// decoder: nearest x2 upsample (NHWC h16), and the front of VQModelInterface.decode (quantise / concat / post_quant_conv)
+int launch_vq_upsample2x(const h16* x, h16* y, int B, int H, int C, cudaStream_t s);
+int launch_vq_post_quant(const float* h, const float* sdis, const float* codebook, int n_embed, const float* w,
+                         const float* bias, float* out, int B, int HW, int ed, int dd, int zc, cudaStream_t s);
 // quant_conv (1x1, zc -> ed) + NHWC fp32 -> NCHW fp32
 int launch_vq_tail(const float* h, const float* wq, const float* bq, float* z, int B, int HW, int zc, int ed, cudaStream_t s);
 

@@ -69,7 +69,7 @@ struct StLayer {
 
 // first-stage VQ encoder layers (vq_enc.inc): the same UNet object carries their parameters / packed operands
 struct VqLayer {
-  int kind = 0;            // 1 ResnetBlock, 2 Downsample (3x3 stride 2, pad right/bottom), 3 AttnBlock
+  int kind = 0;            // 1 ResnetBlock, 2 Downsample (3x3 stride 2, pad right/bottom), 3 AttnBlock, 4 Upsample (nearest x2 + 3x3)
   int cin = 0, cout = 0, H = 0;     // H = input spatial size (square)
   int n1w = -1, n1b = -1, c1w = -1, c1b = -1, n2w = -1, n2b = -1, c2w = -1, c2b = -1, sw = -1, sb = -1;   // res / down (c1*) / attn
   int qw = -1, qb = -1, kw = -1, kb = -1, vw = -1, vb = -1, pw = -1, pb = -1;
@@ -169,7 +169,9 @@ struct UNet {
   // first-stage VQ encoder (model_kind 1): config, layer list, stem / head operands live in stemf / headf
   int model_kind = 0;
   encdiff_vqenc_config vqcfg;
-  std::vector<VqLayer> vq;
+  std::vector<VqLayer> vq;          // registration order (= parameter order)
+  std::vector<int> vq_order;        // execution order (the decoder registers its levels in reverse)
+  int vq_n_embed = 0, vq_dd = 0, vq_emb_w = -1, vq_pq_w = -1, vq_pq_b = -1, vq_img_ch = 0;
   int vq_in_w = -1, vq_in_b = -1, vq_no_w = -1, vq_no_b = -1, vq_co_w = -1, vq_co_b = -1, vq_qc_w = -1, vq_qc_b = -1;
   int vq_out_res = 0, vq_out_ch = 0;
 
@@ -185,6 +187,9 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
 int unet_backward(UNet* u, int B, const float* dout, const float* ctx, float* dx, float* dctx, cudaStream_t s);
 // fp32 validation forward (fp32_ref.cu): fp32 tensors, CUDA-core FMA contractions, reference-layout master parameters
 int vqenc_build(UNet* u, const encdiff_vqenc_config* cfg);
+int vqdec_build(UNet* u, const encdiff_vqdec_config* cfg);
+size_t vqdec_workspace_bytes(UNet* u, int B);
+int vqdec_forward(UNet* u, int B, const float* latent, const float* sdis, int quantize, float* img, char* ws, cudaStream_t s);
 size_t vqenc_workspace_bytes(UNet* u, int B);
 int vqenc_forward(UNet* u, int B, const float* x, float* z, char* ws, cudaStream_t s);
 size_t unet_fp32_workspace_floats(UNet* u, int B);

@@ -420,11 +420,155 @@ int vqenc_build(UNet* u, const encdiff_vqenc_config* c) {
   conv_params("quant_conv", c->embed_dim, c->z_channels, 1, u->vq_qc_w, u->vq_qc_b);
   u->vq_out_res = R;
   u->vq_out_ch = block_in;
+  u->vq_order.clear();
+  for (size_t i = 0; i < u->vq.size(); ++i) u->vq_order.push_back(static_cast<int>(i));
   // conv_in: reference-order flat K (ci*9 + tap) in one 64-wide chunk, like the UNet stem
   u->stemf = b.alloc(c->ch, 64);
   b.entry(4, u->vq_in_w, -1, u->stemf.off, c->ch, c->in_channels, 9, 0, 0, 64, 0, 0);
   u->headf = b.alloc(c->z_channels, 9 * ceil_to(block_in, 64));
   b.pack_fwd(u->headf, u->vq_co_w, c->z_channels, block_in, 9, 0, 0);
+  u->table_bytes = static_cast<size_t>(ceil_to(static_cast<long long>(u->table.size() * sizeof(PackEntry)), 1024));
+  u->h16_bytes = static_cast<size_t>(ceil_to(b.bf_off * 2, 1024));
+  u->f32_bytes = static_cast<size_t>(ceil_to(b.f32_off * 4, 1024));
+  return EDB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// First-stage decoder (model.py:462-568) + quantize.embedding + post_quant_conv (autoencoder.py:44-53).
+// Parameters in the reference's registration order (conv_in, mid, up.0 .. up.L-1, norm_out, conv_out, then
+// quantize.embedding.weight, post_quant_conv.*); execution order is mid, then the levels from the deepest one.
+// ---------------------------------------------------------------------------------------------------------------
+int vqdec_build(UNet* u, const encdiff_vqdec_config* cd) {
+  const encdiff_vqenc_config* c = &cd->dd;
+  u->model_kind = 2;
+  u->vqcfg = *c;
+  memset(&u->cfg, 0, sizeof(u->cfg));
+  EDB_REQUIRE(c->ch >= 32 && c->ch % 32 == 0, "vqdec: ch must be a multiple of 32 (GroupNorm 32)");
+  EDB_REQUIRE(c->n_ch_mult >= 1 && c->n_ch_mult <= 4 && c->num_res_blocks >= 1, "vqdec: bad ch_mult / num_res_blocks");
+  EDB_REQUIRE(c->z_channels * 9 <= 64, "vqdec: z_channels*9 must fit one 64-wide K chunk");
+  EDB_REQUIRE(cd->out_ch >= 1 && cd->out_ch <= 8 && c->embed_dim >= 1 && c->embed_dim <= 8, "vqdec: out_ch / embed_dim <= 8");
+  EDB_REQUIRE(cd->disentangled_dim >= 0 && cd->disentangled_dim <= 64 && cd->n_embed >= 0, "vqdec: bad n_embed / disentangled_dim");
+  const int L = c->n_ch_mult;
+  const int R = c->resolution;
+  EDB_REQUIRE(R >= 8 && R <= 128 && (R & (R - 1)) == 0, "vqdec: resolution must be a power of two in 8..128");
+  const int r0 = R >> (L - 1);
+  int block_in = c->ch * c->ch_mult[L - 1];
+  EDB_REQUIRE(r0 >= 4 && r0 * r0 <= 256 && block_in <= 128 && block_in % 64 == 0,
+              "vqdec: the mid attention kernel handles <= 256 tokens of 64 or 128 channels");
+  u->vq_n_embed = cd->n_embed;
+  u->vq_dd = cd->disentangled_dim;
+  u->vq_img_ch = cd->out_ch;
+  Builder b;
+  b.u = u;
+  auto conv_params = [&](const std::string& n, int co, int ci, int k, int& w, int& bi) {
+    w = b.add_param(n + ".weight", {co, ci, k, k});
+    bi = b.add_param(n + ".bias", {co});
+  };
+  auto norm_params = [&](const std::string& n, int ch, int& w, int& bi) {
+    w = b.add_param(n + ".weight", {ch});
+    bi = b.add_param(n + ".bias", {ch});
+  };
+  auto add_res = [&](const std::string& n, int ci, int co, int H) {
+    VqLayer l;
+    l.kind = 1;
+    l.cin = ci;
+    l.cout = co;
+    l.H = H;
+    norm_params(n + ".norm1", ci, l.n1w, l.n1b);
+    conv_params(n + ".conv1", co, ci, 3, l.c1w, l.c1b);
+    norm_params(n + ".norm2", co, l.n2w, l.n2b);
+    conv_params(n + ".conv2", co, co, 3, l.c2w, l.c2b);
+    if (ci != co) conv_params(n + ".nin_shortcut", co, ci, 1, l.sw, l.sb);
+    const long long ci64 = ceil_to(ci, 64), co64 = ceil_to(co, 64);
+    l.w1 = b.alloc(co, 9 * ci64);
+    b.pack_fwd(l.w1, l.c1w, co, ci, 9, 0, 0);
+    l.w2 = b.alloc(co, 9 * co64 + (l.sw >= 0 ? ci64 : 0));
+    b.pack_fwd(l.w2, l.c2w, co, co, 9, 0, 0);
+    if (l.sw >= 0) {
+      b.pack_fwd(l.w2, l.sw, co, ci, 1, 0, static_cast<int>(9 * co64));
+      l.bias_off = b.f32_off;
+      b.f32_off += ceil_to(co, 64);
+      b.entry(3, l.c2b, l.sb, l.bias_off, co, 1, 1, 0, 0, 0, 0, 0);
+    }
+    u->vq.push_back(l);
+    return static_cast<int>(u->vq.size()) - 1;
+  };
+  conv_params("decoder.conv_in", block_in, c->z_channels, 3, u->vq_in_w, u->vq_in_b);
+  std::vector<int> order;
+  order.push_back(add_res("decoder.mid.block_1", block_in, block_in, r0));
+  {
+    VqLayer l;
+    l.kind = 3;
+    l.cin = l.cout = block_in;
+    l.H = r0;
+    const std::string n = "decoder.mid.attn_1";
+    norm_params(n + ".norm", block_in, l.n1w, l.n1b);
+    conv_params(n + ".q", block_in, block_in, 1, l.qw, l.qb);
+    conv_params(n + ".k", block_in, block_in, 1, l.kw, l.kb);
+    conv_params(n + ".v", block_in, block_in, 1, l.vw, l.vb);
+    conv_params(n + ".proj_out", block_in, block_in, 1, l.pw, l.pb);
+    const int C = block_in;
+    l.w1 = b.alloc(3 * C, ceil_to(C, 64));
+    const int src[3] = {l.qw, l.kw, l.vw}, bsrc[3] = {l.qb, l.kb, l.vb};
+    l.bias_off = b.f32_off;
+    b.f32_off += ceil_to(3 * C, 64);
+    for (int i = 0; i < 3; ++i) {
+      b.pack_fwd(l.w1, src[i], C, C, 1, i * C, 0);
+      b.entry(2, bsrc[i], -1, l.bias_off, C, 1, 1, 0, 0, 0, 0, i * C);
+    }
+    l.w2 = b.alloc(C, ceil_to(C, 64));
+    b.pack_fwd(l.w2, l.pw, C, C, 1, 0, 0);
+    u->vq.push_back(l);
+    order.push_back(static_cast<int>(u->vq.size()) - 1);
+  }
+  order.push_back(add_res("decoder.mid.block_2", block_in, block_in, r0));
+  // channel / resolution of every level at the time it EXECUTES (deepest first)
+  int lvl_in[4], lvl_res[4];
+  {
+    int bi = block_in, rr = r0;
+    for (int lvl = L - 1; lvl >= 0; --lvl) {
+      lvl_in[lvl] = bi;
+      lvl_res[lvl] = rr;
+      bi = c->ch * c->ch_mult[lvl];
+      EDB_REQUIRE(bi % 32 == 0, "vqdec: channel counts must be multiples of 32");
+      if (lvl != 0) rr *= 2;
+    }
+  }
+  std::vector<std::vector<int>> lvl_layers(L);
+  for (int lvl = 0; lvl < L; ++lvl) {          // registration order: up.0 first
+    int bi = lvl_in[lvl];
+    const int bo = c->ch * c->ch_mult[lvl];
+    for (int i = 0; i <= c->num_res_blocks; ++i) {
+      lvl_layers[lvl].push_back(add_res("decoder.up." + std::to_string(lvl) + ".block." + std::to_string(i), bi, bo, lvl_res[lvl]));
+      bi = bo;
+    }
+    if (lvl != 0) {
+      VqLayer l;
+      l.kind = 4;
+      l.cin = l.cout = bo;
+      l.H = lvl_res[lvl];
+      conv_params("decoder.up." + std::to_string(lvl) + ".upsample.conv", bo, bo, 3, l.c1w, l.c1b);
+      l.w1 = b.alloc(bo, 9 * ceil_to(bo, 64));
+      b.pack_fwd(l.w1, l.c1w, bo, bo, 9, 0, 0);
+      u->vq.push_back(l);
+      lvl_layers[lvl].push_back(static_cast<int>(u->vq.size()) - 1);
+    }
+  }
+  for (int lvl = L - 1; lvl >= 0; --lvl)
+    for (int i : lvl_layers[lvl]) order.push_back(i);
+  u->vq_order = order;
+  const int c_last = c->ch * c->ch_mult[0];
+  norm_params("decoder.norm_out", c_last, u->vq_no_w, u->vq_no_b);
+  conv_params("decoder.conv_out", cd->out_ch, c_last, 3, u->vq_co_w, u->vq_co_b);
+  if (cd->n_embed > 0) u->vq_emb_w = b.add_param("quantize.embedding.weight", {cd->n_embed, c->embed_dim});
+  u->vq_pq_w = b.add_param("post_quant_conv.weight", {c->z_channels, c->embed_dim + cd->disentangled_dim, 1, 1});
+  u->vq_pq_b = b.add_param("post_quant_conv.bias", {c->z_channels});
+  u->vq_out_res = R;
+  u->vq_out_ch = c_last;
+  u->stemf = b.alloc(block_in, 64);
+  b.entry(4, u->vq_in_w, -1, u->stemf.off, block_in, c->z_channels, 9, 0, 0, 64, 0, 0);
+  u->headf = b.alloc(cd->out_ch, 9 * ceil_to(c_last, 64));
+  b.pack_fwd(u->headf, u->vq_co_w, cd->out_ch, c_last, 9, 0, 0);
   u->table_bytes = static_cast<size_t>(ceil_to(static_cast<long long>(u->table.size() * sizeof(PackEntry)), 1024));
   u->h16_bytes = static_cast<size_t>(ceil_to(b.bf_off * 2, 1024));
   u->f32_bytes = static_cast<size_t>(ceil_to(b.f32_off * 4, 1024));

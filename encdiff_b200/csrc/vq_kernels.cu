@@ -161,6 +161,72 @@ __global__ void vq_tail_kernel(const float* __restrict__ h, const float* __restr
   }
 }
 
+// nearest-neighbour x2 (Upsample.forward, model.py:53-54): y[b][2y+i][2x+j][c] = x[b][y][x][c]
+__global__ void vq_upsample2x_kernel(const h16* __restrict__ x, h16* __restrict__ y, int B, int H, int C) {
+  pdl_enter();
+  const int cv = C / 8, Ho = 2 * H;
+  const long long total = static_cast<long long>(B) * Ho * Ho * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % cv);
+    long long r = i / cv;
+    const int ox = static_cast<int>(r % Ho);
+    r /= Ho;
+    const int oy = static_cast<int>(r % Ho), b = static_cast<int>(r / Ho);
+    *reinterpret_cast<uint4*>(y + i * 8) =
+        *reinterpret_cast<const uint4*>(x + ((static_cast<long long>(b) * H + (oy >> 1)) * H + (ox >> 1)) * C + c8 * 8);
+  }
+}
+
+// Front of VQModelInterface.decode (autoencoder.py:340-366), one thread per latent pixel, NCHW fp32 in and out:
+//   q = quantize ? nearest code of h (taming VectorQuantizer2 forward value: argmin_k |h|^2 + |e_k|^2 - 2 h.e_k, first
+//       minimum wins like torch.argmin) : h
+//   out[c] = b[c] + sum_e W[c][e] q[e] + sum_n W[c][ed + n] s[b][n]      (the concatenated disentangled channels are constant
+//       over the grid; s == NULL is the reference's zeros branch)
+__global__ void vq_post_quant_kernel(const float* __restrict__ h, const float* __restrict__ sdis,
+                                     const float* __restrict__ codebook, int n_embed, const float* __restrict__ w,
+                                     const float* __restrict__ bias, float* __restrict__ out, int B, int HW, int ed, int dd,
+                                     int zc) {
+  pdl_enter();
+  const long long total = static_cast<long long>(B) * HW;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int pix = static_cast<int>(i % HW), b = static_cast<int>(i / HW);
+    float q[8];
+    float zz = 0.f;
+    for (int e = 0; e < ed; ++e) {
+      q[e] = h[(static_cast<long long>(b) * ed + e) * HW + pix];
+      zz += q[e] * q[e];
+    }
+    if (codebook) {
+      float best = INFINITY;
+      int bi = 0;
+      for (int k = 0; k < n_embed; ++k) {
+        float ee = 0.f, ze = 0.f;
+        for (int e = 0; e < ed; ++e) {
+          const float c = codebook[k * ed + e];
+          ee += c * c;
+          ze += q[e] * c;
+        }
+        const float d = zz + ee - 2.f * ze;
+        if (d < best) {
+          best = d;
+          bi = k;
+        }
+      }
+      for (int e = 0; e < ed; ++e) q[e] = codebook[bi * ed + e];
+    }
+    for (int c = 0; c < zc; ++c) {
+      float a = bias[c];
+      const float* wr = w + c * (ed + dd);
+      for (int e = 0; e < ed; ++e) a = fmaf(wr[e], q[e], a);
+      if (sdis)
+        for (int n = 0; n < dd; ++n) a = fmaf(wr[ed + n], sdis[static_cast<long long>(b) * dd + n], a);
+      out[(static_cast<long long>(b) * zc + c) * HW + pix] = a;
+    }
+  }
+}
+
 inline int vq_grid(long long n, int threads) {
   const long long b = (n + threads - 1) / threads;
   return static_cast<int>(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
@@ -201,6 +267,20 @@ int launch_vq_attn(const h16* qkv, h16* out, int B, int N, int D, cudaStream_t s
 
 int launch_vq_tail(const float* h, const float* wq, const float* bq, float* z, int B, int HW, int zc, int ed, cudaStream_t s) {
   launch_k(vq_tail_kernel, vq_grid(static_cast<long long>(B) * ed * HW, 256), 256, 0, s, h, wq, bq, z, B, HW, zc, ed);
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_vq_upsample2x(const h16* x, h16* y, int B, int H, int C, cudaStream_t s) {
+  if (C & 7) return static_cast<int>(cudaErrorInvalidValue);
+  launch_k(vq_upsample2x_kernel, vq_grid(static_cast<long long>(B) * 4 * H * H * (C / 8), 256), 256, 0, s, x, y, B, H, C);
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_vq_post_quant(const float* h, const float* sdis, const float* codebook, int n_embed, const float* w,
+                         const float* bias, float* out, int B, int HW, int ed, int dd, int zc, cudaStream_t s) {
+  if (ed > 8) return static_cast<int>(cudaErrorInvalidValue);
+  launch_k(vq_post_quant_kernel, vq_grid(static_cast<long long>(B) * HW, 128), 128, 0, s, h, sdis, codebook, n_embed, w, bias,
+           out, B, HW, ed, dd, zc);
   return static_cast<int>(cudaGetLastError());
 }
 

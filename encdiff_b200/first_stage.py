@@ -173,3 +173,133 @@ class VQEncoder(nn.Module):
         return z.type(x.dtype)
 
     forward = encode
+
+
+class _Upsample(nn.Module):             # model.py:41-51 (with_conv)
+    def __init__(self, c):
+        super().__init__()
+        self.conv = nn.Conv2d(c, c, 3, 1, 1)
+
+
+class _Decoder(nn.Module):              # model.py:462-530: levels are created deepest first and PREPENDED to self.up
+    def __init__(self, ch, ch_mult, num_res_blocks, z_channels, out_ch):
+        super().__init__()
+        L = len(ch_mult)
+        block_in = ch * ch_mult[L - 1]
+        self.conv_in = nn.Conv2d(z_channels, block_in, 3, 1, 1)
+        self.mid = nn.Module()
+        self.mid.block_1 = _ResnetBlock(block_in, block_in)
+        self.mid.attn_1 = _AttnBlock(block_in)
+        self.mid.block_2 = _ResnetBlock(block_in, block_in)
+        self.up = nn.ModuleList()
+        for lvl in reversed(range(L)):
+            block_out = ch * ch_mult[lvl]
+            up = nn.Module()
+            up.block = nn.ModuleList()
+            up.attn = nn.ModuleList()
+            for _ in range(num_res_blocks + 1):
+                up.block.append(_ResnetBlock(block_in, block_out))
+                block_in = block_out
+            if lvl != 0:
+                up.upsample = _Upsample(block_in)
+            self.up.insert(0, up)
+        self.norm_out = _norm(block_in)
+        self.conv_out = nn.Conv2d(block_in, out_ch, 3, 1, 1)
+
+
+class _Quantize(nn.Module):             # holder of taming's VectorQuantizer2.embedding (n_e x e_dim)
+    def __init__(self, n_embed, embed_dim):
+        super().__init__()
+        self.embedding = nn.Embedding(n_embed, embed_dim)
+
+
+class VQDecoder(nn.Module):
+    """The decode half of the reference's ``VQModelInterface`` (ldm/models/autoencoder.py:328-369):
+    ``decode(h, force_not_quantize=False, disentangled_repr=None)`` = nearest-code quantisation (unless told not to), concat of
+    the disentangled representation over the latent grid (when built with ``use_disentangled_concat``; zeros if none is
+    given), ``post_quant_conv`` and the ``Decoder``.  Parameter names ``decoder.*``, ``quantize.embedding.weight``,
+    ``post_quant_conv.*`` as in a reference checkpoint.  Inference only, CUDA only."""
+
+    def __init__(self, embed_dim, n_embed=0, ddconfig=None, use_disentangled_concat=False, disentangled_dim=0, **ddkw):
+        super().__init__()
+        dd = dict(ddconfig or {})
+        dd.update(ddkw)
+        ch, ch_mult = int(dd["ch"]), tuple(int(v) for v in dd.get("ch_mult", (1, 2, 4, 8)))
+        nrb, res, zc, out_ch = int(dd["num_res_blocks"]), int(dd["resolution"]), int(dd["z_channels"]), int(dd.get("out_ch", 3))
+        if list(dd.get("attn_resolutions", [])):
+            raise NotImplementedError("encdiff_b200.VQDecoder: attn_resolutions must be empty (the shipped first stages)")
+        if float(dd.get("dropout", 0.0)) != 0.0 or dd.get("use_linear_attn", False) or dd.get("attn_type", "vanilla") != "vanilla":
+            raise NotImplementedError("encdiff_b200.VQDecoder: dropout / linear attention are not implemented")
+        if dd.get("give_pre_end", False) or dd.get("tanh_out", False) or not dd.get("resamp_with_conv", True):
+            raise NotImplementedError("encdiff_b200.VQDecoder: give_pre_end / tanh_out / resamp_with_conv=False are not implemented")
+        self.embed_dim, self.n_embed, self.resolution, self.out_ch = int(embed_dim), int(n_embed), res, out_ch
+        self.use_disentangled_concat = bool(use_disentangled_concat)
+        self.disentangled_dim = int(disentangled_dim) if use_disentangled_concat else 0
+        self.latent_res = res // (2 ** (len(ch_mult) - 1))
+        self.decoder = _Decoder(ch, ch_mult, nrb, zc, out_ch)
+        if self.n_embed > 0:
+            self.quantize = _Quantize(self.n_embed, self.embed_dim)
+        self.post_quant_conv = nn.Conv2d(self.embed_dim + self.disentangled_dim, zc, 1)
+        self._lib = _lib.load()
+        cfg = _lib.VQDecConfigStruct()
+        cfg.dd.ch, cfg.dd.n_ch_mult = ch, len(ch_mult)
+        for i, v in enumerate(ch_mult):
+            cfg.dd.ch_mult[i] = v
+        cfg.dd.num_res_blocks, cfg.dd.in_channels, cfg.dd.resolution = nrb, int(dd.get("in_channels", 3)), res
+        cfg.dd.z_channels, cfg.dd.embed_dim = zc, self.embed_dim
+        cfg.out_ch, cfg.n_embed, cfg.disentangled_dim = out_ch, self.n_embed, self.disentangled_dim
+        h = C.c_void_p()
+        _lib.check(self._lib.encdiff_vqdec_create(C.byref(cfg), C.byref(h)), "vqdec_create")
+        self._h = h
+        n = self._lib.encdiff_unet_num_params(self._h)
+        mine = list(self.named_parameters())
+        if n != len(mine):
+            raise RuntimeError(f"encdiff_b200.VQDecoder: library expects {n} parameter tensors, module has {len(mine)}")
+        buf, shape, nd = C.create_string_buffer(256), (C.c_longlong * 4)(), C.c_int()
+        for i, (name, p) in enumerate(mine):
+            _lib.check(self._lib.encdiff_unet_param_info(self._h, i, buf, 256, shape, C.byref(nd)), "param_info")
+            if buf.value.decode() != name or tuple(shape[k] for k in range(nd.value)) != tuple(p.shape):
+                raise RuntimeError(f"encdiff_b200.VQDecoder: parameter {i} mismatch: module {name}{tuple(p.shape)} vs library "
+                                   f"{buf.value.decode()}{tuple(shape[k] for k in range(nd.value))}")
+        self._bound_key = None
+        self._packed = None
+        self._ws = None
+        for p in self.parameters():
+            p.requires_grad_(False)
+
+    __del__ = VQEncoder.__del__
+    refresh_weights = VQEncoder.refresh_weights
+
+    def load_state_dict(self, *a, **k):
+        out = super().load_state_dict(*a, **k)
+        self._bound_key = None
+        return out
+
+    @torch.no_grad()
+    def decode(self, h, force_not_quantize=False, disentangled_repr=None):
+        if not h.is_cuda:
+            raise RuntimeError("encdiff_b200.VQDecoder.decode needs CUDA tensors (no CPU fallback)")
+        B = h.shape[0]
+        if tuple(h.shape[1:]) != (self.embed_dim, self.latent_res, self.latent_res):
+            raise RuntimeError(f"encdiff_b200.VQDecoder: expected (B,{self.embed_dim},{self.latent_res},{self.latent_res}), "
+                               f"got {tuple(h.shape)}")
+        if not force_not_quantize and self.n_embed <= 0:
+            raise RuntimeError("encdiff_b200.VQDecoder: built without a codebook (n_embed=0): pass force_not_quantize=True")
+        if self._bound_key is None or self._bound_key[0] != next(self.parameters()).data_ptr():
+            self.refresh_weights()
+        hf = h.contiguous().float()
+        s = None
+        if self.disentangled_dim > 0 and disentangled_repr is not None:
+            s = disentangled_repr.reshape(B, -1).contiguous().float()
+            if s.shape[1] != self.disentangled_dim:
+                raise RuntimeError(f"encdiff_b200.VQDecoder: disentangled_repr has {s.shape[1]} dims, model has {self.disentangled_dim}")
+        nbytes = self._lib.encdiff_vqdec_workspace_bytes(self._h, B)
+        if self._ws is None or self._ws.numel() < nbytes + 1024 or self._ws.device != h.device:
+            self._ws = torch.empty(nbytes + 1024, dtype=torch.uint8, device=h.device)
+        ws_ptr = (self._ws.data_ptr() + 1023) // 1024 * 1024
+        img = torch.empty(B, self.out_ch, self.resolution, self.resolution, dtype=torch.float32, device=h.device)
+        _lib.check(self._lib.encdiff_vqdec_forward(self._h, B, hf.data_ptr(), _lib.ptr(s), 0 if force_not_quantize else 1,
+                                                   img.data_ptr(), ws_ptr, _lib.current_stream()), "vqdec_forward")
+        return img.type(h.dtype)
+
+    forward = decode

@@ -244,6 +244,26 @@ long long encdiff_vqenc_workspace_bytes(encdiff_unet* h, int batch);
  * workspace: 1 KB aligned, >= encdiff_vqenc_workspace_bytes(h, batch).  Enqueue-only. */
 int encdiff_vqenc_forward(encdiff_unet* h, int batch, const float* x, float* z, void* workspace, void* stream);
 
+/* First-stage DECODE path: img = Decoder(post_quant_conv([quantize(h) | s])).  Replaces
+ * VQModelInterface.decode (ldm/models/autoencoder.py:328-369): nearest-codebook-entry quantisation (taming's
+ * VectorQuantizer2 forward value; skipped with force_not_quantize), channel concatenation of the disentangled
+ * representation s [B, disentangled_dim] broadcast over the latent grid (zeros when NULL; only when the model is built with
+ * disentangled_dim > 0, i.e. use_disentangled_concat), the 1x1 post_quant_conv, and Decoder.forward
+ * (ldm/modules/diffusionmodules/model.py:532-568: conv_in, mid ResnetBlock / AttnBlock / ResnetBlock, per level
+ * num_res_blocks + 1 ResnetBlocks and Upsample = nearest x2 + conv3x3 :41-57, norm_out / swish / conv_out).  Same handle
+ * type and generic calls as the encoder; parameter names `decoder.*`, `quantize.embedding.weight` (when n_embed > 0),
+ * `post_quant_conv.*` in the reference's registration order (Decoder PREPENDS its levels: up.0 .. up.L-1). */
+typedef struct encdiff_vqdec_config {
+  encdiff_vqenc_config dd;          /* the shared ddconfig (in_channels unused) */
+  int out_ch, n_embed, disentangled_dim;
+} encdiff_vqdec_config;
+int encdiff_vqdec_create(const encdiff_vqdec_config* cfg /*host*/, encdiff_unet** out /*host*/);
+long long encdiff_vqdec_workspace_bytes(encdiff_unet* h, int batch);
+/* h [B, embed_dim, r, r] fp32 NCHW latent; s [B, disentangled_dim] fp32 or NULL; quantize != 0 needs n_embed > 0;
+ * img [B, out_ch, R, R] fp32 NCHW.  Enqueue-only; workspace 1 KB aligned. */
+int encdiff_vqdec_forward(encdiff_unet* h, int batch, const float* latent, const float* s, int quantize, float* img,
+                          void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

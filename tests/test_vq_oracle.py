@@ -31,3 +31,26 @@ def test_vq_param_inventory_matches_reference_order():
     assert "encoder.down.1.block.0.nin_shortcut.weight" in names and "encoder.down.0.block.0.nin_shortcut.weight" not in names
     assert "encoder.down.1.downsample.conv.weight" in names and "encoder.down.2.downsample.conv.weight" not in names
     assert "encoder.mid.attn_1.proj_out.bias" in names
+
+
+@pytest.mark.parametrize("name,cfg", [("tiny", VO.TINY_VQ), ("shapes3d", VO.SHAPES3D_VQ)])
+def test_vq_decode_oracle_vs_reference_golden(name, cfg):
+    g = np.load(os.path.join(GOLDEN, f"vq_decoder_{name}.npz"))
+    dd = int(g["disentangled_dim"])
+    params = VO.make_dec_params(cfg, seed=2, n_embed=64, disentangled_dim=dd)
+    assert sum(v.numel() for k, v in params.items() if not k.startswith("quantize.")) == int(g["n_params"])
+    with torch.no_grad():
+        img = VO.vq_decode(params, cfg, torch.tensor(g["h"]), force_not_quantize=True, disentangled_repr=torch.tensor(g["s"]),
+                           disentangled_dim=dd)
+        img0 = VO.vq_decode(params, cfg, torch.tensor(g["h"]), force_not_quantize=True, disentangled_dim=dd)
+    assert (img - torch.tensor(g["img"])).abs().max().item() / np.abs(g["img"]).max() <= 2e-5
+    assert (img0 - torch.tensor(g["img_zero_s"])).abs().max().item() / np.abs(g["img_zero_s"]).max() <= 2e-5
+
+
+def test_vq_nearest_is_argmin_of_squared_distance():
+    g = torch.Generator().manual_seed(3)
+    z, e = torch.randn(2, 3, 4, 4, generator=g), torch.randn(50, 3, generator=g)
+    q = VO.vq_nearest(z, e)
+    zf = z.permute(0, 2, 3, 1).reshape(-1, 3)
+    idx = ((zf[:, None] - e[None]) ** 2).sum(-1).argmin(1)
+    assert torch.equal(q.permute(0, 2, 3, 1).reshape(-1, 3), e[idx])
