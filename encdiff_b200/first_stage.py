@@ -303,3 +303,41 @@ class VQDecoder(nn.Module):
         return img.type(h.dtype)
 
     forward = decode
+
+
+# ---- reference seam ------------------------------------------------------------------------------------------------
+def _ddconfig_of(fs):
+    """ddconfig of a reference VQModel(Interface) instance, read back from its modules (the constructor does not keep it)."""
+    enc = fs.encoder
+    ch = enc.ch
+    mult = [blk.block[-1].out_channels // ch for blk in enc.down]
+    return dict(double_z=False, z_channels=fs.quant_conv.in_channels, resolution=enc.resolution, in_channels=enc.in_channels,
+                out_ch=fs.decoder.conv_out.out_channels, ch=ch, ch_mult=mult, num_res_blocks=enc.num_res_blocks,
+                attn_resolutions=[], dropout=0.0)
+
+
+def from_reference(fs, device=None):
+    """(VQEncoder, VQDecoder) holding the weights of a reference ``VQModelInterface`` instance (``model.first_stage_model``)."""
+    dd = _ddconfig_of(fs)
+    sd = fs.state_dict()
+    dev = device if device is not None else next(fs.parameters()).device
+    enc = VQEncoder(embed_dim=fs.embed_dim, ddconfig=dd)
+    enc.load_state_dict({k: v for k, v in sd.items() if k.startswith(("encoder.", "quant_conv."))}, strict=True)
+    cat = bool(getattr(fs, "use_disentangled_concat", False))
+    dec = VQDecoder(embed_dim=fs.embed_dim, n_embed=fs.n_embed, ddconfig=dd, use_disentangled_concat=cat,
+                    disentangled_dim=getattr(fs, "disentangled_dim", 0) if cat else 0)
+    dec.load_state_dict({k: v for k, v in sd.items()
+                         if k.startswith(("decoder.", "post_quant_conv.")) or k == "quantize.embedding.weight"}, strict=True)
+    return enc.to(dev), dec.to(dev)
+
+
+def install(fs):
+    """Rebind ``fs.encode`` / ``fs.decode`` of a reference ``VQModelInterface`` instance to the CUDA paths (the frozen first
+    stage of LatentDiffusion: ``encode_first_stage`` / ``decode_first_stage`` call exactly these two methods,
+    ddpm_enc.py).  Returns (encoder, decoder); ``fs`` keeps its own modules and parameters (checkpoints keep loading; call
+    ``install`` again after loading new first-stage weights)."""
+    enc, dec = from_reference(fs)
+    fs.encode = enc.encode
+    fs.decode = dec.decode
+    fs._encdiff_b200 = (enc, dec)
+    return enc, dec

@@ -145,3 +145,29 @@ def test_swap_vs_reference_log_images_golden(cuda_device):
     per_run = min(psnr(got[i * N:(i + 1) * N], want[i * N:(i + 1) * N]) for i in range(cfg.latent_unit))
     print(f"swap generation vs the reference's log_images: PSNR {p:.1f} dB (worst run {per_run:.1f} dB)")
     assert p >= 40.0 and per_run >= 40.0
+
+
+@needs_ref
+def test_first_stage_install_encode_decode(pair, cuda_device):
+    """encdiff_b200.first_stage.install() on the reference's OWN first_stage_model (the real VQModelInterface built by
+    instantiate_from_config; its quantiser is ref_shim's restatement of the absent taming module): encode and decode through
+    the rebound methods against the reference modules in fp32 on the same GPU."""
+    from encdiff_b200 import first_stage
+    cfg, ref, mine = pair
+    fs_ref, fs = ref.first_stage_model, mine.first_stage_model
+    g = torch.Generator().manual_seed(41)
+    x = (torch.rand(6, 3, 64, 64, generator=g) * 2 - 1).to(cuda_device)
+    s = torch.randn(6, cfg.latent_unit, generator=g).to(cuda_device)
+    with torch.no_grad():
+        z_ref = fs_ref.encode(x)
+        img_ref = fs_ref.decode(z_ref, disentangled_repr=s)
+        img_ref_nq = fs_ref.decode(z_ref, force_not_quantize=True)
+    enc, dec = first_stage.install(fs)
+    z = fs.encode(x)
+    img = fs.decode(z_ref, disentangled_repr=s)
+    img_nq = fs.decode(z_ref, force_not_quantize=True)
+    rel = lambda a, b: ((a - b).abs().max() / b.abs().max()).item()
+    print(f"first stage through the reference seam: encode {rel(z, z_ref):.3e}, decode {rel(img, img_ref):.3e}, "
+          f"decode w/o quantisation {rel(img_nq, img_ref_nq):.3e}")
+    assert type(enc).__name__ == "VQEncoder" and type(dec).__name__ == "VQDecoder"
+    assert rel(z, z_ref) <= 1e-2 and rel(img, img_ref) <= 1e-2 and rel(img_nq, img_ref_nq) <= 1e-2

@@ -1,4 +1,4 @@
-"""First-stage VQ-f4 encode throughput at the training batch: encdiff_b200.VQEncoder (eager launches
+"""First-stage VQ-f4 encode AND decode throughput at the training / sampling batch: encdiff_b200.VQEncoder (eager launches
 and a replayed CUDA graph) next to the reference's own Encoder + quant_conv (oracle/_ref through oracle/make_vq_golden's
 builder) in PyTorch eager mode on the same GPU (TF32, as the reference ships) and on the host cores (bounded sample).
 Prints one JSON line.  usage: python tools/vq_bench.py [B]"""
@@ -26,6 +26,53 @@ def timed(fn, reps):
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / reps
+
+
+GFLOP_IMG_DEC = 2.492      # VQ decode
+
+
+def decode_leg(B, dev, pk):
+    """VQDecoder.decode (quantise + concat + post_quant_conv + Decoder) at batch B, replayed graph, next to the reference
+    Decoder + post_quant_conv in eager mode on the same GPU (TF32) on an already-quantised latent."""
+    from test_vq_gpu import make_vqdec
+    cfg = VO.SHAPES3D_VQ
+    m, params = make_vqdec(cfg, dev, 2048, 20)
+    g = torch.Generator().manual_seed(29)
+    h = torch.randn(B, 3, 16, 16, generator=g).to(dev)
+    s = torch.randn(B, 20, generator=g).to(dev)
+    for _ in range(2):
+        m.decode(h, disentangled_repr=s)
+    ms_eager = timed(lambda: m.decode(h, disentangled_repr=s), 10)
+    graph = torch.cuda.CUDAGraph()
+    torch.cuda.synchronize()
+    with torch.cuda.graph(graph):
+        img = m.decode(h, disentangled_repr=s)
+    for _ in range(3):
+        graph.replay()
+    ms_graph = timed(graph.replay, 20)
+    out = {"metric": "vq_f4_decode_img_per_s", "batch": B, "value": B / (ms_graph / 1e3), "ms_per_batch_graph": ms_graph,
+           "ms_per_batch_eager": ms_eager, "gflop_per_img": GFLOP_IMG_DEC,
+           "tensor_frac": B / (ms_graph / 1e3) * GFLOP_IMG_DEC / 1e3 / pk["tf_sustained"],
+           "workspace_gb": m._lib.encdiff_vqdec_workspace_bytes(m._h, B) / 1e9}
+    try:
+        from oracle.make_vq_golden import reference_decoder
+        dec, pqc = reference_decoder(cfg, params, 20)
+        dec, pqc = dec.to(dev), pqc.to(dev)
+        torch.backends.cuda.matmul.allow_tf32 = True
+        torch.backends.cudnn.allow_tf32 = True
+        with torch.no_grad():
+            q = torch.cat([h, s[:, :, None, None].expand(-1, -1, 16, 16)], dim=1)
+            for _ in range(2):
+                dec(pqc(q))
+            ms_ref = timed(lambda: dec(pqc(q)), 5)
+            out["ref_eager_gpu_tf32"] = {"img_per_s": B / (ms_ref / 1e3), "ms_per_batch": ms_ref,
+                                         "note": "Decoder + post_quant_conv only (no quantiser)"}
+            ref = dec(pqc(q))
+            out["rel_err_vs_ref_gpu_tf32_no_quant"] = ((m.decode(h, force_not_quantize=True, disentangled_repr=s) - ref).abs().max()
+                                                       / ref.abs().max()).item()
+    except Exception as e:
+        out["ref_error"] = repr(e)[:200]
+    return out
 
 
 def main():
@@ -98,6 +145,7 @@ def main():
             out["ref_cpu"] = {"img_per_s": 32 / sec, "cores": torch.get_num_threads(), "sample": "3 passes of a batch-32 sample, fp32"}
     except Exception as e:      # oracle/_ref missing on this box
         out["ref_error"] = repr(e)[:200]
+    out["decode"] = decode_leg(B, dev, pk)
     print(json.dumps(out), flush=True)
 
 
