@@ -360,12 +360,28 @@ def run_b200(args):
         line["swap_ddim200"] = swap
     if world == 1 and not args.no_cpu:
         sec, cores, kind = cpu_train_step_time(B, 3, 1)
+        cfg1 = None
+        if kind == "reference":
+            try:
+                from oracle import ref_bench
+                s1, c1, _ = ref_bench.full_step_time(8, 3, 1, "cpu")
+                cfg1 = {"img_per_s": 8 / s1, "ms_per_step": s1 * 1e3, "batch": 8, "cores": c1,
+                        "what": "configs[0]: the complete reference step from images (VQ-f4 encode + Encoder4 + UNet p_losses "
+                                "fwd+bwd + AdamW + LitEma), batch 8, host cores"}
+            except Exception as e:
+                cfg1 = {"error": repr(e)[:200]}
+        line["config1_cpu_full_step"] = cfg1
         line["cpu_baseline"] = {"value": B / sec, "unit": UNIT, "cores": cores, "kind": kind,
                                 "sample": f"3 timed steps (median, 1 warm-up) of the full batch {B}, fp32, all host threads: "
                                           + ("the unmodified reference LatentDiffusion.p_losses fwd+bwd+AdamW+LitEma "
                                              "(oracle/_ref)" if kind == "reference" else "oracle port of p_losses fwd+bwd+AdamW")}
     if world == 1 and not args.no_comparators:
         line["comparators"] = gpu_comparators(model, dev, B, args.ddim_batch)
+        if args.workload == "shapes3d":
+            try:
+                line["full_pipeline"] = full_pipeline(dev, B)
+            except Exception as e:           # an extra leg must never take the headline down with it
+                line["full_pipeline_error"] = repr(e)[:300]
     print(json.dumps(line), flush=True)
     if dist_on:
         torch.distributed.destroy_process_group()
@@ -390,6 +406,10 @@ def gpu_comparators(model, dev, B, ddim_B):
                 dsec = ref_bench.ddim_time(ddim_B, 50, 2, dev, model=ref, **kw)
                 out[name] = {"train_img_per_s": B / sec, "train_ms_per_step": sec * 1e3, "batch": B,
                              "ddim50_img_per_s": ddim_B / dsec, "ddim50_batch": ddim_B}
+                if name == "ref_eager_gpu_tf32":      # the COMPLETE reference step from images (configs[0] at the benched batch)
+                    fsec, _, _ = ref_bench.full_step_time(B, 3, 2, dev, tf32=True, model=ref)
+                    out[name]["full_step_from_images_img_per_s"] = B / fsec
+                    out[name]["full_step_from_images_ms"] = fsec * 1e3
             del ref
             gc.collect()
             torch.cuda.empty_cache()
@@ -424,6 +444,48 @@ def gpu_comparators(model, dev, B, ddim_B):
     except Exception as e:
         out["dropin_autograd_error"] = repr(e)[:300]
     return out
+
+
+def full_pipeline(dev, B, steps=10):
+    """The COMPLETE EncDiff training step from images through this package (configs[0] / [1] as a training loop runs them):
+    pinned host images -> H2D -> frozen VQ-f4 encode (encdiff_b200.VQEncoder) -> concept encoder (encdiff_b200.Encoder4:
+    PyTorch conv trunk + the one-launch ConceptMLP) -> fused UNet step (DenoiserTrainer: q_sample, forward, L1, backward,
+    AdamW + EMA, re-pack) -> d loss / d tokens back through the concept encoder with torch autograd -> its AdamW.
+    Synthetic images, random-init weights; the loss is read back every step."""
+    from encdiff_b200 import Encoder4, VQEncoder
+    from encdiff_b200.train import DenoiserTrainer
+    torch.manual_seed(23)
+    vq = VQEncoder(embed_dim=3, ddconfig=dict(double_z=False, z_channels=3, resolution=64, in_channels=3, out_ch=3, ch=32,
+                                              ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[], dropout=0.0)).to(dev)
+    enc4 = Encoder4(d=128, context_dim=16, latent_unit=20).to(dev).train()
+    unet = build_model(dev)
+    trainer = DenoiserTrainer(unet, lr=1e-4)
+    opt_c = torch.optim.AdamW(enc4.parameters(), lr=1e-4)
+    g = torch.Generator().manual_seed(31)
+    host = [(torch.rand(B, 64, 64, 3, generator=g) * 2 - 1).pin_memory() for _ in range(3)]
+    gd = torch.Generator(device=dev).manual_seed(37)
+    loss_host = torch.zeros(1).pin_memory()
+
+    def step(i):
+        img = host[i % 3].to(dev, non_blocking=True).permute(0, 3, 1, 2).contiguous()    # 'b h w c -> b c h w', get_input
+        with torch.no_grad():
+            z = vq.encode(img)                                       # encode_first_stage (frozen), scale_factor 1
+        cond = enc4(img)                                             # get_learned_conditioning (trainable)
+        t = torch.randint(0, 1000, (B,), device=dev, generator=gd)
+        noise = torch.randn(z.shape, device=dev, generator=gd)
+        loss, dcond = trainer.step(z, cond.detach(), t, noise)
+        opt_c.zero_grad(set_to_none=True)
+        cond.backward(dcond)
+        opt_c.step()
+        loss_host.copy_(loss, non_blocking=True)
+
+    for i in range(4):
+        step(i)
+    ms = timed(step, steps, False) / steps
+    return {"img_per_s": B / (ms / 1e3), "ms_per_step": ms, "batch": B,
+            "h2d_bytes_per_step": host[0].numel() * 4,
+            "path": "images (pinned host) -> VQEncoder.encode -> Encoder4 (torch trunk + ConceptMLP) -> DenoiserTrainer.step "
+                    "-> concept-encoder backward + AdamW"}
 
 
 def ddim50(model, dev, B, dist_on, world):

@@ -9,5 +9,5 @@ __version__ = "0.1.0"
 from .modules import CrossAttention, SpatialTransformer  # noqa: F401
 from .unet import UNetModel  # noqa: F401
 from .sampler import DDIMSampler  # noqa: F401
-from .concept import ConceptMLP  # noqa: F401
+from .concept import ConceptMLP, Encoder4  # noqa: F401
 from .first_stage import VQDecoder, VQEncoder  # noqa: F401

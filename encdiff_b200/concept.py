@@ -84,10 +84,10 @@ class ConceptMLP(nn.Module):
 
     @staticmethod
     def _to_reference_keys(module, state, prefix, local_metadata):
-        for mine, ref in ConceptMLP._MAP:
-            stacked = state.pop(prefix + mine)
-            for i in range(module.latent_unit):
-                t = stacked[i]
+        stacked = {mine: state.pop(prefix + mine) for mine, _ in ConceptMLP._MAP}
+        for i in range(module.latent_unit):                 # unit-major: the key ORDER of the reference's ModuleList too
+            for mine, ref in ConceptMLP._MAP:
+                t = stacked[mine][i]
                 state[f"{prefix}{i}.{ref}"] = t.reshape(H1, 1) if mine == "w1" else t
         return state
 
@@ -121,3 +121,49 @@ class ConceptMLP(nn.Module):
         [B, L * context_dim] (what ``x[:, i][:, None]`` and ``th.cat(out, dim=1)`` produce in the reference)."""
         y = self.forward(x)
         return y.reshape(x.shape[0], self.latent_unit, self.context_dim) if x.dim() == 3 else y
+
+
+class _EncResBlock(nn.Module):
+    """Parameter / structure mirror of the reference's EncResBlock (openaimodel_enc.py:969-989): x + convs(x)."""
+
+    def __init__(self, cin, cout, bn=False):
+        super().__init__()
+        layers = [nn.ReLU(), nn.Conv2d(cin, cout, 3, 1, 1), nn.ReLU(), nn.Conv2d(cout, cout, 1, 1, 0)]
+        if bn:
+            layers.insert(2, nn.BatchNorm2d(cout))
+        self.convs = nn.Sequential(*layers)
+
+    def forward(self, x):
+        return x + self.convs(x)
+
+
+class Encoder4(nn.Module):
+    """Drop-in for the reference's concept encoder (``cond_stage_config.target: encdiff_b200.Encoder4``; constructor,
+    ``forward`` / ``encoding`` / ``warp`` and ``state_dict`` keys of openaimodel_enc.py:991-1041).  The 20 per-unit MLPs run
+    as ONE CUDA launch (``ConceptMLP``; the reference loops over ``self.net[i]`` in Python, :1029-1031 and :1039-1040).  The
+    convolutional trunk (four 4x4 stride-2 convolutions, BatchNorm, two EncResBlocks, one Linear: 0.1 GFLOP per image)
+    stays a PyTorch ``nn.Sequential`` with the reference's layer order -- the north star keeps the concept encoder's trunk
+    a PyTorch front end; it is NOT one of this package's hand-written kernels."""
+
+    def __init__(self, d, context_dim, latent_unit, bn=True, num_channels=3):
+        super().__init__()
+        self.context_dim, self.latent_unit = context_dim, latent_unit
+        self.encoder = nn.Sequential(
+            nn.Conv2d(num_channels, d, 4, 2, 1), nn.BatchNorm2d(d), nn.ReLU(inplace=True),
+            nn.Conv2d(d, d, 4, 2, 1), nn.BatchNorm2d(d), nn.ReLU(inplace=True),
+            nn.Conv2d(d, d, 4, 2, 1), nn.BatchNorm2d(d),
+            nn.Conv2d(d, d, 4, 2, 1), nn.BatchNorm2d(d), nn.ReLU(inplace=True),
+            _EncResBlock(d, d, bn=bn), nn.BatchNorm2d(d), nn.ReLU(inplace=True),
+            _EncResBlock(d, d, bn=bn),
+            nn.Flatten(1),                              # the reference's View((-1, 128 * 4 * 4)): no parameters either
+            nn.Linear(2048, latent_unit))
+        self.net = ConceptMLP(latent_unit, context_dim)
+
+    def encoding(self, x):
+        return self.encoder(x)
+
+    def warp(self, x):
+        return self.net.warp(x)
+
+    def forward(self, x):
+        return self.net(self.encoder(x))

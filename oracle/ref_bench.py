@@ -103,3 +103,39 @@ def ddim_time(B, S, reps, device, tf32=False, autocast_dtype=None, model=None):
             times.append(time.perf_counter() - t0)
     model.train()
     return statistics.median(times)
+
+
+def full_step_time(B, steps, warmup, device="cpu", tf32=False, model=None):
+    """configs[0] as defined (SURVEY.md 8d "Config 1"): the COMPLETE reference training step from images --
+    ``LatentDiffusion.shared_step`` (ddpm_enc.py:1018-1021) = get_input (VQ-f4 encode of the images, frozen) + forward
+    (Encoder4 on the images, random t, p_losses through the UNet) -- then ``loss.backward()``, AdamW over the UNet and the
+    trainable concept encoder (configure_optimizers, ddpm_enc.py:1598-1612) and LitEma.  Median seconds per step."""
+    dev = torch.device(device)
+    if dev.type == "cpu":
+        torch.set_num_threads(os.cpu_count() or 1)
+    else:
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+        torch.backends.cudnn.allow_tf32 = tf32
+    model = build(dev) if model is None else model
+    params = list(model.model.parameters()) + list(model.cond_stage_model.parameters())
+    opt = torch.optim.AdamW(params, lr=1e-4)
+    g = torch.Generator().manual_seed(23)
+    batch = {"image": (torch.rand(B, 64, 64, 3, generator=g) * 2 - 1).to(dev)}
+    times = []
+    for i in range(warmup + steps):
+        if dev.type == "cuda":
+            torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        opt.zero_grad(set_to_none=True)
+        out = model.shared_step(batch)
+        loss = out[0] if isinstance(out, tuple) else out
+        loss = loss[0] if isinstance(loss, tuple) else loss
+        loss.backward()
+        opt.step()
+        if model.use_ema:
+            model.model_ema(model.model)
+        if dev.type == "cuda":
+            torch.cuda.synchronize()
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    return statistics.median(times), (torch.get_num_threads() if dev.type == "cpu" else 0), float(loss.detach())
