@@ -455,6 +455,9 @@ def full_pipeline(dev, B, steps=10):
     from encdiff_b200 import Encoder4, VQEncoder
     from encdiff_b200.train import DenoiserTrainer
     torch.manual_seed(23)
+    # the PyTorch trunk of the concept encoder runs as the reference runs it on a GPU: TF32 (main_val.py:524-525)
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.allow_tf32 = True
     vq = VQEncoder(embed_dim=3, ddconfig=dict(double_z=False, z_channels=3, resolution=64, in_channels=3, out_ch=3, ch=32,
                                               ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[], dropout=0.0)).to(dev)
     enc4 = Encoder4(d=128, context_dim=16, latent_unit=20).to(dev).train()
