@@ -449,15 +449,12 @@ def gpu_comparators(model, dev, B, ddim_B):
 def full_pipeline(dev, B, steps=10):
     """The COMPLETE EncDiff training step from images through this package (configs[0] / [1] as a training loop runs them):
     pinned host images -> H2D -> frozen VQ-f4 encode (encdiff_b200.VQEncoder) -> concept encoder (encdiff_b200.Encoder4:
-    PyTorch conv trunk + the one-launch ConceptMLP) -> fused UNet step (DenoiserTrainer: q_sample, forward, L1, backward,
-    AdamW + EMA, re-pack) -> d loss / d tokens back through the concept encoder with torch autograd -> its AdamW.
+    encdiff_enc4_* trunk + the one-launch ConceptMLP) -> fused UNet step (DenoiserTrainer: q_sample, forward, L1, backward,
+    AdamW + EMA, re-pack) -> d loss / d tokens back through the concept encoder (encdiff_enc4_backward) -> its AdamW.
     Synthetic images, random-init weights; the loss is read back every step."""
     from encdiff_b200 import Encoder4, VQEncoder
     from encdiff_b200.train import DenoiserTrainer
     torch.manual_seed(23)
-    # the PyTorch trunk of the concept encoder runs as the reference runs it on a GPU: TF32 (main_val.py:524-525)
-    torch.backends.cuda.matmul.allow_tf32 = True
-    torch.backends.cudnn.allow_tf32 = True
     vq = VQEncoder(embed_dim=3, ddconfig=dict(double_z=False, z_channels=3, resolution=64, in_channels=3, out_ch=3, ch=32,
                                               ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[], dropout=0.0)).to(dev)
     enc4 = Encoder4(d=128, context_dim=16, latent_unit=20).to(dev).train()
@@ -487,7 +484,7 @@ def full_pipeline(dev, B, steps=10):
     ms = timed(step, steps, False) / steps
     return {"img_per_s": B / (ms / 1e3), "ms_per_step": ms, "batch": B,
             "h2d_bytes_per_step": host[0].numel() * 4,
-            "path": "images (pinned host) -> VQEncoder.encode -> Encoder4 (torch trunk + ConceptMLP) -> DenoiserTrainer.step "
+            "path": "images (pinned host) -> VQEncoder.encode -> Encoder4 (CUDA trunk + ConceptMLP) -> DenoiserTrainer.step "
                     "-> concept-encoder backward + AdamW"}
 
 

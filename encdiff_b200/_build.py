@@ -53,6 +53,20 @@ def _headers() -> list[Path]:
     return list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inc")) + [PKG_DIR.parent / "include" / "encdiff_b200.h"]
 
 
+def _includes(src: Path, seen=None) -> list[Path]:
+    """Files under csrc/ or include/ that ``src`` #includes with quotes, transitively (so a change to one .inc or .cuh
+    recompiles only the translation units that see it)."""
+    import re
+    seen = {} if seen is None else seen
+    for name in re.findall(r'^\s*#\s*include\s+"([^"]+)"', src.read_text(), flags=re.M):
+        for base in (CSRC, PKG_DIR.parent / "include"):
+            cand = base / name
+            if cand.exists() and cand not in seen:
+                seen[cand] = True
+                _includes(cand, seen)
+    return list(seen)
+
+
 def is_fresh() -> bool:
     stamp = BUILD_DIR / "stamp"
     deps = list(CSRC.glob("*.cu")) + _headers()
@@ -67,12 +81,11 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     BUILD_DIR.mkdir(exist_ok=True)
     srcs = sources()
     headers = _headers()
-    hdig = _digest(headers)
 
     def compile_one(src: Path):
         obj = BUILD_DIR / (src.stem + ".o")
         tag = BUILD_DIR / (src.stem + ".tag")
-        dig = hashlib.sha256((hdig + _digest([src])).encode()).hexdigest()
+        dig = hashlib.sha256((_digest(_includes(src)) + _digest([src])).encode()).hexdigest()
         if not force and obj.exists() and tag.exists() and tag.read_text() == dig:
             return obj, ""
         cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]

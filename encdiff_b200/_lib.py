@@ -63,6 +63,12 @@ PROTOTYPES = {
     "encdiff_vqdec_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
     "encdiff_vqdec_workspace_bytes": (c_ll, [c_void_p, c_int]),
     "encdiff_vqdec_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "encdiff_enc4_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
+    "encdiff_enc4_num_batchnorm": (c_int, [c_void_p]),
+    "encdiff_enc4_bind_stats": (c_int, [c_void_p, c_void_p]),
+    "encdiff_enc4_workspace_bytes": (c_ll, [c_void_p, c_int]),
+    "encdiff_enc4_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, C.c_float, c_void_p]),
+    "encdiff_enc4_backward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "encdiff_unet_fp32_workspace_bytes": (c_ll, [c_void_p, c_int]),
     "encdiff_unet_forward_fp32": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "encdiff_unet_profile": (c_int, [c_void_p, c_int]),
@@ -102,6 +108,11 @@ class VQEncConfigStruct(C.Structure):
 class VQDecConfigStruct(C.Structure):
     """Mirror of ``encdiff_vqdec_config`` (include/encdiff_b200.h)."""
     _fields_ = [("dd", VQEncConfigStruct), ("out_ch", c_int), ("n_embed", c_int), ("disentangled_dim", c_int)]
+
+
+class Enc4ConfigStruct(C.Structure):
+    """Mirror of ``encdiff_enc4_config`` (include/encdiff_b200.h)."""
+    _fields_ = [("d", c_int), ("latent_unit", c_int), ("num_channels", c_int), ("resolution", c_int), ("bn", c_int)]
 
 
 def lib_path() -> Path:

@@ -1,4 +1,5 @@
-"""The concept-token MLPs of EncDiff's encoder as one CUDA launch (the MLP half of it).
+"""EncDiff's concept encoder: the per-unit MLPs as one CUDA launch (``ConceptMLP``) and the
+drop-in ``Encoder4`` whose convolutional trunk runs forward and backward through ``encdiff_enc4_*``.
 
 Reference: ``Encoder4`` (ldm/modules/diffusionmodules/openaimodel_enc.py:991-1041) ends in ``latent_unit`` independent
 3-layer MLPs ``Linear(1, 64) - ELU - Linear(64, 128) - ELU - Linear(128, context_dim)`` held in ``self.net`` and run in a
@@ -10,10 +11,12 @@ and writes the reference's ``state_dict`` keys (``{i}.0.weight`` ... ``{i}.4.bia
     enc.net_fast = ConceptMLP.from_reference(enc.net)       # enc: the reference's Encoder4
     tokens = enc.net_fast(enc.encoding(images))             # == enc(images);   enc.net_fast(codes) == enc.warp(codes)
 
-The convolutional trunk of Encoder4 (4x4 stride-2 convolutions + BatchNorm) stays the reference's PyTorch code.
+``Encoder4`` (below) is the whole module: trunk (4x4 stride-2 convolutions, BatchNorm2d, EncResBlocks, Linear) + ConceptMLP.
 No CPU fallback: CPU tensors raise.
 """
 from __future__ import annotations
+
+import ctypes as C
 
 import torch
 from torch import nn
@@ -137,15 +140,39 @@ class _EncResBlock(nn.Module):
         return x + self.convs(x)
 
 
+class _TrunkFn(torch.autograd.Function):
+    """Autograd node over ``encdiff_enc4_forward`` / ``encdiff_enc4_backward``: every trunk parameter is an input and gets
+    its gradient as an output, so ``param.grad`` accumulates with torch semantics (hooks, DDP reducer)."""
+
+    @staticmethod
+    def forward(ctx, enc, x, *params):
+        codes = enc._trunk_forward(x)
+        ctx.enc, ctx.fwd_id, ctx.B = enc, enc._fwd_id, x.shape[0]
+        ctx.need = tuple(p.requires_grad for p in params)
+        return codes
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, dcodes):
+        enc = ctx.enc
+        if ctx.fwd_id != enc._fwd_id:
+            raise RuntimeError("encdiff_b200.Encoder4: the activation workspace of this forward was overwritten by a later "
+                               "forward; run backward before the next forward")
+        grads = enc._trunk_backward(dcodes, ctx.B)
+        return (None, None) + tuple(g if need else None for g, need in zip(grads, ctx.need))
+
+
 class Encoder4(nn.Module):
     """Drop-in for the reference's concept encoder (``cond_stage_config.target: encdiff_b200.Encoder4``; constructor,
     ``forward`` / ``encoding`` / ``warp`` and ``state_dict`` keys of openaimodel_enc.py:991-1041).  The 20 per-unit MLPs run
     as ONE CUDA launch (``ConceptMLP``; the reference loops over ``self.net[i]`` in Python, :1029-1031 and :1039-1040).  The
-    convolutional trunk (four 4x4 stride-2 convolutions, BatchNorm, two EncResBlocks, one Linear: 0.1 GFLOP per image)
-    stays a PyTorch ``nn.Sequential`` with the reference's layer order -- the north star keeps the concept encoder's trunk
-    a PyTorch front end; it is NOT one of this package's hand-written kernels."""
+    convolutional trunk (four 4x4 stride-2 convolutions, BatchNorm2d in train or eval mode, two EncResBlocks, one Linear:
+    0.1 GFLOP per image) runs forward and backward through ``encdiff_enc4_*`` (im2col + tcgen05 GEMMs, csrc/enc4.inc) for
+    the shipped configuration (d = 128, bn=True, 64 x 64 images); ``self.encoder`` is the parameter / buffer holder with
+    the reference's layer indices.  Other configurations raise at construction unless ``torch_trunk=True`` asks for the
+    plain PyTorch ``nn.Sequential`` (a front end outside this package's kernels)."""
 
-    def __init__(self, d, context_dim, latent_unit, bn=True, num_channels=3):
+    def __init__(self, d, context_dim, latent_unit, bn=True, num_channels=3, torch_trunk=False):
         super().__init__()
         self.context_dim, self.latent_unit = context_dim, latent_unit
         self.encoder = nn.Sequential(
@@ -158,12 +185,121 @@ class Encoder4(nn.Module):
             nn.Flatten(1),                              # the reference's View((-1, 128 * 4 * 4)): no parameters either
             nn.Linear(2048, latent_unit))
         self.net = ConceptMLP(latent_unit, context_dim)
+        self.torch_trunk = bool(torch_trunk)
+        self.num_channels, self.resolution = num_channels, 64
+        self._h = None
+        if not self.torch_trunk:
+            if d != 128 or not bn or num_channels * 16 > 64 or latent_unit > 64:
+                raise NotImplementedError("encdiff_b200.Encoder4: the CUDA trunk implements d=128, bn=True, num_channels<=4, "
+                                          "latent_unit<=64 (pass torch_trunk=True for the PyTorch trunk)")
+            self._lib = _lib.load()
+            cfg = _lib.Enc4ConfigStruct(d, latent_unit, num_channels, 64, 1)
+            h = C.c_void_p()
+            _lib.check(self._lib.encdiff_enc4_create(C.byref(cfg), C.byref(h)), "enc4_create")
+            self._h = h
+            mine = list(self.encoder.named_parameters())
+            n = self._lib.encdiff_unet_num_params(self._h)
+            buf, shape, nd = C.create_string_buffer(256), (C.c_longlong * 4)(), C.c_int()
+            if n != len(mine):
+                raise RuntimeError(f"encdiff_b200.Encoder4: library expects {n} trunk tensors, module has {len(mine)}")
+            for i, (name, p) in enumerate(mine):
+                _lib.check(self._lib.encdiff_unet_param_info(self._h, i, buf, 256, shape, C.byref(nd)), "param_info")
+                if buf.value.decode() != "encoder." + name or tuple(shape[k] for k in range(nd.value)) != tuple(p.shape):
+                    raise RuntimeError(f"encdiff_b200.Encoder4: parameter {i} mismatch: module encoder.{name}{tuple(p.shape)} "
+                                       f"vs library {buf.value.decode()}{tuple(shape[k] for k in range(nd.value))}")
+        self._bound_key = None
+        self._packed = self._ws = self._gflat = None
+        self._fwd_id = 0
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.encdiff_unet_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    # ---- CUDA trunk ---------------------------------------------------------------------------------------------
+    def _bns(self):
+        return [m for m in self.encoder.modules() if isinstance(m, nn.BatchNorm2d)]
+
+    def _bind(self):
+        params = list(self.encoder.parameters())
+        stats = [t for m in self._bns() for t in (m.running_mean, m.running_var)]
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("encdiff_b200.Encoder4 runs on CUDA only (sm_100a kernels, no CPU fallback)")
+        for p in params + stats:
+            if p.dtype != torch.float32 or not p.is_contiguous():
+                raise RuntimeError("encdiff_b200.Encoder4 keeps fp32 contiguous parameters and BatchNorm statistics")
+        key = tuple(p.data_ptr() for p in params + stats)
+        if key == self._bound_key:
+            return
+        if self._packed is None or self._packed.device != dev:
+            self._packed = torch.empty(self._lib.encdiff_unet_packed_bytes(self._h) + 1024, dtype=torch.uint8, device=dev)
+            self._gflat = torch.zeros(sum(p.numel() for p in params), dtype=torch.float32, device=dev)
+        views, off = [], 0
+        for p in params:
+            views.append(self._gflat[off:off + p.numel()].view_as(p))
+            off += p.numel()
+        self._grad_views = views
+        ptr = (self._packed.data_ptr() + 1023) // 1024 * 1024
+        pp = (C.c_void_p * len(params))(*[p.data_ptr() for p in params])
+        gp = (C.c_void_p * len(params))(*[v.data_ptr() for v in views])
+        _lib.check(self._lib.encdiff_unet_bind(self._h, pp, gp, ptr, _lib.current_stream()), "enc4 bind")
+        sp = (C.c_void_p * len(stats))(*[t.data_ptr() for t in stats])
+        _lib.check(self._lib.encdiff_enc4_bind_stats(self._h, sp), "enc4 bind_stats")
+        self._bound_key = key
+
+    def _workspace(self, B, dev):
+        nbytes = self._lib.encdiff_enc4_workspace_bytes(self._h, B)
+        if self._ws is None or self._ws.numel() < nbytes + 1024 or self._ws.device != dev:
+            self._ws = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
+        return (self._ws.data_ptr() + 1023) // 1024 * 1024
+
+    def _trunk_forward(self, x):
+        B = x.shape[0]
+        if tuple(x.shape[1:]) != (self.num_channels, self.resolution, self.resolution):
+            raise RuntimeError(f"encdiff_b200.Encoder4: expected (B,{self.num_channels},64,64) images, got {tuple(x.shape)}")
+        self._bind()
+        _lib.check(self._lib.encdiff_unet_pack_weights(self._h, _lib.current_stream()), "enc4 pack")
+        xf = x.contiguous().float()
+        codes = torch.empty(B, self.latent_unit, dtype=torch.float32, device=x.device)
+        bns = self._bns()
+        training = bool(self.encoder.training)
+        _lib.check(self._lib.encdiff_enc4_forward(self._h, B, xf.data_ptr(), codes.data_ptr(), self._workspace(B, x.device),
+                                                  int(training), float(bns[0].momentum), _lib.current_stream()), "enc4_forward")
+        if training:
+            torch._foreach_add_([m.num_batches_tracked for m in bns], 1)
+        self._fwd_id += 1
+        return codes
+
+    def _trunk_backward(self, dcodes, B):
+        self._gflat.zero_()
+        d = dcodes.contiguous().float()
+        _lib.check(self._lib.encdiff_enc4_backward(self._h, B, d.data_ptr(), self._workspace(B, d.device),
+                                                   _lib.current_stream()), "enc4_backward")
+        flat = self._gflat.clone()
+        out, off = [], 0
+        for v in self._grad_views:
+            out.append(flat[off:off + v.numel()].view_as(v))
+            off += v.numel()
+        return out
 
     def encoding(self, x):
-        return self.encoder(x)
+        if self.torch_trunk:
+            return self.encoder(x)
+        if not x.is_cuda:
+            raise RuntimeError("encdiff_b200.Encoder4 needs CUDA tensors (no CPU fallback)")
+        if x.requires_grad:
+            raise NotImplementedError("encdiff_b200.Encoder4: gradients w.r.t. the images are not implemented")
+        params = list(self.encoder.parameters())
+        if torch.is_grad_enabled() and any(p.requires_grad for p in params):
+            return _TrunkFn.apply(self, x, *params)
+        return self._trunk_forward(x)
 
     def warp(self, x):
         return self.net.warp(x)
 
     def forward(self, x):
-        return self.net(self.encoder(x))
+        return self.net(self.encoding(x))

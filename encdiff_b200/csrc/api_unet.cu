@@ -161,6 +161,50 @@ extern "C" int encdiff_vqdec_forward(encdiff_unet* h, int batch, const float* la
                        static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int encdiff_enc4_create(const encdiff_enc4_config* cfg, encdiff_unet** out) {
+  EDB_REQUIRE(cfg && out, "enc4_create: null argument");
+  encdiff_unet* h = new (std::nothrow) encdiff_unet();
+  EDB_REQUIRE(h, "enc4_create: out of host memory");
+  int rc = enc4_build(&h->u, cfg);
+  if (rc) {
+    delete h;
+    return rc;
+  }
+  h->u.side_on = false;        // one stream: the im2col matrices are overwritten by their gradients in place
+  h->u.group_wgrad = false;
+  *out = h;
+  return EDB_OK;
+}
+
+extern "C" int encdiff_enc4_num_batchnorm(const encdiff_unet* h) { return h && h->u.model_kind == 3 ? 7 : -1; }
+
+extern "C" int encdiff_enc4_bind_stats(encdiff_unet* h, float* const* stats) {
+  EDB_REQUIRE(h && h->u.model_kind == 3, "enc4_bind_stats: not a concept-encoder handle");
+  for (int i = 0; i < 14; ++i) h->u.e4.run[i] = stats ? stats[i] : nullptr;
+  return EDB_OK;
+}
+
+extern "C" long long encdiff_enc4_workspace_bytes(encdiff_unet* h, int batch) {
+  if (!h || batch <= 0 || h->u.model_kind != 3) return -1;
+  return static_cast<long long>(enc4_workspace_bytes(&h->u, batch));
+}
+
+extern "C" int encdiff_enc4_forward(encdiff_unet* h, int batch, const float* images, float* codes, void* workspace,
+                                    int training, float momentum, void* stream) {
+  EDB_REQUIRE(h && images && codes && workspace && batch > 0, "enc4_forward: bad argument");
+  EDB_REQUIRE(h->u.model_kind == 3, "enc4_forward: not a concept-encoder handle");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, "enc4_forward: workspace must be 1 KB aligned");
+  return enc4_forward(&h->u, batch, images, codes, static_cast<char*>(workspace), training, momentum,
+                      static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int encdiff_enc4_backward(encdiff_unet* h, int batch, const float* dcodes, void* workspace, void* stream) {
+  EDB_REQUIRE(h && dcodes && workspace && batch > 0, "enc4_backward: bad argument");
+  EDB_REQUIRE(h->u.model_kind == 3, "enc4_backward: not a concept-encoder handle");
+  EDB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, "enc4_backward: workspace must be 1 KB aligned");
+  return enc4_backward(&h->u, batch, dcodes, static_cast<char*>(workspace), static_cast<cudaStream_t>(stream));
+}
+
 extern "C" long long encdiff_unet_fp32_workspace_bytes(encdiff_unet* h, int batch) {
   if (!h || batch <= 0) return -1;
   return static_cast<long long>(unet_fp32_workspace_floats(&h->u, batch) * sizeof(float));

@@ -473,8 +473,12 @@ __global__ void __launch_bounds__(256) pack_kernel(const PackEntry* __restrict__
     if (en.kind == 4) {        // stem: flat reference order
       row = en.row0 + r;
       col = en.col0 + rem;
-    } else {                   // 5: stem transposed
+    } else if (en.kind == 5) { // stem transposed
       row = en.row0 + rem;
+      col = en.col0 + r;
+    } else {                   // 6: transposed, tap-major rows: dst[row0 + tap * cin_pad + ci][col0 + r]  (src [r][ci][tap])
+      const int ci = rem / en.taps, tap = rem - ci * en.taps;
+      row = en.row0 + static_cast<long long>(tap) * en.cin_pad + ci;
       col = en.col0 + r;
     }
     abf[en.dst_off + row * en.dst_ld + col] = f2h(v);

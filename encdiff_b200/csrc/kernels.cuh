@@ -165,6 +165,7 @@ struct PackEntry {
                          // 3: fp32 sum   dst[col0 + i] = src[i] + src2[i]
                          // 4: dst[row0+r][col0 + ci*taps + tap]      (stem: flat reference order)
                          // 5: dst[row0 + ci*taps + tap][col0 + r]    (stem transposed)
+                         // 6: dst[row0 + tap*cin_pad + ci][col0 + r]  (transposed, tap-major rows: dgrad of an im2col conv)
   int rows, cin, taps;
   int cin_pad, rows_pad;
   int dst_ld, row0, col0;
@@ -198,5 +199,24 @@ int launch_vq_post_quant(const float* h, const float* sdis, const float* codeboo
                          const float* bias, float* out, int B, int HW, int ed, int dd, int zc, cudaStream_t s);
 // quant_conv (1x1, zc -> ed) + NHWC fp32 -> NCHW fp32
 int launch_vq_tail(const float* h, const float* wq, const float* bq, float* z, int B, int HW, int zc, int ed, cudaStream_t s);
+
+// ---- concept-encoder trunk (enc4_kernels.cu) ---------------------------------------------------------------------
+// tap-major im2col of a k x k / stride / pad convolution over NHWC h16, its image (fp32 NCHW, flat (ci, tap) order, K <= 64)
+// variant, and the col2im gather of the input gradient (optional ReLU gate on `gate` > 0 and added skip gradient)
+int launch_e4_im2col(const h16* x, h16* cols, int B, int H, int W, int C, int k, int stride, int pad, cudaStream_t s);
+int launch_e4_im2col_image(const float* x, h16* cols, int B, int Cin, int H, int W, int k, int stride, int pad, cudaStream_t s);
+int launch_e4_col2im(const h16* dcols, h16* dx, const h16* gate, const h16* add, const float* add_from, const float* add_to,
+                     int B, int H, int W, int C, int k, int stride, int pad, cudaStream_t s);
+// BatchNorm2d: column sums (forward: x, x^2; backward: masked dy, dy * xhat), forward apply (+ running statistics, + ReLU),
+// backward apply (+ dgamma / dbeta)
+int launch_e4_bn_sums(const h16* x, const h16* dy, const h16* out, const float* stat, float* sums, long long M, int C, int bwd,
+                      cudaStream_t s);
+int launch_e4_bn_apply(const h16* x, const float* sums, const float* gamma, const float* beta, float* run_mean, float* run_var,
+                       float* stat, h16* y, long long M, int C, float eps, float momentum, int training, int relu, cudaStream_t s);
+int launch_e4_bn_bwd_apply(const h16* x, const h16* dy, const h16* out, const float* stat, const float* sums, const float* gamma,
+                           float* dgamma, float* dbeta, const float* gs_in, float* gs_out, h16* dx, long long M, int C,
+                           int training, cudaStream_t s);
+int launch_e4_flatten(const h16* in, h16* out, int B, int HW, int C, int to_flat, cudaStream_t s);
+int launch_e4_wgrad_finalize(float* stage, float* grad, int Cout, int C, int KK, cudaStream_t s);
 
 }  // namespace edb

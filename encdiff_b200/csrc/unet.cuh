@@ -171,6 +171,17 @@ struct UNet {
   encdiff_vqenc_config vqcfg;
   std::vector<VqLayer> vq;          // registration order (= parameter order)
   std::vector<int> vq_order;        // execution order (the decoder registers its levels in reverse)
+  // concept-encoder trunk (model_kind 3, enc4.inc): parameter indices and operands of the fixed Encoder4.encoder sequence
+  struct E4 {
+    encdiff_enc4_config cfg;
+    int cw[4], cb[4];            // the four 4x4 stride-2 convolutions (encoder.0 / 3 / 6 / 8)
+    int bw[7], bb[7];            // BatchNorm2d: encoder.1, 4, 7, 9, 11.convs.2, 12, 14.convs.2
+    int r3w[2], r3b[2], r1w[2], r1b[2];   // EncResBlock 3x3 / 1x1 convolutions (encoder.11, encoder.14)
+    int lw, lb;                  // encoder.16 Linear
+    Packed c0f, cf[4], ct[4], r3f[2], r3t[2], r1f[2], r1t[2], lf, lt;
+    float* run[14] = {nullptr};  // running_mean / running_var of the 7 BatchNorms (bind_stats)
+    int last_training = 1;
+  } e4;
   int vq_n_embed = 0, vq_dd = 0, vq_emb_w = -1, vq_pq_w = -1, vq_pq_b = -1, vq_img_ch = 0;
   int vq_in_w = -1, vq_in_b = -1, vq_no_w = -1, vq_no_b = -1, vq_co_w = -1, vq_co_b = -1, vq_qc_w = -1, vq_qc_b = -1;
   int vq_out_res = 0, vq_out_ch = 0;
@@ -188,6 +199,10 @@ int unet_backward(UNet* u, int B, const float* dout, const float* ctx, float* dx
 // fp32 validation forward (fp32_ref.cu): fp32 tensors, CUDA-core FMA contractions, reference-layout master parameters
 int vqenc_build(UNet* u, const encdiff_vqenc_config* cfg);
 int vqdec_build(UNet* u, const encdiff_vqdec_config* cfg);
+int enc4_build(UNet* u, const encdiff_enc4_config* cfg);
+size_t enc4_workspace_bytes(UNet* u, int B);
+int enc4_forward(UNet* u, int B, const float* img, float* codes, char* ws, int training, float momentum, cudaStream_t s);
+int enc4_backward(UNet* u, int B, const float* dcodes, char* ws, cudaStream_t s);
 size_t vqdec_workspace_bytes(UNet* u, int B);
 int vqdec_forward(UNet* u, int B, const float* latent, const float* sdis, int quantize, float* img, char* ws, cudaStream_t s);
 size_t vqenc_workspace_bytes(UNet* u, int B);

@@ -575,4 +575,75 @@ int vqdec_build(UNet* u, const encdiff_vqdec_config* cd) {
   return EDB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Concept encoder trunk: Encoder4.encoder (openaimodel_enc.py:995-1014).  Parameters in registration order; operands:
+// forward [Cout, taps * Cin] tap-major (the im2col column order), input-gradient [taps * Cin, Cout] (kind 6), the first
+// layer in the reference's flat order over one 64-wide chunk.
+// ---------------------------------------------------------------------------------------------------------------
+int enc4_build(UNet* u, const encdiff_enc4_config* c) {
+  u->model_kind = 3;
+  u->e4.cfg = *c;
+  memset(&u->cfg, 0, sizeof(u->cfg));
+  EDB_REQUIRE(c->d == 128, "enc4: d must be 128 (the reference's View((-1, 128 * 4 * 4)) fixes it)");
+  EDB_REQUIRE(c->resolution == 64, "enc4: resolution must be 64 (four stride-2 convolutions down to the 4 x 4 the Linear expects)");
+  EDB_REQUIRE(c->num_channels * 16 <= 64, "enc4: num_channels * 16 must fit one 64-wide K chunk");
+  EDB_REQUIRE(c->bn == 1, "enc4: only bn=True (the reference default) is implemented");
+  EDB_REQUIRE(c->latent_unit >= 1 && c->latent_unit <= 64, "enc4: latent_unit must be in 1..64");
+  UNet::E4& e = u->e4;
+  Builder b;
+  b.u = u;
+  const int d = c->d, L = c->latent_unit;
+  auto P = [&](const std::string& n, std::initializer_list<long long> shape) { return b.add_param("encoder." + n, shape); };
+  const int conv_idx[4] = {0, 3, 6, 8}, bn_idx[4] = {1, 4, 7, 9};
+  for (int i = 0; i < 4; ++i) {
+    const int cin = i == 0 ? c->num_channels : d;
+    e.cw[i] = P(std::to_string(conv_idx[i]) + ".weight", {d, cin, 4, 4});
+    e.cb[i] = P(std::to_string(conv_idx[i]) + ".bias", {d});
+    e.bw[i] = P(std::to_string(bn_idx[i]) + ".weight", {d});
+    e.bb[i] = P(std::to_string(bn_idx[i]) + ".bias", {d});
+  }
+  auto resblock = [&](int r, int idx, int bn_slot) {
+    const std::string n = std::to_string(idx) + ".convs.";
+    e.r3w[r] = P(n + "1.weight", {d, d, 3, 3});
+    e.r3b[r] = P(n + "1.bias", {d});
+    e.bw[bn_slot] = P(n + "2.weight", {d});
+    e.bb[bn_slot] = P(n + "2.bias", {d});
+    e.r1w[r] = P(n + "4.weight", {d, d, 1, 1});
+    e.r1b[r] = P(n + "4.bias", {d});
+  };
+  resblock(0, 11, 4);
+  e.bw[5] = P("12.weight", {d});
+  e.bb[5] = P("12.bias", {d});
+  resblock(1, 14, 6);
+  e.lw = P("16.weight", {L, 16LL * d});
+  e.lb = P("16.bias", {L});
+  // operands
+  e.c0f = b.alloc(d, 64);
+  b.entry(4, e.cw[0], -1, e.c0f.off, d, c->num_channels, 16, 0, 0, 64, 0, 0);
+  for (int i = 1; i < 4; ++i) {
+    e.cf[i] = b.alloc(d, 16LL * d);
+    b.pack_fwd(e.cf[i], e.cw[i], d, d, 16, 0, 0);
+    e.ct[i] = b.alloc(16LL * d, d);
+    b.entry(6, e.cw[i], -1, e.ct[i].off, d, d, 16, d, 0, d, 0, 0);
+  }
+  for (int r = 0; r < 2; ++r) {
+    e.r3f[r] = b.alloc(d, 9LL * d);
+    b.pack_fwd(e.r3f[r], e.r3w[r], d, d, 9, 0, 0);
+    e.r3t[r] = b.alloc(9LL * d, d);
+    b.entry(6, e.r3w[r], -1, e.r3t[r].off, d, d, 9, d, 0, d, 0, 0);
+    e.r1f[r] = b.alloc(d, d);
+    b.pack_fwd(e.r1f[r], e.r1w[r], d, d, 1, 0, 0);
+    e.r1t[r] = b.alloc(d, d);
+    b.pack_t(e.r1t[r], e.r1w[r], d, d, 1, 0, 0);
+  }
+  e.lf = b.alloc(L, 16LL * d);
+  b.pack_fwd(e.lf, e.lw, L, 16 * d, 1, 0, 0);
+  e.lt = b.alloc(16LL * d, 64);
+  b.pack_t(e.lt, e.lw, L, 16 * d, 1, 0, 0);
+  u->table_bytes = static_cast<size_t>(ceil_to(static_cast<long long>(u->table.size() * sizeof(PackEntry)), 1024));
+  u->h16_bytes = static_cast<size_t>(ceil_to(b.bf_off * 2, 1024));
+  u->f32_bytes = static_cast<size_t>(ceil_to(b.f32_off * 4, 1024));
+  return EDB_OK;
+}
+
 }  // namespace edb

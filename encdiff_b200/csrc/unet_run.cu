@@ -697,3 +697,4 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
 
 #include "unet_bwd.inc"
 #include "vq_enc.inc"
+#include "enc4.inc"

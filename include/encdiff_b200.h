@@ -264,6 +264,28 @@ long long encdiff_vqdec_workspace_bytes(encdiff_unet* h, int batch);
 int encdiff_vqdec_forward(encdiff_unet* h, int batch, const float* latent, const float* s, int quantize, float* img,
                           void* workspace, void* stream);
 
+/* Concept encoder trunk (the convolutional half): codes = Encoder4.encoder(images)
+ * (ldm/modules/diffusionmodules/openaimodel_enc.py:995-1014: four 4x4 stride-2 convolutions with BatchNorm2d / ReLU, two
+ * EncResBlocks :969-989 with a BatchNorm between them, View, Linear(16 d -> latent_unit)), forward AND backward (the concept
+ * encoder is trained with the UNet).  Same handle type and generic calls as the UNet: parameter names `encoder.N...` in the
+ * reference's registration order; bind() with gradient tensors for training.  BatchNorm follows torch.nn.BatchNorm2d
+ * (eps 1e-5): training != 0 normalises with batch statistics and updates the bound running statistics with `momentum`;
+ * training == 0 normalises with the running statistics.  The per-unit MLPs behind the trunk are encdiff_concept_mlp_*. */
+typedef struct encdiff_enc4_config {   /* cond_stage_config.params of shapes3d-vq-4-16-encdiff.yaml:77-82 (+ image size) */
+  int d, latent_unit, num_channels, resolution, bn;
+} encdiff_enc4_config;
+int encdiff_enc4_create(const encdiff_enc4_config* cfg /*host*/, encdiff_unet** out /*host*/);
+int encdiff_enc4_num_batchnorm(const encdiff_unet* h);
+/* running_mean / running_var device pointers of every BatchNorm2d in module order: stats[2 i], stats[2 i + 1] */
+int encdiff_enc4_bind_stats(encdiff_unet* h, float* const* stats /*host*/);
+long long encdiff_enc4_workspace_bytes(encdiff_unet* h, int batch);
+/* images [B, num_channels, R, R] fp32 NCHW -> codes [B, latent_unit] fp32; keeps what backward needs in the workspace */
+int encdiff_enc4_forward(encdiff_unet* h, int batch, const float* images, float* codes, void* workspace, int training,
+                         float momentum, void* stream);
+/* backward of the last forward (same workspace, same training flag): dcodes [B, latent_unit] fp32; parameter gradients are
+ * ACCUMULATED into the bound gradient tensors */
+int encdiff_enc4_backward(encdiff_unet* h, int batch, const float* dcodes, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

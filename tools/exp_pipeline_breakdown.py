@@ -1,5 +1,6 @@
-"""Where the full-pipeline step (bench.py full_pipeline) goes: CUDA-event time per phase, B = 256, TF32 off / on for the
-PyTorch trunk of the concept encoder, and channels_last / bf16-autocast variants of that trunk."""
+"""Where the full-pipeline step (bench.py full_pipeline) goes: CUDA-event time per phase, B = 256; the concept encoder's
+trunk through encdiff_enc4_* (the product path) and, for comparison, as the PyTorch nn.Sequential (torch_trunk=True) with
+TF32 off / on, channels_last and bf16 autocast."""
 import os
 import sys
 
@@ -19,10 +20,13 @@ def main():
     unet = bench.build_model(dev)
     trainer = DenoiserTrainer(unet, lr=1e-4)
     host = (torch.rand(B, 64, 64, 3) * 2 - 1).pin_memory()
-    for tf32, cl, ac in ((False, False, None), (True, False, None), (True, True, None), (True, True, torch.bfloat16)):
+    for tf32, cl, ac in (("cuda", False, None), (False, False, None), (True, False, None), (True, True, None),
+                         (True, True, torch.bfloat16)):
+        cuda_trunk = tf32 == "cuda"
+        tf32 = bool(tf32)
         torch.backends.cuda.matmul.allow_tf32 = tf32
         torch.backends.cudnn.allow_tf32 = tf32
-        enc4 = Encoder4(d=128, context_dim=16, latent_unit=20).to(dev).train()
+        enc4 = Encoder4(d=128, context_dim=16, latent_unit=20, torch_trunk=not cuda_trunk).to(dev).train()
         if cl:
             enc4.encoder = enc4.encoder.to(memory_format=torch.channels_last)
         opt_c = torch.optim.AdamW(enc4.parameters(), lr=1e-4, fused=True)
@@ -60,7 +64,7 @@ def main():
                 for k in range(7):
                     acc[k] += ev[k].elapsed_time(ev[k + 1])
         names = ["h2d+permute", "vq.encode", "enc4 fwd", "rng", "unet step", "enc4 bwd", "enc4 adamw"]
-        print(f"tf32={tf32} channels_last={cl} autocast={ac}: total {sum(acc)/n:.2f} ms  " +
+        print(f"{'CUDA trunk' if cuda_trunk else 'torch trunk'} tf32={tf32} channels_last={cl} autocast={ac}: total {sum(acc)/n:.2f} ms  " +
               "  ".join(f"{nm} {a/n:.2f}" for nm, a in zip(names, acc)), flush=True)
 
 
