@@ -453,30 +453,19 @@ def full_pipeline(dev, B, steps=10):
     AdamW + EMA, re-pack) -> d loss / d tokens back through the concept encoder (encdiff_enc4_backward) -> its AdamW.
     Synthetic images, random-init weights; the loss is read back every step."""
     from encdiff_b200 import Encoder4, VQEncoder
-    from encdiff_b200.train import DenoiserTrainer
+    from encdiff_b200.train import EncDiffTrainer
     torch.manual_seed(23)
     vq = VQEncoder(embed_dim=3, ddconfig=dict(double_z=False, z_channels=3, resolution=64, in_channels=3, out_ch=3, ch=32,
                                               ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[], dropout=0.0)).to(dev)
     enc4 = Encoder4(d=128, context_dim=16, latent_unit=20).to(dev).train()
-    unet = build_model(dev)
-    trainer = DenoiserTrainer(unet, lr=1e-4)
-    opt_c = torch.optim.AdamW(enc4.parameters(), lr=1e-4)
+    trainer = EncDiffTrainer(vq, enc4, build_model(dev), lr=1e-4)
     g = torch.Generator().manual_seed(31)
     host = [(torch.rand(B, 64, 64, 3, generator=g) * 2 - 1).pin_memory() for _ in range(3)]
-    gd = torch.Generator(device=dev).manual_seed(37)
     loss_host = torch.zeros(1).pin_memory()
 
     def step(i):
         img = host[i % 3].to(dev, non_blocking=True).permute(0, 3, 1, 2).contiguous()    # 'b h w c -> b c h w', get_input
-        with torch.no_grad():
-            z = vq.encode(img)                                       # encode_first_stage (frozen), scale_factor 1
-        cond = enc4(img)                                             # get_learned_conditioning (trainable)
-        t = torch.randint(0, 1000, (B,), device=dev, generator=gd)
-        noise = torch.randn(z.shape, device=dev, generator=gd)
-        loss, dcond = trainer.step(z, cond.detach(), t, noise)
-        opt_c.zero_grad(set_to_none=True)
-        cond.backward(dcond)
-        opt_c.step()
+        loss = trainer.step(img)              # t = randint, noise = randn_like drawn on the device, as forward / p_losses do
         loss_host.copy_(loss, non_blocking=True)
 
     for i in range(4):
@@ -484,8 +473,8 @@ def full_pipeline(dev, B, steps=10):
     ms = timed(step, steps, False) / steps
     return {"img_per_s": B / (ms / 1e3), "ms_per_step": ms, "batch": B,
             "h2d_bytes_per_step": host[0].numel() * 4,
-            "path": "images (pinned host) -> VQEncoder.encode -> Encoder4 (CUDA trunk + ConceptMLP) -> DenoiserTrainer.step "
-                    "-> concept-encoder backward + AdamW"}
+            "path": "encdiff_b200.train.EncDiffTrainer.step: images (pinned host) -> VQEncoder.encode -> Encoder4 (CUDA trunk + "
+                    "ConceptMLP) -> DenoiserTrainer.step -> concept-encoder backward -> its fused AdamW"}
 
 
 def ddim50(model, dev, B, dist_on, world):

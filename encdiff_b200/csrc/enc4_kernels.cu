@@ -15,65 +15,79 @@ inline int e4_grid(long long n, int threads, int cap = 148 * 16) {
 }
 
 // cols[(b, oy, ox)][tap * C + c] = x[b][oy*stride - pad + ky][ox*stride - pad + kx][c]   (tap = ky * k + kx; 0 outside)
-__global__ void e4_im2col_kernel(const h16* __restrict__ x, h16* __restrict__ cols, int B, int H, int W, int C, int k,
-                                 int stride, int pad, int Ho, int Wo) {
+// thread = (output pixel, kernel row ky, 8-channel chunk): the K taps of the row are K independent 16-byte loads in flight
+// (one load per thread left the kernel at a third of the HBM bandwidth: too few bytes in flight per SM)
+template <int K>
+__global__ void __launch_bounds__(256) e4_im2col_kernel(const h16* __restrict__ x, h16* __restrict__ cols, int B, int H, int W,
+                                                        int C, int stride, int pad, int Ho, int Wo) {
   pdl_enter();
-  const int cv = C / 8, KK = k * k;
-  const long long total = static_cast<long long>(B) * Ho * Wo * KK * cv;
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(B) * Ho * Wo * K * cv;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c8 = static_cast<int>(i % cv);
     long long r = i / cv;
-    const int tap = static_cast<int>(r % KK);
-    r /= KK;
+    const int ky = static_cast<int>(r % K);
+    r /= K;
     const int ox = static_cast<int>(r % Wo);
-    r /= Wo;
-    const int oy = static_cast<int>(r % Ho), b = static_cast<int>(r / Ho);
-    const int y = oy * stride - pad + tap / k, xx = ox * stride - pad + tap % k;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (y >= 0 && y < H && xx >= 0 && xx < W)
-      v = *reinterpret_cast<const uint4*>(x + ((static_cast<long long>(b) * H + y) * W + xx) * C + c8 * 8);
-    *reinterpret_cast<uint4*>(cols + i * 8) = v;
+    const long long bo = r / Wo;               // b * Ho + oy
+    const int oy = static_cast<int>(bo % Ho);
+    const long long b = bo / Ho;
+    const int y = oy * stride - pad + ky, x0 = ox * stride - pad;
+    const bool yin = y >= 0 && y < H;
+    const h16* src = x + ((b * H + y) * W + x0) * C + c8 * 8;
+    uint4 v[K];
+#pragma unroll
+    for (int kx = 0; kx < K; ++kx) {
+      v[kx] = make_uint4(0u, 0u, 0u, 0u);
+      if (yin && x0 + kx >= 0 && x0 + kx < W) v[kx] = *reinterpret_cast<const uint4*>(src + static_cast<long long>(kx) * C);
+    }
+    h16* dst = cols + (r * (K * K) + ky * K) * C + c8 * 8;
+#pragma unroll
+    for (int kx = 0; kx < K; ++kx) *reinterpret_cast<uint4*>(dst + static_cast<long long>(kx) * C) = v[kx];
   }
 }
 
-// first layer: fp32 NCHW image -> cols [M, 64] in the reference's flat weight order (ci * k*k + ky * k + kx), zero padded
-__global__ void e4_im2col_image_kernel(const float* __restrict__ x, h16* __restrict__ cols, int B, int Cin, int H, int W, int k,
-                                       int stride, int pad, int Ho, int Wo) {
+// first layer: fp32 NCHW image -> cols [M, 64] in the reference's flat weight order (ci * k*k + ky * k + kx), zero padded.
+// thread = (output pixel, 8-column chunk): one 16-byte store; a chunk is 8 consecutive (ci, tap) columns
+__global__ void __launch_bounds__(256) e4_im2col_image_kernel(const float* __restrict__ x, h16* __restrict__ cols, int B, int Cin,
+                                                              int H, int W, int k, int stride, int pad, int Ho, int Wo) {
   pdl_enter();
-  const long long total = static_cast<long long>(B) * Ho * Wo;
-  const int KK = k * k;
-  for (long long m = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; m < total;
-       m += static_cast<long long>(gridDim.x) * blockDim.x) {
+  const long long total = static_cast<long long>(B) * Ho * Wo * 8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int chunk = static_cast<int>(i & 7);
+    const long long m = i >> 3;
     const int ox = static_cast<int>(m % Wo);
-    const int oy = static_cast<int>((m / Wo) % Ho), b = static_cast<int>(m / (static_cast<long long>(Wo) * Ho));
-    h16 row[64];
+    const int oy = static_cast<int>((m / Wo) % Ho);
+    const long long b = m / (static_cast<long long>(Wo) * Ho);
+    // k = 4: a chunk is two kernel rows (ky = 2 * (chunk & 1) + {0, 1}) of input channel ci = chunk >> 1
+    const int ci = chunk >> 1, x0 = ox * stride - pad;
+    float f[8];
 #pragma unroll
-    for (int i = 0; i < 64; ++i) row[i] = f2h(0.f);
-    for (int ci = 0; ci < Cin; ++ci) {
-      const float* plane = x + (static_cast<long long>(b) * Cin + ci) * H * W;
-      for (int t = 0; t < KK; ++t) {
-        const int y = oy * stride - pad + t / k, xx = ox * stride - pad + t % k;
-        if (y >= 0 && y < H && xx >= 0 && xx < W && ci * KK + t < 64) row[ci * KK + t] = f2h(plane[y * W + xx]);
-      }
+    for (int j = 0; j < 8; ++j) {
+      const int y = oy * stride - pad + 2 * (chunk & 1) + (j >> 2), xx = x0 + (j & 3);
+      f[j] = 0.f;
+      if (ci < Cin && y >= 0 && y < H && xx >= 0 && xx < W) f[j] = x[((b * Cin + ci) * H + y) * W + xx];
     }
-    uint4* dst = reinterpret_cast<uint4*>(cols + m * 64);
-    const uint4* src = reinterpret_cast<const uint4*>(row);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) dst[i] = src[i];
+    *reinterpret_cast<uint4*>(cols + i * 8) = pack8(f);
   }
 }
 
 // dx[b][y][x][c] = (sum over the (oy, ox, tap) that read input pixel (y, x)) dcols[(b, oy, ox)][tap * C + c]
 //                  [* (gate[..] > 0)]  [+ add[..]]
 // gate: the block input of an EncResBlock (its leading ReLU, openaimodel_enc.py:976); add: the gradient of the skip path
-// (the skip gradient carries the range scale add_from, the result add_to: both powers of two, the factor is exact)
-__global__ void e4_col2im_kernel(const h16* __restrict__ dcols, h16* __restrict__ dx, const h16* __restrict__ gate,
-                                 const h16* __restrict__ add, const float* __restrict__ add_from,
-                                 const float* __restrict__ add_to, int B, int H, int W, int C, int k, int stride, int pad,
-                                 int Ho, int Wo) {
+// (the skip gradient carries the range scale add_from, the result add_to: both powers of two, the factor is exact).
+// Per dimension a pixel is read by T = ceil(K / S) taps: ky = ((y + pad) % S) + S * a.  All T*T loads are issued before
+// the sum.
+template <int K, int S>
+__global__ void __launch_bounds__(256) e4_col2im_kernel(const h16* __restrict__ dcols, h16* __restrict__ dx,
+                                                        const h16* __restrict__ gate, const h16* __restrict__ add,
+                                                        const float* __restrict__ add_from, const float* __restrict__ add_to,
+                                                        int B, int H, int W, int C, int pad, int Ho, int Wo) {
   pdl_enter();
-  const int cv = C / 8, KK = k * k;
+  constexpr int T = (K + S - 1) / S;
+  const int cv = C / 8;
   const float add_f = (add && add_from && add_to) ? add_to[0] * add_from[1] : 1.f;
   const long long total = static_cast<long long>(B) * H * W * cv;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -82,40 +96,49 @@ __global__ void e4_col2im_kernel(const h16* __restrict__ dcols, h16* __restrict_
     long long r = i / cv;
     const int xx = static_cast<int>(r % W);
     r /= W;
-    const int y = static_cast<int>(r % H), b = static_cast<int>(r / H);
-    float a[8];
+    const int y = static_cast<int>(r % H);
+    const long long b = r / H;
+    uint4 v[T * T];
+    uint4 gv = make_uint4(0u, 0u, 0u, 0u), av = gv;
+    if (gate) gv = *reinterpret_cast<const uint4*>(gate + i * 8);
+    if (add) av = *reinterpret_cast<const uint4*>(add + i * 8);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a[j] = 0.f;
-    for (int ky = 0; ky < k; ++ky) {
-      const int ty = y + pad - ky;
-      if (ty < 0 || ty % stride) continue;
-      const int oy = ty / stride;
-      if (oy >= Ho) continue;
-      for (int kx = 0; kx < k; ++kx) {
-        const int tx = xx + pad - kx;
-        if (tx < 0 || tx % stride) continue;
-        const int ox = tx / stride;
-        if (ox >= Wo) continue;
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(dcols + ((static_cast<long long>(b) * Ho + oy) * Wo + ox) * (static_cast<long long>(KK) * C) +
-                                                (ky * k + kx) * C + c8 * 8), f);
+    for (int a = 0; a < T; ++a) {
+      const int ky = (y + pad) % S + S * a, oy = (y + pad - ky) / S;      // y + pad - ky is a non-negative multiple of S or < 0
+      const bool yok = ky < K && y + pad - ky >= 0 && oy < Ho;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) a[j] += f[j];
+      for (int c = 0; c < T; ++c) {
+        const int kx = (xx + pad) % S + S * c, ox = (xx + pad - kx) / S;
+        const bool ok = yok && kx < K && xx + pad - kx >= 0 && ox < Wo;
+        v[a * T + c] = make_uint4(0u, 0u, 0u, 0u);
+        if (ok)
+          v[a * T + c] = *reinterpret_cast<const uint4*>(dcols + ((b * Ho + oy) * Wo + ox) * (static_cast<long long>(K * K) * C) +
+                                                         (ky * K + kx) * C + c8 * 8);
       }
+    }
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int t = 0; t < T * T; ++t) {
+      float f[8];
+      unpack8(v[t], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
     }
     if (gate) {
       float g[8];
-      unpack8(*reinterpret_cast<const uint4*>(gate + i * 8), g);
+      unpack8(gv, g);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) a[j] = g[j] > 0.f ? a[j] : 0.f;
+      for (int j = 0; j < 8; ++j) acc[j] = g[j] > 0.f ? acc[j] : 0.f;
     }
     if (add) {
       float g[8];
-      unpack8(*reinterpret_cast<const uint4*>(add + i * 8), g);
+      unpack8(av, g);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) a[j] += g[j] * add_f;
+      for (int j = 0; j < 8; ++j) acc[j] += g[j] * add_f;
     }
-    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(a);
+    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(acc);
   }
 }
 
@@ -142,29 +165,44 @@ __global__ void __launch_bounds__(256) e4_bn_sums_kernel(const h16* __restrict__
     rs[j] = BWD ? stat[C + chunk * 8 + j] : 0.f;
   }
   if (rl < rows) {
-    for (long long m = blockIdx.x * static_cast<long long>(rows) + rl; m < M; m += static_cast<long long>(gridDim.x) * rows) {
-      float f[8];
-      unpack8(*reinterpret_cast<const uint4*>(x + m * C + chunk * 8), f);
-      if (BWD) {
-        float d[8];
-        unpack8(*reinterpret_cast<const uint4*>(dy + m * C + chunk * 8), d);
-        if (out) {
-          float o[8];
-          unpack8(*reinterpret_cast<const uint4*>(out + m * C + chunk * 8), o);
+    // four rows per iteration: 4 (forward) or 12 (backward) independent 16-byte loads in flight per thread
+    const long long stride = static_cast<long long>(gridDim.x) * rows;
+    for (long long m0 = blockIdx.x * static_cast<long long>(rows) + rl; m0 < M; m0 += 4 * stride) {
+      uint4 xv[4], dv[4], ov[4];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) d[j] = o[j] > 0.f ? d[j] : 0.f;
-        }
+      for (int u = 0; u < 4; ++u) {
+        const long long m = m0 + u * stride;
+        const bool ok = m < M;
+        xv[u] = dv[u] = ov[u] = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) xv[u] = *reinterpret_cast<const uint4*>(x + m * C + chunk * 8);
+        if (BWD && ok) dv[u] = *reinterpret_cast<const uint4*>(dy + m * C + chunk * 8);
+        if (BWD && ok && out) ov[u] = *reinterpret_cast<const uint4*>(out + m * C + chunk * 8);
+      }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          s[j] += d[j];
-          q[j] += d[j] * (f[j] - mu[j]) * rs[j];
-          mx = fmaxf(mx, fabsf(d[j]));
-        }
-      } else {
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8(xv[u], f);
+        if (BWD) {
+          float d[8];
+          unpack8(dv[u], d);
+          if (out) {
+            float o[8];
+            unpack8(ov[u], o);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          s[j] += f[j];
-          q[j] += f[j] * f[j];
+            for (int j = 0; j < 8; ++j) d[j] = o[j] > 0.f ? d[j] : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s[j] += d[j];
+            q[j] += d[j] * (f[j] - mu[j]) * rs[j];
+            mx = fmaxf(mx, fabsf(d[j]));
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s[j] += f[j];
+            q[j] += f[j] * f[j];
+          }
         }
       }
     }
@@ -220,19 +258,34 @@ __global__ void __launch_bounds__(256) e4_bn_apply_kernel(const h16* __restrict_
     sh[C + c] = beta[c] - mean * a;
   }
   __syncthreads();
+  // blockDim is a multiple of C / 8, so a thread stays on one 8-channel chunk: coefficients in registers, four vectors
+  // in flight per iteration
   const int cv = C / 8;
-  const long long total = M * cv;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c0 = static_cast<int>(i % cv) * 8;
-    float f[8];
-    unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
+  const long long total = M * cv, T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int c0 = static_cast<int>(threadIdx.x % cv) * 8;
+  float ca[8], cb[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float v = f[j] * sh[c0 + j] + sh[C + c0 + j];
-      f[j] = relu ? fmaxf(v, 0.f) : v;
+  for (int j = 0; j < 8; ++j) {
+    ca[j] = sh[c0 + j];
+    cb[j] = sh[C + c0 + j];
+  }
+  for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < total; i0 += 4 * T) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i0 + u * T < total) v[u] = *reinterpret_cast<const uint4*>(x + (i0 + u * T) * 8);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (i0 + u * T >= total) break;
+      float f[8];
+      unpack8(v[u], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float w = f[j] * ca[j] + cb[j];
+        f[j] = relu ? fmaxf(w, 0.f) : w;
+      }
+      *reinterpret_cast<uint4*>(y + (i0 + u * T) * 8) = pack8(f);
     }
-    *reinterpret_cast<uint4*>(y + i * 8) = pack8(f);
   }
 }
 
@@ -286,26 +339,48 @@ __global__ void __launch_bounds__(256) e4_bn_bwd_apply_kernel(const h16* __restr
     gs_out[1] = gs_in[1] / r;
   }
   const int cv = C / 8;
-  const long long total = M * cv;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c0 = static_cast<int>(i % cv) * 8;
-    float f[8], d[8];
-    unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
-    unpack8(*reinterpret_cast<const uint4*>(dy + i * 8), d);
-    if (out) {
-      float o[8];
-      unpack8(*reinterpret_cast<const uint4*>(out + i * 8), o);
+  const long long total = M * cv, T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int c0 = static_cast<int>(threadIdx.x % cv) * 8;      // blockDim is a multiple of C / 8: one chunk per thread
+  float mu[8], ga[8], k1[8], k2[8], rs[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) d[j] = o[j] > 0.f ? d[j] : 0.f;
+  for (int j = 0; j < 8; ++j) {
+    mu[j] = sh[c0 + j];
+    rs[j] = sh[C + c0 + j];
+    ga[j] = r * gamma[c0 + j] * rs[j];
+    k1[j] = sh[2 * C + c0 + j];
+    k2[j] = sh[3 * C + c0 + j];
+  }
+  for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < total; i0 += 2 * T) {
+    uint4 xv[2], dv[2], ov[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long long i = i0 + u * T;
+      if (i < total) {
+        xv[u] = *reinterpret_cast<const uint4*>(x + i * 8);
+        dv[u] = *reinterpret_cast<const uint4*>(dy + i * 8);
+        if (out) ov[u] = *reinterpret_cast<const uint4*>(out + i * 8);
+      }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = c0 + j;
-      const float xh = (f[j] - sh[c]) * sh[C + c];
-      f[j] = r * gamma[c] * sh[C + c] * (d[j] - sh[2 * C + c] - xh * sh[3 * C + c]);
+    for (int u = 0; u < 2; ++u) {
+      const long long i = i0 + u * T;
+      if (i >= total) break;
+      float f[8], d[8];
+      unpack8(xv[u], f);
+      unpack8(dv[u], d);
+      if (out) {
+        float o[8];
+        unpack8(ov[u], o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] = o[j] > 0.f ? d[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xh = (f[j] - mu[j]) * rs[j];
+        f[j] = ga[j] * (d[j] - k1[j] - xh * k2[j]);
+      }
+      *reinterpret_cast<uint4*>(dx + i * 8) = pack8(f);
     }
-    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(f);
   }
 }
 
@@ -324,42 +399,52 @@ __global__ void e4_flatten_kernel(const h16* __restrict__ in, h16* __restrict__ 
   }
 }
 
-// grad_ref[co][ci][tap] += stage[co][tap * C + ci]; stage = 0     (tap-major weight-gradient staging -> reference layout)
-__global__ void e4_wgrad_finalize_kernel(float* __restrict__ stage, float* __restrict__ grad, int Cout, int C, int KK) {
+// grad_ref[co][ci][tap] += stage[co][tap * C + ci]     (tap-major weight-gradient staging -> reference layout); one launch
+// for all im2col convolutions of the backward (blockIdx.y = entry)
+__global__ void __launch_bounds__(256) e4_wgrad_finalize_kernel(E4Finalize f) {
   pdl_enter();
-  const long long total = static_cast<long long>(Cout) * C * KK;
+  const int e = blockIdx.y;
+  const float* __restrict__ stage = f.stage[e];
+  float* __restrict__ grad = f.grad[e];
+  const int C = f.C, KK = f.KK[e];
+  const long long total = static_cast<long long>(f.Cout) * C * KK;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int ci = static_cast<int>(i % C);
     const int tap = static_cast<int>((i / C) % KK);
     const long long co = i / (static_cast<long long>(C) * KK);
     grad[(co * C + ci) * KK + tap] += stage[i];
-    stage[i] = 0.f;
   }
 }
 
 }  // namespace
 
 int launch_e4_im2col(const h16* x, h16* cols, int B, int H, int W, int C, int k, int stride, int pad, cudaStream_t s) {
-  if (C & 7) return static_cast<int>(cudaErrorInvalidValue);
+  if ((C & 7) || (k != 3 && k != 4)) return static_cast<int>(cudaErrorInvalidValue);
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
-  launch_k(e4_im2col_kernel, e4_grid(static_cast<long long>(B) * Ho * Wo * k * k * (C / 8), 256), 256, 0, s, x, cols, B, H, W, C, k,
-           stride, pad, Ho, Wo);
+  const int grid = e4_grid(static_cast<long long>(B) * Ho * Wo * k * (C / 8), 256);
+  if (k == 4) launch_k(e4_im2col_kernel<4>, grid, 256, 0, s, x, cols, B, H, W, C, stride, pad, Ho, Wo);
+  else launch_k(e4_im2col_kernel<3>, grid, 256, 0, s, x, cols, B, H, W, C, stride, pad, Ho, Wo);
   return static_cast<int>(cudaGetLastError());
 }
 int launch_e4_im2col_image(const float* x, h16* cols, int B, int Cin, int H, int W, int k, int stride, int pad, cudaStream_t s) {
-  if (Cin * k * k > 64) return static_cast<int>(cudaErrorInvalidValue);
+  if (k != 4 || Cin > 4) return static_cast<int>(cudaErrorInvalidValue);
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
-  launch_k(e4_im2col_image_kernel, e4_grid(static_cast<long long>(B) * Ho * Wo, 128), 128, 0, s, x, cols, B, Cin, H, W, k, stride, pad,
-           Ho, Wo);
+  launch_k(e4_im2col_image_kernel, e4_grid(static_cast<long long>(B) * Ho * Wo * 8, 256), 256, 0, s, x, cols, B, Cin, H, W, k, stride,
+           pad, Ho, Wo);
   return static_cast<int>(cudaGetLastError());
 }
 int launch_e4_col2im(const h16* dcols, h16* dx, const h16* gate, const h16* add, const float* add_from, const float* add_to,
                      int B, int H, int W, int C, int k, int stride, int pad, cudaStream_t s) {
   if (C & 7) return static_cast<int>(cudaErrorInvalidValue);
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
-  launch_k(e4_col2im_kernel, e4_grid(static_cast<long long>(B) * H * W * (C / 8), 256), 256, 0, s, dcols, dx, gate, add, add_from, add_to, B,
-           H, W, C, k, stride, pad, Ho, Wo);
+  const int grid = e4_grid(static_cast<long long>(B) * H * W * (C / 8), 256);
+  if (k == 4 && stride == 2)
+    launch_k(e4_col2im_kernel<4, 2>, grid, 256, 0, s, dcols, dx, gate, add, add_from, add_to, B, H, W, C, pad, Ho, Wo);
+  else if (k == 3 && stride == 1)
+    launch_k(e4_col2im_kernel<3, 1>, grid, 256, 0, s, dcols, dx, gate, add, add_from, add_to, B, H, W, C, pad, Ho, Wo);
+  else
+    return static_cast<int>(cudaErrorInvalidValue);
   return static_cast<int>(cudaGetLastError());
 }
 int launch_e4_bn_sums(const h16* x, const h16* dy, const h16* out, const float* stat, float* sums, long long M, int C, int bwd,
@@ -367,7 +452,7 @@ int launch_e4_bn_sums(const h16* x, const h16* dy, const h16* out, const float* 
   if ((C & 7) || C > 2048 || 256 % (C / 8) != 0) return static_cast<int>(cudaErrorInvalidValue);
   const int rows = 256 / (C / 8);
   const size_t smem = static_cast<size_t>(rows) * 2 * C * sizeof(float);
-  const int grid = e4_grid(M, rows * 4, 148 * 4);
+  const int grid = e4_grid(M, rows * 4, 148 * 6);
   if (bwd) launch_k(e4_bn_sums_kernel<true>, grid, 256, smem, s, x, dy, out, stat, sums, M, C);
   else launch_k(e4_bn_sums_kernel<false>, grid, 256, smem, s, x, dy, out, stat, sums, M, C);
   return static_cast<int>(cudaGetLastError());
@@ -389,8 +474,12 @@ int launch_e4_flatten(const h16* in, h16* out, int B, int HW, int C, int to_flat
   launch_k(e4_flatten_kernel, e4_grid(static_cast<long long>(B) * HW * C, 256), 256, 0, s, in, out, B, HW, C, to_flat);
   return static_cast<int>(cudaGetLastError());
 }
-int launch_e4_wgrad_finalize(float* stage, float* grad, int Cout, int C, int KK, cudaStream_t s) {
-  launch_k(e4_wgrad_finalize_kernel, e4_grid(static_cast<long long>(Cout) * C * KK, 256), 256, 0, s, stage, grad, Cout, C, KK);
+int launch_e4_wgrad_finalize(const E4Finalize& f, cudaStream_t s) {
+  if (f.n <= 0) return 0;
+  int kk = 0;
+  for (int e = 0; e < f.n; ++e) kk = f.KK[e] > kk ? f.KK[e] : kk;
+  dim3 grid(e4_grid(static_cast<long long>(f.Cout) * f.C * kk, 256, 148 * 4), f.n);
+  launch_k(e4_wgrad_finalize_kernel, grid, 256, 0, s, f);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -217,6 +217,12 @@ int launch_e4_bn_bwd_apply(const h16* x, const h16* dy, const h16* out, const fl
                            float* dgamma, float* dbeta, const float* gs_in, float* gs_out, h16* dx, long long M, int C,
                            int training, cudaStream_t s);
 int launch_e4_flatten(const h16* in, h16* out, int B, int HW, int C, int to_flat, cudaStream_t s);
-int launch_e4_wgrad_finalize(float* stage, float* grad, int Cout, int C, int KK, cudaStream_t s);
+struct E4Finalize {            // the tap-major staging matrices of one backward and the reference-layout gradients they fold into
+  float* stage[8];
+  float* grad[8];
+  int KK[8];
+  int Cout, C, n;
+};
+int launch_e4_wgrad_finalize(const E4Finalize& f, cudaStream_t s);
 
 }  // namespace edb

@@ -288,3 +288,79 @@ class DenoiserTrainer:
             out[name] = self.opt.ema[off:off + p.numel()].view_as(p)
             off += p.numel()
         return out
+
+
+class EncDiffTrainer:
+    """The complete EncDiff training step FROM IMAGES on this package's kernels: what ``LatentDiffusion.shared_step`` does
+    with ``cond_stage_trainable`` (ddpm_enc.py:1018-1021 -> get_input :774-866: frozen ``encode_first_stage`` and
+    ``scale_factor *`` :662-669; forward :1040-1053: ``t = randint``, ``c = get_learned_conditioning(images)``; p_losses
+    :1183-1213) followed by the optimiser of ``configure_optimizers`` (:1598-1604: ONE AdamW over the UNet's and the concept
+    encoder's parameters; LitEma shadows the UNet only, :95-97).
+
+      first_stage   encdiff_b200.VQEncoder   (frozen, no gradient)
+      cond_stage    encdiff_b200.Encoder4    (trainable: encdiff_enc4_forward / backward + ConceptMLP)
+      unet          encdiff_b200.UNetModel   (DenoiserTrainer: captured forward + backward, AdamW + EMA + re-pack)
+
+    Data parallel: the UNet's flat gradient bucket and the concept encoder's (1.4 M elements) are summed over the ranks by one
+    NCCL all-reduce each; BatchNorm uses per-rank batch statistics (no SyncBatchNorm) and, like DistributedDataParallel with
+    its default ``broadcast_buffers=True``, every forward starts from rank 0's running statistics."""
+
+    def __init__(self, first_stage, cond_stage, unet: UNetModel, lr=1e-4, weight_decay=0.01, use_ema=True, scale_factor=1.0,
+                 process_group=None, broadcast_buffers=True, **denoiser_kw):
+        self.first_stage, self.cond_stage = first_stage, cond_stage
+        self.scale_factor = float(scale_factor)
+        self.denoiser = DenoiserTrainer(unet, lr=lr, weight_decay=weight_decay, use_ema=use_ema, process_group=process_group,
+                                        **denoiser_kw)
+        self.pg, self.world = process_group, self.denoiser.world
+        self.cond_params = [p for p in cond_stage.parameters() if p.requires_grad]
+        self.cond_opt = FlatAdamWEMA(self.cond_params, lr, weight_decay, use_ema=False)
+        if self.world > 1:
+            from . import parallel
+            src = torch.distributed.get_global_rank(process_group, 0) if process_group is not None else 0
+            parallel.broadcast_(self.cond_opt.flat, src, process_group)
+            self._src = src
+        self._buffers = [b for b in cond_stage.buffers()] if (self.world > 1 and broadcast_buffers) else []
+        self.num_timesteps = self.denoiser.num_timesteps
+
+    def _sync_buffers(self):
+        """DDP's per-forward buffer broadcast (torch/nn/parallel/distributed.py, _sync_buffers): one coalesced broadcast."""
+        if not self._buffers:
+            return
+        pg = self.pg if self.pg is not None else torch.distributed.group.WORLD
+        try:
+            torch.distributed._broadcast_coalesced(pg, self._buffers, 25 * 1024 * 1024, self._src)
+        except (AttributeError, TypeError, RuntimeError):
+            for b in self._buffers:
+                torch.distributed.broadcast(b, self._src, group=self.pg)
+
+    @property
+    def unet(self):
+        return self.denoiser.unet
+
+    def step(self, images, t=None, noise=None, lr: Optional[float] = None):
+        """One optimisation step on ``images`` [B, C, H, W] (device, values in [-1, 1]); ``t`` / ``noise`` default to the
+        draws of LatentDiffusion.forward / p_losses (torch's CUDA generator).  Returns the loss as a [1] device tensor."""
+        if not images.is_cuda:
+            raise RuntimeError("encdiff_b200.EncDiffTrainer.step needs CUDA tensors (no CPU fallback)")
+        with torch.no_grad():
+            z = self.first_stage.encode(images)
+            if self.scale_factor != 1.0:
+                z = z * self.scale_factor
+        self._sync_buffers()
+        cond = self.cond_stage(images)
+        B = images.shape[0]
+        if t is None:
+            t = torch.randint(0, self.num_timesteps, (B,), device=images.device)
+        if noise is None:
+            noise = torch.randn_like(z)
+        loss, dcond = self.denoiser.step(z, cond.detach(), t, noise, lr)
+        for p in self.cond_params:
+            p.grad = None
+        cond.backward(dcond)
+        flat = torch.cat([p.grad.reshape(-1) for p in self.cond_params])
+        if self.world > 1:
+            torch.distributed.all_reduce(flat, group=self.pg)
+        self.cond_opt.write_hyper(lr)
+        self.cond_opt.launch(flat, grad_scale=1.0 / self.world)
+        return loss
+

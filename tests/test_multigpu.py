@@ -65,8 +65,33 @@ def _worker(rank, world, port, out):
     shape = (cfg.in_channels, cfg.image_size, cfg.image_size)
     sharded = sample_swap(DDIMSampler(host), tokens, None, ddim_steps=S, eta=0., shape=shape, x_T=xT,
                           reference_rng=False)
+    # ---- the full step from images (EncDiffTrainer): different initial weights and different images on each rank; the
+    # constructor's broadcast and the two gradient all-reduces must leave the replicas bit-identical ----------------------
+    from encdiff_b200 import Encoder4, VQEncoder
+    from encdiff_b200.train import EncDiffTrainer
+    cfg_s = CONFIGS["shapes3d"]
+    torch.manual_seed(7)
+    vq = VQEncoder(embed_dim=3, ddconfig=dict(double_z=False, z_channels=3, resolution=64, in_channels=3, out_ch=3, ch=32,
+                                              ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[], dropout=0.0)).to(dev)
+    torch.manual_seed(100 + r)
+    enc = Encoder4(d=128, context_dim=cfg_s.context_dim, latent_unit=cfg_s.latent_unit).to(dev).train()
+    unet = _model(cfg_s, dev).train()
+    with torch.no_grad():
+        for q in unet.parameters():
+            q.add_(0.01 * r)
+    full = EncDiffTrainer(vq, enc, unet, lr=1e-3, use_cuda_graph=False)
+    start = full.cond_opt.flat.clone()
+    gi = torch.Generator().manual_seed(500 + r)
+    for _ in range(2):
+        full.step((torch.rand(4, 3, 64, 64, generator=gi) * 2 - 1).to(dev))
+    mine = torch.cat([full.cond_opt.flat, full.denoiser.opt.flat])
+    both = [torch.empty_like(mine) for _ in range(w)]
+    torch.distributed.all_gather(both, mine)
+    replicas_equal = bool(torch.equal(both[0], both[1]))
+    moved = float((full.cond_opt.flat - start).abs().max())
     if r == 0:
-        torch.save({"grad": grad, "loss": loss_mean, "swap": sharded.cpu()}, out)
+        torch.save({"grad": grad, "loss": loss_mean, "swap": sharded.cpu(), "replicas_equal": replicas_equal,
+                    "moved": moved}, out)
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 
@@ -99,3 +124,5 @@ def test_dp_step_and_sharded_swap_nccl_world2(cuda_device, tmp_path):
     whole = sample_swap(DDIMSampler(host), tokens, None, ddim_steps=S, eta=0.,
                         shape=(cfg.in_channels, cfg.image_size, cfg.image_size), x_T=xT, reference_rng=False)
     assert torch.equal(got["swap"], whole.cpu())       # a sample does not depend on its batch neighbours: bit-identical
+    print(f"EncDiffTrainer dp2: replicas identical after 2 steps: {got['replicas_equal']}; concept encoder moved {got['moved']:.2e}")
+    assert got["replicas_equal"] and got["moved"] > 0
