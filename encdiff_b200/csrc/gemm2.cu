@@ -206,9 +206,13 @@ __global__ void __launch_bounds__(192, OCC) sgemm2_kernel(const __grid_constant_
       uint4 rres[8];
       const bool has_res = p.res && row_ok;
       const h16* res_row = reinterpret_cast<const h16*>(p.res) + row * p.ldres + n_tile * BN;
+      // (N = 32, the first stage's level-0 layers, runs as half of a 64-wide tile: the weight rows beyond N are the operand's
+      // zero padding, the TMA store clips the columns beyond N, and the residual row is only read up to N)
+      const int res_vecs = min(8, (p.N - n_tile * BN) >> 3);
       if (has_res) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) rres[j] = __ldg(reinterpret_cast<const uint4*>(res_row + 8 * j));
+        for (int j = 0; j < 8; ++j)
+          rres[j] = j < res_vecs ? __ldg(reinterpret_cast<const uint4*>(res_row + 8 * j)) : make_uint4(0u, 0u, 0u, 0u);
       }
       mbar_wait(&tfull[acc], aph);
       tc_fence_after();
@@ -293,6 +297,7 @@ static int launch_sgemm2_t(const Sgemm2Params& p, int num_sms, cudaStream_t stre
 // per FLOP but leaves SMs idle when it produces fewer tiles than SMs.  cost = rounds * (k-blocks * stage bytes / fill
 // rate + epilogue panels); constants from the in-graph timings in profiles/ (about 90 GB/s per SM, 0.4 us per panel).
 int sgemm2_pick_bn(int m_tiles, int N, int num_sms, int nkb) {
+  if (N == 32) return 64;            // half-used 64-wide tile (see the epilogue); these layers are bandwidth-bound
   if (N % 64 != 0) return 0;
   int best = 64;
   float best_cost = 1e30f;

@@ -106,7 +106,8 @@ int make_out_tmap(CUtensorMap* m, const void* base, long long M, int N, int ld) 
     set_last_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
     return EDB_ERR_CUDA;
   }
-  EDB_REQUIRE((N % 64) == 0 && (ld % 8) == 0, "output map: N must be a multiple of 64 and ld of 8");
+  // N = 32: the 64-wide store box is clipped at the tensor edge (gemm2.cu, half-used tile)
+  EDB_REQUIRE(((N % 64) == 0 || N == 32) && (ld % 8) == 0, "output map: N must be a multiple of 64 (or 32) and ld of 8");
   EDB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "output base must be 16-byte aligned");
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(N), static_cast<cuuint64_t>(M)};
   cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
