@@ -65,6 +65,24 @@ def _worker(rank, world, port, out):
     shape = (cfg.in_channels, cfg.image_size, cfg.image_size)
     sharded = sample_swap(DDIMSampler(host), tokens, None, ddim_steps=S, eta=0., shape=shape, x_T=xT,
                           reference_rng=False)
+    # ---- torch DistributedDataParallel around the drop-in module (the reference's Lightning 'ddp' strategy, main_val.py:
+    # 656-660, find_unused_parameters as Lightning sets it): every parameter's AccumulateGrad hook must fire so the bucket
+    # reducer sees all tensors; two iterations, the second one is where a missing hook raises -------------------------
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    md = _model(cfg, dev).train()
+    ddp = DDP(md, device_ids=[local], find_unused_parameters=True)
+    gw = torch.Generator().manual_seed(77)
+    wgt = torch.randn(x.shape, generator=gw)
+    for _ in range(2):
+        ddp.zero_grad(set_to_none=True)
+        out_d = ddp(x[b:e].to(dev), t[b:e].to(dev), context=[ctx[b:e].to(dev)])
+        (out_d * wgt[b:e].to(dev)).sum().backward()
+    g_ddp = torch.cat([q.grad.flatten() for q in md.parameters()])
+    both_g = [torch.empty_like(g_ddp) for _ in range(w)]
+    torch.distributed.all_gather(both_g, g_ddp)
+    ddp_equal = bool(torch.equal(both_g[0], both_g[1]))
+    g_ddp = g_ddp.cpu()
+    del ddp
     # ---- the full step from images (EncDiffTrainer): different initial weights and different images on each rank; the
     # constructor's broadcast and the two gradient all-reduces must leave the replicas bit-identical ----------------------
     from encdiff_b200 import Encoder4, VQEncoder
@@ -91,7 +109,7 @@ def _worker(rank, world, port, out):
     moved = float((full.cond_opt.flat - start).abs().max())
     if r == 0:
         torch.save({"grad": grad, "loss": loss_mean, "swap": sharded.cpu(), "replicas_equal": replicas_equal,
-                    "moved": moved}, out)
+                    "moved": moved, "ddp_grad": g_ddp, "ddp_equal": ddp_equal}, out)
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 
@@ -124,5 +142,14 @@ def test_dp_step_and_sharded_swap_nccl_world2(cuda_device, tmp_path):
     whole = sample_swap(DDIMSampler(host), tokens, None, ddim_steps=S, eta=0.,
                         shape=(cfg.in_channels, cfg.image_size, cfg.image_size), x_T=xT, reference_rng=False)
     assert torch.equal(got["swap"], whole.cpu())       # a sample does not depend on its batch neighbours: bit-identical
+    # DDP averages the ranks' gradients: 2 x that == the gradient of the whole-batch sum loss on one GPU
+    md = _model(cfg, dev).train()
+    gw = torch.Generator().manual_seed(77)
+    wgt = torch.randn(x.shape, generator=gw).to(dev)
+    (md(x.to(dev), t.to(dev), context=[ctx.to(dev)]) * wgt).sum().backward()
+    want_d = torch.cat([q.grad.flatten() for q in md.parameters()]).cpu()
+    err_d = ((2 * got["ddp_grad"] - want_d).abs().max() / want_d.abs().max()).item()
+    print(f"torch DDP around UNetModel: ranks hold identical gradients: {got['ddp_equal']}; vs single-GPU whole batch {err_d:.2e}")
+    assert got["ddp_equal"] and err_d < 5e-3
     print(f"EncDiffTrainer dp2: replicas identical after 2 steps: {got['replicas_equal']}; concept encoder moved {got['moved']:.2e}")
     assert got["replicas_equal"] and got["moved"] > 0
