@@ -163,9 +163,12 @@ def run_reference(args):
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------------
 def measured_traffic():
-    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/r01_sgemm2_dram.json, written
-    by tools/ncu_dram_summary.py from `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`); None if absent."""
-    p = os.path.join(ROOT, "profiles", "r01_sgemm2_dram.json")
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/r02_sgemm2_dram.json, written
+    by tools/ncu_dram_summary.py from `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum` of one step of the final
+    round-2 build; the round-1 file as a fallback); None if absent."""
+    p = os.path.join(ROOT, "profiles", "r02_sgemm2_dram.json")
+    if not os.path.exists(p):
+        p = os.path.join(ROOT, "profiles", "r01_sgemm2_dram.json")
     if not os.path.exists(p):
         return None, None
     d = json.load(open(p))

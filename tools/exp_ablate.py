@@ -33,7 +33,7 @@ FAMILIES = [
     ("cross_attn_fwd", "cross_attn_fwd_mma_kernel"),
     ("cross_attn_bwd", "cross_attn_bwd_mma_kernel"),
     ("cross_attn_bwd_proj", "cross_attn_bwd_proj_group_kernel"),
-    ("adamw", "adamw_dev_kernel"),
+    ("adamw", "adamw_dev"),
     ("pack", "pack_kernel"),
     ("wgrad_finalize", "wgrad_finalize_kernel"),
     ("all norms+geglu", "gn_fwd_kernel,gn_bwd_kernel,ln_fwd_kernel,ln_bwd_kernel,geglu_fwd_kernel,geglu_bwd_kernel"),
