@@ -33,23 +33,34 @@ __device__ __forceinline__ float vquad_sum(float v) {
 }
 
 // cols[(b, oy, ox)][tap * C64 + c] = x[b][2 oy + ky][2 ox + kx][c]  (0 beyond the bottom / right edge and for c >= C)
-__global__ void vq_down_im2col_kernel(const h16* __restrict__ x, h16* __restrict__ cols, int B, int H, int C, int C64) {
+// thread = (output pixel, kernel row, 8-channel chunk): the row's three taps are three independent 16-byte loads in flight
+__global__ void __launch_bounds__(256) vq_down_im2col_kernel(const h16* __restrict__ x, h16* __restrict__ cols, int B, int H,
+                                                             int C, int C64) {
   pdl_enter();
   const int Ho = H / 2, cv = C64 / 8;
-  const long long total = static_cast<long long>(B) * Ho * Ho * 9 * cv;
+  const long long total = static_cast<long long>(B) * Ho * Ho * 3 * cv;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c8 = static_cast<int>(i % cv);
     long long r = i / cv;
-    const int tap = static_cast<int>(r % 9);
-    r /= 9;
+    const int ky = static_cast<int>(r % 3);
+    r /= 3;                                      // output pixel (b, oy, ox)
     const int ox = static_cast<int>(r % Ho);
-    r /= Ho;
-    const int oy = static_cast<int>(r % Ho), b = static_cast<int>(r / Ho);
-    const int y = 2 * oy + tap / 3, xx = 2 * ox + tap % 3;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (y < H && xx < H && c8 * 8 < C) v = *reinterpret_cast<const uint4*>(x + ((static_cast<long long>(b) * H + y) * H + xx) * C + c8 * 8);
-    *reinterpret_cast<uint4*>(cols + i * 8) = v;
+    const long long bo = r / Ho;
+    const int oy = static_cast<int>(bo % Ho);
+    const long long b = bo / Ho;
+    const int y = 2 * oy + ky, x0 = 2 * ox;
+    const bool ok = y < H && c8 * 8 < C;
+    const h16* src = x + ((b * H + y) * H + x0) * C + c8 * 8;
+    uint4 v[3];
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      v[kx] = make_uint4(0u, 0u, 0u, 0u);
+      if (ok && x0 + kx < H) v[kx] = *reinterpret_cast<const uint4*>(src + static_cast<long long>(kx) * C);
+    }
+    h16* dst = cols + (r * 9 + ky * 3) * C64 + c8 * 8;
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) *reinterpret_cast<uint4*>(dst + static_cast<long long>(kx) * C64) = v[kx];
   }
 }
 
@@ -237,7 +248,7 @@ inline int vq_grid(long long n, int threads) {
 int launch_vq_down_im2col(const h16* x, h16* cols, int B, int H, int C, cudaStream_t s) {
   const int C64 = (C + 63) / 64 * 64;
   if ((H & 1) || (C & 7)) return static_cast<int>(cudaErrorInvalidValue);
-  const long long total = static_cast<long long>(B) * (H / 2) * (H / 2) * 9 * (C64 / 8);
+  const long long total = static_cast<long long>(B) * (H / 2) * (H / 2) * 3 * (C64 / 8);
   launch_k(vq_down_im2col_kernel, vq_grid(total, 256), 256, 0, s, x, cols, B, H, C, C64);
   return static_cast<int>(cudaGetLastError());
 }
