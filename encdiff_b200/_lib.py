@@ -57,6 +57,8 @@ PROTOTYPES = {
     "encdiff_unet_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_void_p]),
     "encdiff_unet_backward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "encdiff_unet_set_grad_split": (c_int, [c_void_p, c_void_p]),
+    "encdiff_unet_backward_tail": (c_int, [c_void_p, c_void_p]),
     "encdiff_vqenc_create": (c_int, [c_void_p, C.POINTER(c_void_p)]),
     "encdiff_vqenc_workspace_bytes": (c_ll, [c_void_p, c_int]),
     "encdiff_vqenc_forward": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -232,6 +232,20 @@ extern "C" int encdiff_unet_backward(encdiff_unet* h, int batch, const float* do
   return unet_backward(&h->u, batch, dout, ctx, dx, dctx, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int encdiff_unet_set_grad_split(encdiff_unet* h, const float* split) {
+  EDB_REQUIRE(h, "unet_set_grad_split: null handle");
+  if (h->u.grad_split != split) {
+    h->u.grad_split = split;
+    h->u.fin_dirty = true;           // the next backward re-partitions its deferred-gradient tables
+  }
+  return EDB_OK;
+}
+
+extern "C" int encdiff_unet_backward_tail(encdiff_unet* h, void* stream) {
+  EDB_REQUIRE(h, "unet_backward_tail: null handle");
+  return unet_backward_tail(&h->u, static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int encdiff_unet_profile(encdiff_unet* h, int enable) {
   EDB_REQUIRE(h, "unet_profile: null handle");
   h->u.prof = enable != 0;

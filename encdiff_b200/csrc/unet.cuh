@@ -154,6 +154,13 @@ struct UNet {
   bool group_wgrad = true;    // ENCDIFF_NO_WGRAD_GROUP: launch per layer (side stream) instead
   std::vector<Wgrad2Params> wg_host;
   std::vector<int> wg_prefix;
+  std::vector<const float*> wg_dst;   // reference-layout gradient tensor each recorded problem accumulates into
+  // Gradient split for data parallelism (encdiff_unet_set_grad_split): problems / finalize entries whose gradient lies at or
+  // above `grad_split` in the caller's flat bucket form group A, run by unet_backward(); the rest form group B, run by
+  // unet_backward_tail(), so the caller can all-reduce the bucket's tail while group B is still being computed.
+  const float* grad_split = nullptr;
+  int wg_nA = 0, wg_totalA = 0, wg_totalB = 0, fin_nA = 0;
+  long long fin_totalA = 0, fin_totalB = 0;
   Wgrad2Params* wg_dev = nullptr;
   int* wg_prefix_dev = nullptr;
   int wg_total = 0;
@@ -197,6 +204,7 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
                  const float* ctx, float* out, float* xt, cudaStream_t s);
 int unet_backward(UNet* u, int B, const float* dout, const float* ctx, float* dx, float* dctx, cudaStream_t s);
 // fp32 validation forward (fp32_ref.cu): fp32 tensors, CUDA-core FMA contractions, reference-layout master parameters
+int unet_backward_tail(UNet* u, cudaStream_t s);
 int vqenc_build(UNet* u, const encdiff_vqenc_config* cfg);
 int vqdec_build(UNet* u, const encdiff_vqdec_config* cfg);
 int enc4_build(UNet* u, const encdiff_enc4_config* cfg);

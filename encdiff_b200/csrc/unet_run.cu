@@ -64,7 +64,7 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
     u->fin_dirty = true;
     u->wg_dev = reinterpret_cast<Wgrad2Params*>(a.take<char>(UNet::kWgCap * sizeof(Wgrad2Params) + 64));
     u->wg_dev = reinterpret_cast<Wgrad2Params*>((reinterpret_cast<uintptr_t>(u->wg_dev) + 63) & ~uintptr_t(63));
-    u->wg_prefix_dev = reinterpret_cast<int*>(a.take<char>((UNet::kWgCap + 1) * sizeof(int)));
+    u->wg_prefix_dev = reinterpret_cast<int*>(a.take<char>((UNet::kWgCap + 2) * sizeof(int)));
     u->cp_dev = reinterpret_cast<CrossProjEntry*>(a.take<char>(64 * sizeof(CrossProjEntry)));
     u->gs = a.take<float>(2);
     u->dfilm = a.take<h16>(static_cast<size_t>(B) * u->film_cols);
@@ -484,6 +484,7 @@ struct Exec {
         u->wg_prefix.push_back(u->wg_total);
         u->wg_total += wgrad2_prepare_group(&q, 16);
         u->wg_host.push_back(q);
+        u->wg_dst.push_back(out);
         return;
       }
       fail(launch_wgrad2(q, device_sm_count(), fork_side()), "wgrad");

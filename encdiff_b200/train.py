@@ -11,6 +11,7 @@ optimiser update are captured once as CUDA graphs and replayed; the only per-ste
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import numpy as np
@@ -98,7 +99,8 @@ class DenoiserTrainer:
     """p_losses forward/backward + gradient all-reduce + AdamW/EMA for one ``encdiff_b200.UNetModel``."""
 
     def __init__(self, unet: UNetModel, lr=1e-4, weight_decay=0.01, use_ema=True, timesteps=1000,
-                 linear_start=0.0015, linear_end=0.0155, process_group=None, use_cuda_graph=True, allreduce_chunks=1):
+                 linear_start=0.0015, linear_end=0.0155, process_group=None, use_cuda_graph=True, allreduce_chunks=1,
+                 overlap_allreduce=True):
         self.unet = unet
         dev = next(unet.parameters()).device
         if dev.type != "cuda":
@@ -129,6 +131,11 @@ class DenoiserTrainer:
         # (profiles/experiments/r01_allreduce_chunks.txt): 1 chunk 10.63 ms, 2: 10.64, 4: 10.69, 8: 10.81 -- the optimiser
         # kernel and the NCCL kernel compete for the same HBM, so the default stays 1
         self.allreduce_chunks = max(1, int(allreduce_chunks))
+        # world > 1: all-reduce the tail of the gradient bucket (the output blocks: complete first) on NCCL's stream while the
+        # deferred weight gradients of the rest are still being computed (encdiff_unet_set_grad_split / _backward_tail)
+        self.overlap_allreduce = (bool(overlap_allreduce) and self.world > 1 and self.allreduce_chunks == 1
+                                  and os.environ.get("ENCDIFF_NO_AR_OVERLAP") is None)
+        self._split = 0
         self._static = None
         self._bound_once = False
 
@@ -180,6 +187,35 @@ class DenoiserTrainer:
         _lib.check(lib.encdiff_unet_backward(u._h, B, deps.data_ptr(), st["cond"].data_ptr(), 0,
                                              st["dcond"].data_ptr(), _lib.current_stream()), "unet_backward")
 
+    def _bwd_tail(self, st):
+        """Group B of the deferred weight gradients (everything below the split of the bucket); enqueue-only."""
+        _lib.check(_lib.load().encdiff_unet_backward_tail(self.unet._h, _lib.current_stream()), "unet_backward_tail")
+
+    def _set_split(self):
+        """Split the flat bucket at the first parameter of the middle block (registration order = bucket order): both groups
+        of deferred gradients are launched after the activation-gradient chain, so any contiguous tail works; on two B200s
+        the step took 9.257 / 9.235 / 9.278 / 9.329 ms with the split at output_blocks / middle_block / input_blocks.9 /
+        input_blocks.8 (9.362 without overlap)."""
+        u = self.unet
+        off = 0
+        at = os.environ.get("ENCDIFF_AR_SPLIT_AT", "middle_block.")      # 70 % of the bucket in the overlapped part (measured best)
+        for name, p in u.named_parameters():
+            if name.startswith(at):
+                break
+            off += p.numel()
+        self._split = off if 0 < off < u._gflat.numel() else 0
+        ptr = u._gflat.data_ptr() + 4 * self._split if self._split else 0
+        _lib.check(_lib.load().encdiff_unet_set_grad_split(u._h, ptr), "unet_set_grad_split")
+
+    def _allreduce_overlapped(self, tail_fn):
+        """all-reduce(bucket[split:]) runs on NCCL's stream under `tail_fn` (group B's weight gradients), then the head."""
+        g = self.unet._gflat
+        wa = torch.distributed.all_reduce(g[self._split:], group=self.pg, async_op=True)
+        tail_fn()
+        wb = torch.distributed.all_reduce(g[:self._split], group=self.pg, async_op=True)
+        wa.wait()
+        wb.wait()
+
     def _opt(self, st):
         self.opt.advance()                      # device clock tick: inside the captured optimiser graph
         self.opt.launch(self.unet._gflat, 1.0 / self.world)
@@ -226,16 +262,22 @@ class DenoiserTrainer:
             u._bind(need_grads=True)
             u._prepare_grads()
             self._bound_once = True
+            if self.overlap_allreduce:
+                self._set_split()
         if not u._packed_valid:
             u.refresh_weights()
         prev = u.cache_packed_weights
         u.cache_packed_weights = True       # weights are re-packed right after each optimiser update instead
         try:
             chunked = self.world > 1 and self.allreduce_chunks > 1
+            split = self.overlap_allreduce and self._split > 0
             if not self.use_cuda_graph:
                 self._fwd_bwd(st)
                 if chunked:
                     self._allreduce_and_opt(st)
+                elif split:
+                    self._allreduce_overlapped(lambda: self._bwd_tail(st))
+                    self._opt(st)
                 else:
                     self._allreduce()
                     self._opt(st)
@@ -245,6 +287,9 @@ class DenoiserTrainer:
                     self._fwd_bwd(st)                       # eager warm-up (also a real step)
                     if chunked:
                         self._allreduce_and_opt(st)
+                    elif split:
+                        self._allreduce_overlapped(lambda: self._bwd_tail(st))
+                        self._opt(st)
                     else:
                         self._allreduce()
                         self._opt(st)
@@ -252,6 +297,10 @@ class DenoiserTrainer:
                     g_fb, g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g_fb):
                         self._fwd_bwd(st)
+                    if split:
+                        st["g_tail"] = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(st["g_tail"]):
+                            self._bwd_tail(st)
                     with torch.cuda.graph(g_opt):           # chunked mode: only the re-pack (AdamW is launched per chunk)
                         if chunked:
                             u.refresh_weights()
@@ -263,6 +312,9 @@ class DenoiserTrainer:
                     st["g_fb"].replay()
                     if chunked:
                         self._allreduce_and_opt(st)
+                    elif split:
+                        self._allreduce_overlapped(st["g_tail"].replay)
+                        st["g_opt"].replay()
                     else:
                         self._allreduce()
                         st["g_opt"].replay()

@@ -309,6 +309,8 @@ class UNetModel(nn.Module):
         dctx = torch.empty_like(cond)
         _lib.check(self._lib.encdiff_unet_backward(self._h, B, dout.data_ptr(), cond.data_ptr(), _lib.ptr(dx),
                                                    dctx.data_ptr(), _lib.current_stream()), "unet_backward")
+        # (a no-op unless a data-parallel DenoiserTrainer set a gradient split on this handle)
+        _lib.check(self._lib.encdiff_unet_backward_tail(self._h, _lib.current_stream()), "unet_backward_tail")
         # clones: AccumulateGrad may keep the tensor it is handed as param.grad, and the bucket is reused next backward
         parts = self._gflat.clone().split([v.numel() for v in self._grad_views])
         return dx, dctx, tuple(c.view_as(v) for c, v in zip(parts, self._grad_views))
@@ -396,6 +398,7 @@ class UNetModel(nn.Module):
                 self._gflat.zero_()
                 _lib.check(self._lib.encdiff_unet_backward(self._h, B, sd.data_ptr(), sc.data_ptr(), _lib.ptr(dx),
                                                            dctx.data_ptr(), _lib.current_stream()), "unet_backward")
+                _lib.check(self._lib.encdiff_unet_backward_tail(self._h, _lib.current_stream()), "unet_backward_tail")
             st.update(g=g, d=sd, c=sc, dx=dx, dctx=dctx)
         else:
             for p, v in zip(self._params(), self._grad_views):

@@ -173,6 +173,15 @@ int encdiff_unet_forward_fp32(encdiff_unet* h, int batch, const float* x, const 
  * dctx [B, latent_unit*context_dim] fp32 (overwritten); parameter gradients are accumulated into the bound tensors. */
 int encdiff_unet_backward(encdiff_unet* h, int batch, const float* dout, const float* ctx, float* dx, float* dctx,
                           void* stream);
+/* Data-parallel overlap (what DistributedDataParallel's bucketed all-reduce gives the reference, main_val.py:656-660).
+ * The weight gradients of a step only become complete in the deferred launches at the very end of the backward; with a split
+ * pointer into the caller's flat gradient bucket, encdiff_unet_backward() completes every gradient at or above `split`
+ * (group A: in registration order the bucket's tail, i.e. the output blocks, whose activation gradients are produced
+ * first) and leaves the rest to encdiff_unet_backward_tail(), so the caller can all-reduce [split, end) on another stream
+ * while group B is computed.  split = NULL (default): encdiff_unet_backward() does everything, the tail call is a no-op.
+ * Takes effect at the next backward (which rebuilds its tables: not capturable, run it eagerly once). */
+int encdiff_unet_set_grad_split(encdiff_unet* h, const float* split /*device*/);
+int encdiff_unet_backward_tail(encdiff_unet* h, void* stream);
 
 /* Live per-launch timing for bench.py's roofline figure: while enabled, forward/backward record one CUDA event after
  * every kernel launch on the launching stream.  profile_read synchronises on the last event, writes one text line
