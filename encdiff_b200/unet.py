@@ -253,7 +253,15 @@ class UNetModel(nn.Module):
         if ws is None or ws.device != dev:
             nbytes = self._lib.encdiff_unet_workspace_bytes(self._h, B, int(training))
             ws = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
-            self._ws = {key: ws}     # one live workspace: batch-size changes free the old one
+            # two live workspaces (most recently used): a training loop that samples now and then (train at B = 256,
+            # log_images at B = 128) keeps both instead of freeing and re-allocating 6 GB at every switch; a third
+            # shape evicts the older one
+            self._ws.pop(key, None)
+            while len(self._ws) >= 2:
+                self._ws.pop(next(iter(self._ws)))
+            self._ws[key] = ws
+        else:
+            self._ws[key] = self._ws.pop(key)        # most recently used last
         return ws
 
     def plan_key(self):
@@ -434,7 +442,7 @@ class UNetModel(nn.Module):
         ptr, c, h, w = C.c_void_p(), C.c_int(), C.c_int(), C.c_int()
         _lib.check(self._lib.encdiff_unet_debug_block(self._h, section, index, C.byref(ptr), C.byref(c), C.byref(h),
                                                       C.byref(w)), "debug_block")
-        (B, _training), ws = next(iter(self._ws.items()))
+        (B, _training), ws = list(self._ws.items())[-1]       # the workspace of the last forward
         off = ptr.value - ws.data_ptr()
         n = B * h.value * w.value * c.value
         t = ws[off:off + 2 * n].view(_lib.act_dtype()).view(B, h.value, w.value, c.value)

@@ -142,6 +142,20 @@ def test_backward_with_heavy_tailed_upstream_gradient(cuda_device, outlier):
     assert l2 <= 2e-2 and e_ctx <= TOL.grad
 
 
+
+def test_two_live_workspaces(cuda_device):
+    """A training shape and a sampling shape keep their workspaces side by side (no free / re-allocate at every switch);
+    a third shape evicts the least recently used one."""
+    cfg = CONFIGS["tiny"]
+    m, _ = make_model(cfg, cuda_device)
+    a = m._workspace(8, True, cuda_device)
+    b = m._workspace(4, False, cuda_device)
+    assert m._workspace(8, True, cuda_device) is a and m._workspace(4, False, cuda_device) is b and len(m._ws) == 2
+    m._workspace(8, True, cuda_device)
+    c = m._workspace(2, False, cuda_device)
+    assert set(m._ws) == {(8, True), (2, False)} and m._workspace(2, False, cuda_device) is c
+
+
 def test_init_anchors(cuda_device):
     """Reference initialisation anchors: zero-init head => eps == 0, first-step L1 ~ 0.798,
     37,469,635 parameters in 734 tensors, same names as the reference."""
