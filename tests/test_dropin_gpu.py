@@ -213,3 +213,52 @@ def test_ddim_decoded_images_vs_reference(pair, cuda_device):
     print(f"DDIM-{S} end to end vs reference: latent PSNR {p_lat:.1f} dB; decoded (no quantiser) {p_nq:.1f} dB; decoded "
           f"(quantised) {p_q:.1f} dB with {100 * same:.1f} % of the code indices equal")
     assert p_lat >= 40.0 and p_nq >= 40.0 and p_q >= 40.0 and same >= 0.99
+
+
+@needs_ref
+def test_both_targets_swapped_training_step_through_the_reference_seam(pair, cuda_device):
+    """``unet_config.target: encdiff_b200.UNetModel`` AND ``cond_stage_config.target: encdiff_b200.Encoder4`` in the reference's
+    own ``instantiate_from_config``; the reference's ``LatentDiffusion.forward`` + ``loss.backward()`` then run the concept
+    encoder's trunk forward / backward through encdiff_enc4_* as well.  State dict keys and order are the reference's; loss and
+    gradient directions against the all-reference model in fp32 on the same GPU."""
+    import encdiff_b200
+    cfg, ref, _ = pair
+    both = ref_shim.reference_latent_diffusion(cfg, unet_target="encdiff_b200.UNetModel", device=cuda_device,
+                                               unet_params=UO.make_params(cfg, seed=1), cond_target="encdiff_b200.Encoder4")
+    assert type(both.cond_stage_model) is encdiff_b200.Encoder4 and type(both.model.diffusion_model) is encdiff_b200.UNetModel
+    assert list(both.state_dict().keys()) == list(ref.state_dict().keys())
+    missing, unexpected = both.load_state_dict(ref.state_dict(), strict=True)
+    assert not missing and not unexpected
+    g = torch.Generator().manual_seed(29)
+    batch = {"image": (torch.rand(16, 64, 64, 3, generator=g) * 2 - 1).to(cuda_device)}
+    out = {}
+    for name, model in (("ref", ref), ("both", both)):
+        model.train()
+        model.zero_grad(set_to_none=True)
+        x, c = model.get_input(batch, "image")
+        torch.manual_seed(78)
+        loss, _ = model(x, c)
+        loss.backward()
+        enc_grads = {k: p.grad.detach().clone() for k, p in model.cond_stage_model.named_parameters() if p.grad is not None}
+        if name == "both":          # ConceptMLP holds the 20 MLPs stacked: back to the reference's per-unit names
+            from encdiff_b200.concept import ConceptMLP
+            for mine_name, ref_name in ConceptMLP._MAP:
+                stacked = enc_grads.pop("net." + mine_name)
+                for i in range(cfg.latent_unit):
+                    gi = stacked[i]
+                    enc_grads[f"net.{i}.{ref_name}"] = gi.reshape(-1, 1) if mine_name == "w1" else gi
+        out[name] = (loss.item(), enc_grads,
+                     {k: p.grad.detach().clone() for k, p in model.model.diffusion_model.named_parameters()})
+
+    def cos(da, db):
+        a = torch.cat([da[k].flatten().double() for k in db])
+        b = torch.cat([db[k].flatten().double() for k in db])
+        return (torch.dot(a, b) / (a.norm() * b.norm())).item()
+    l_ref, l_both = out["ref"][0], out["both"][0]
+    assert set(out["both"][1]) == set(out["ref"][1])
+    c_enc, c_unet = cos(out["both"][1], out["ref"][1]), cos(out["both"][2], out["ref"][2])
+    print(f"both targets swapped: loss {l_both:.6f} vs reference {l_ref:.6f}; gradient cosine concept encoder {c_enc:.5f}, "
+          f"UNet {c_unet:.5f}")
+    assert abs(l_ref - l_both) <= 2e-3 * abs(l_ref)
+    assert c_enc > 0.99 and c_unet > 0.99
+    ref.zero_grad(set_to_none=True)
