@@ -305,6 +305,71 @@ class VQDecoder(nn.Module):
     forward = decode
 
 
+class VQModelInterface(nn.Module):
+    """Drop-in for the reference's frozen first stage as LatentDiffusion builds it (``first_stage_config.target:
+    encdiff_b200.VQModelInterface``; ldm/models/autoencoder.py:20-75 constructor keywords, :308-369 ``encode`` / ``decode``):
+    one module with the reference's sub-module names in the reference's registration order (``encoder``, ``decoder``,
+    ``loss``, ``quantize``, ``quant_conv``, ``post_quant_conv``), so ``state_dict`` keys and their order are those of a
+    reference checkpoint, over the two CUDA paths (``VQEncoder`` / ``VQDecoder`` share these parameter holders).  Inference
+    only, as the first stage is used by ``LatentDiffusion`` (instantiate_first_stage: eval, requires_grad False); training
+    the first stage itself, EMA, colorize, remap and per-batch resizing are the reference's business and raise here."""
+
+    def __init__(self, embed_dim, ddconfig=None, lossconfig=None, n_embed=0, ckpt_path=None, ignore_keys=(), image_key="image",
+                 colorize_nlabels=None, monitor=None, batch_resize_range=None, scheduler_config=None, lr_g_factor=1.0,
+                 remap=None, sane_index_shape=False, use_ema=False, use_disentangled_concat=False, disentangled_dim=0):
+        super().__init__()
+        bad = {"colorize_nlabels": colorize_nlabels is not None, "batch_resize_range": batch_resize_range is not None,
+               "remap": remap is not None, "use_ema": bool(use_ema)}
+        if any(bad.values()):
+            raise NotImplementedError("encdiff_b200.VQModelInterface does not implement: " +
+                                      ", ".join(k for k, v in bad.items() if v))
+        if lossconfig is not None and dict(lossconfig).get("target", "torch.nn.Identity") != "torch.nn.Identity":
+            raise NotImplementedError("encdiff_b200.VQModelInterface is the frozen first stage: lossconfig must be "
+                                      "torch.nn.Identity (as in the EncDiff yamls)")
+        self.embed_dim, self.n_embed, self.image_key = int(embed_dim), int(n_embed), image_key
+        self.use_disentangled_concat, self.disentangled_dim = bool(use_disentangled_concat), int(disentangled_dim)
+        if monitor is not None:
+            self.monitor = monitor
+        enc = VQEncoder(embed_dim=embed_dim, ddconfig=ddconfig)
+        dec = VQDecoder(embed_dim=embed_dim, n_embed=n_embed, ddconfig=ddconfig, use_disentangled_concat=use_disentangled_concat,
+                        disentangled_dim=disentangled_dim)
+        if self.n_embed <= 0:
+            raise ValueError("encdiff_b200.VQModelInterface needs n_embed > 0 (the VQ codebook size)")
+        # the reference's registration order (autoencoder.py:46-56); the two CUDA paths keep working on the same modules
+        self.encoder = enc.encoder
+        self.decoder = dec.decoder
+        self.loss = nn.Identity()
+        self.quantize = dec.quantize
+        self.quant_conv = enc.quant_conv
+        self.post_quant_conv = dec.post_quant_conv
+        object.__setattr__(self, "_enc", enc)            # not registered: their parameters are the ones above
+        object.__setattr__(self, "_dec", dec)
+        if ckpt_path is not None:
+            self.init_from_ckpt(ckpt_path, ignore_keys=ignore_keys)
+
+    def init_from_ckpt(self, path, ignore_keys=()):
+        """VQModel.init_from_ckpt (autoencoder.py:92-104): ``state_dict`` entry of a Lightning checkpoint, keys starting
+        with one of ``ignore_keys`` dropped, non-strict."""
+        sd = torch.load(path, map_location="cpu")["state_dict"]
+        sd = {k: v for k, v in sd.items() if not any(k.startswith(ik) for ik in ignore_keys)}
+        missing, unexpected = self.load_state_dict(sd, strict=False)
+        print(f"Restored from {path} with {len(missing)} missing and {len(unexpected)} unexpected keys")
+
+    def load_state_dict(self, *a, **k):
+        out = super().load_state_dict(*a, **k)
+        self._enc._bound_key = self._dec._bound_key = None          # same storages, new values: re-pack on the next call
+        return out
+
+    def encode(self, x):
+        return self._enc.encode(x)
+
+    def decode(self, h, force_not_quantize=False, disentangled_repr=None):
+        return self._dec.decode(h, force_not_quantize=force_not_quantize, disentangled_repr=disentangled_repr)
+
+    def forward(self, x):
+        raise NotImplementedError("encdiff_b200.VQModelInterface is used through encode() / decode() (frozen first stage)")
+
+
 # ---- reference seam ------------------------------------------------------------------------------------------------
 def _ddconfig_of(fs):
     """ddconfig of a reference VQModel(Interface) instance, read back from its modules (the constructor does not keep it)."""

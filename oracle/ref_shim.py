@@ -189,7 +189,11 @@ REF_UNET_TARGET = "ldm.modules.diffusionmodules.openaimodel_enc.UNetModel"
 REF_COND_TARGET = "ldm.modules.diffusionmodules.openaimodel_enc.Encoder4"
 
 
-def latent_diffusion_config(cfg, unet_target=REF_UNET_TARGET, resolution=None, cond_target=REF_COND_TARGET):
+REF_FIRST_TARGET = "ldm.models.autoencoder.VQModelInterface"
+
+
+def latent_diffusion_config(cfg, unet_target=REF_UNET_TARGET, resolution=None, cond_target=REF_COND_TARGET,
+                            first_target=REF_FIRST_TARGET):
     """The ``model`` node of configs/latent-diffusion/shapes3d-vq-4-16-encdiff.yaml as a plain dict, for an oracle
     ``UNetConfig`` (the yaml's own values for cfg = SHAPES3D).  ``unet_target`` is the drop-in seam (ldm/util.py:78-93):
     ``encdiff_b200.UNetModel`` swaps the denoiser and nothing else.  eval_name is left out (it loads a dataset)."""
@@ -211,18 +215,19 @@ def latent_diffusion_config(cfg, unet_target=REF_UNET_TARGET, resolution=None, c
                             channels=3, cond_stage_trainable=True, concat_mode=False, scale_by_std=True,
                             monitor="train/loss_simple", conditioning_key="crossattn",
                             unet_config=dict(target=unet_target, params=unet),
-                            first_stage_config=dict(target="ldm.models.autoencoder.VQModelInterface", params=first),
+                            first_stage_config=dict(target=first_target, params=first),
                             cond_stage_config=dict(target=cond_target, params=cond)))
 
 
 def reference_latent_diffusion(cfg, unet_target=REF_UNET_TARGET, device="cpu", seed=23, unet_params=None,
-                               cond_target=REF_COND_TARGET):
+                               cond_target=REF_COND_TARGET, first_target=REF_FIRST_TARGET):
     """instantiate_from_config(config.model) as main_val.py:677 does, on ``device``.  With ``unet_params`` the denoiser's
     parameters are loaded through the wrapper's own prefix (``model.diffusion_model.``) and the EMA shadow is re-synced."""
     _install_stubs()
     from ldm.util import instantiate_from_config
     torch.manual_seed(seed)
-    model = instantiate_from_config(latent_diffusion_config(cfg, unet_target, cond_target=cond_target))
+    model = instantiate_from_config(latent_diffusion_config(cfg, unet_target, cond_target=cond_target,
+                                                            first_target=first_target))
     if unet_params is not None:
         sd = {"model.diffusion_model." + k: v for k, v in unet_params.items()}
         missing, unexpected = model.load_state_dict(sd, strict=False)

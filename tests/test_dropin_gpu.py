@@ -216,16 +216,19 @@ def test_ddim_decoded_images_vs_reference(pair, cuda_device):
 
 
 @needs_ref
-def test_both_targets_swapped_training_step_through_the_reference_seam(pair, cuda_device):
-    """``unet_config.target: encdiff_b200.UNetModel`` AND ``cond_stage_config.target: encdiff_b200.Encoder4`` in the reference's
-    own ``instantiate_from_config``; the reference's ``LatentDiffusion.forward`` + ``loss.backward()`` then run the concept
-    encoder's trunk forward / backward through encdiff_enc4_* as well.  State dict keys and order are the reference's; loss and
-    gradient directions against the all-reference model in fp32 on the same GPU."""
+def test_all_targets_swapped_training_step_through_the_reference_seam(pair, cuda_device):
+    """``unet_config.target: encdiff_b200.UNetModel``, ``cond_stage_config.target: encdiff_b200.Encoder4`` AND
+    ``first_stage_config.target: encdiff_b200.VQModelInterface`` in the reference's own ``instantiate_from_config``; the
+    reference's ``LatentDiffusion.get_input`` / ``forward`` / ``loss.backward()`` then run the frozen VQ-f4 encode, the
+    concept encoder's trunk forward / backward and the UNet through this package's kernels.  State dict keys and order are
+    the reference's; loss and gradient directions against the all-reference model in fp32 on the same GPU."""
     import encdiff_b200
     cfg, ref, _ = pair
     both = ref_shim.reference_latent_diffusion(cfg, unet_target="encdiff_b200.UNetModel", device=cuda_device,
-                                               unet_params=UO.make_params(cfg, seed=1), cond_target="encdiff_b200.Encoder4")
+                                               unet_params=UO.make_params(cfg, seed=1), cond_target="encdiff_b200.Encoder4",
+                                               first_target="encdiff_b200.VQModelInterface")
     assert type(both.cond_stage_model) is encdiff_b200.Encoder4 and type(both.model.diffusion_model) is encdiff_b200.UNetModel
+    assert type(both.first_stage_model) is encdiff_b200.VQModelInterface
     assert list(both.state_dict().keys()) == list(ref.state_dict().keys())
     missing, unexpected = both.load_state_dict(ref.state_dict(), strict=True)
     assert not missing and not unexpected
@@ -257,7 +260,7 @@ def test_both_targets_swapped_training_step_through_the_reference_seam(pair, cud
     l_ref, l_both = out["ref"][0], out["both"][0]
     assert set(out["both"][1]) == set(out["ref"][1])
     c_enc, c_unet = cos(out["both"][1], out["ref"][1]), cos(out["both"][2], out["ref"][2])
-    print(f"both targets swapped: loss {l_both:.6f} vs reference {l_ref:.6f}; gradient cosine concept encoder {c_enc:.5f}, "
+    print(f"all three targets swapped: loss {l_both:.6f} vs reference {l_ref:.6f}; gradient cosine concept encoder {c_enc:.5f}, "
           f"UNet {c_unet:.5f}")
     assert abs(l_ref - l_both) <= 2e-3 * abs(l_ref)
     assert c_enc > 0.99 and c_unet > 0.99
