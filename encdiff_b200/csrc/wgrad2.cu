@@ -185,6 +185,7 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
     const bool leader = elect_one();
     {
       constexpr uint32_t idesc = make_idesc(kWN, true, true);
+      constexpr uint32_t idesc_nobias = make_idesc(kWBN, true, true);   // items that do not feed a bias gradient skip the ones block
       const uint32_t ones_addr = smem_u32(ones);
       uint32_t lt = 0, ph = 0;
       int st = 0;
@@ -206,6 +207,7 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
         mbar_wait(&tempty[acc], aph ^ 1);
         tc_fence_after();
         const uint32_t tacc = tmem_base + acc * 128;
+        const uint32_t id = (p.bias0 && w.q_tile == 0 && w.tap == 0) ? idesc : idesc_nobias;
         for (int i = 0; i < nsteps; ++i) {
           mbar_wait(&full_bar[st], ph);
           tc_fence_after();
@@ -215,7 +217,7 @@ __device__ __forceinline__ void wgrad2_body(const Src& src) {
           if (leader) {
 #pragma unroll
             for (int k = 0; k < kPix / 16; ++k)   // 16 pixels (the reduction) = 16 rows of 128 B = 2048 B per MMA step
-              umma_f16(tacc, da + k * (2048 >> 4), db + k * (2048 >> 4), idesc, (i | k) ? 1u : 0u);
+              umma_f16(tacc, da + k * (2048 >> 4), db + k * (2048 >> 4), id, (i | k) ? 1u : 0u);
             umma_commit(&empty_bar[st]);
           }
           if (++st == kWStages) {
