@@ -168,3 +168,29 @@ def ptr(t) -> int:
 def current_stream() -> int:
     import torch
     return torch.cuda.current_stream().cuda_stream
+
+
+class NativeStateMixin:
+    """``copy.deepcopy`` / ``pickle`` for modules that own a library handle.  Parameters, buffers and plain attributes travel
+    as usual; the handle, the ctypes library object, device scratch and captured graphs (``_NATIVE_KEYS`` of the class) are
+    per-instance and are rebuilt on the other side by constructing a fresh instance from the recorded constructor keywords
+    and adopting ITS native members."""
+    _NATIVE_KEYS = ()
+
+    def _record_ctor(self, kw):
+        kw = {k: v for k, v in kw.items() if k not in ("self", "__class__")}
+        object.__setattr__(self, "_ctor_kw", kw)
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        for k in self._NATIVE_KEYS:
+            d.pop(k, None)
+        return d
+
+    def __setstate__(self, d):
+        super().__setstate__(d)
+        fresh = type(self)(**self._ctor_kw)
+        for k in self._NATIVE_KEYS:
+            if k in fresh.__dict__:
+                self.__dict__[k] = fresh.__dict__[k]
+        fresh.__dict__["_h"] = None          # the handle now belongs to this instance

@@ -162,7 +162,7 @@ class _TrunkFn(torch.autograd.Function):
         return (None, None) + tuple(g if need else None for g, need in zip(grads, ctx.need))
 
 
-class Encoder4(nn.Module):
+class Encoder4(_lib.NativeStateMixin, nn.Module):
     """Drop-in for the reference's concept encoder (``cond_stage_config.target: encdiff_b200.Encoder4``; constructor,
     ``forward`` / ``encoding`` / ``warp`` and ``state_dict`` keys of openaimodel_enc.py:991-1041).  The 20 per-unit MLPs run
     as ONE CUDA launch (``ConceptMLP``; the reference loops over ``self.net[i]`` in Python, :1029-1031 and :1039-1040).  The
@@ -172,8 +172,12 @@ class Encoder4(nn.Module):
     the reference's layer indices.  Other configurations raise at construction unless ``torch_trunk=True`` asks for the
     plain PyTorch ``nn.Sequential`` (a front end outside this package's kernels)."""
 
+    _NATIVE_KEYS = ("_h", "_lib", "_bound_key", "_packed", "_ws", "_gflat", "_grad_views", "_fwd_id")
+
     def __init__(self, d, context_dim, latent_unit, bn=True, num_channels=3, torch_trunk=False):
         super().__init__()
+        self._record_ctor(dict(d=d, context_dim=context_dim, latent_unit=latent_unit, bn=bn, num_channels=num_channels,
+                               torch_trunk=torch_trunk))
         self.context_dim, self.latent_unit = context_dim, latent_unit
         self.encoder = nn.Sequential(
             nn.Conv2d(num_channels, d, 4, 2, 1), nn.BatchNorm2d(d), nn.ReLU(inplace=True),

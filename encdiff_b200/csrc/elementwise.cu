@@ -454,17 +454,25 @@ __global__ void __launch_bounds__(256) pack_kernel(const PackEntry* __restrict__
     __syncthreads();
     h16* dst = abf + en.dst_off;
     if (en.kind == 0) {         // dst[row0 + r][col0 + tap * cin_pad + ci]: ci fastest
+      // two channels per lane: 4-byte stores (the kernel was issue-bound on 2-byte stores); every offset below is even
       for (int rr = warp; rr < nr; rr += 8) {
         h16* drow = dst + static_cast<long long>(en.row0 + r0 + rr) * en.dst_ld + en.col0 + ci0;
         for (int tap = 0; tap < en.taps; ++tap)
-          for (int c = lane; c < nci; c += 32) drow[tap * en.cin_pad + c] = f2h(tile[rr][c * en.taps + tap]);
+          for (int c = 2 * lane; c < nci; c += 64) {
+            const float v0 = tile[rr][c * en.taps + tap];
+            if (c + 1 < nci) *reinterpret_cast<h162*>(drow + tap * en.cin_pad + c) = f22h2(v0, tile[rr][(c + 1) * en.taps + tap]);
+            else drow[tap * en.cin_pad + c] = f2h(v0);
+          }
       }
     } else {                    // dst[row0 + ci][col0 + tap * rows_pad + r]: r fastest
       const int pairs = nci * en.taps;
-      for (int pr = warp; pr < pairs; pr += 8) {
+      // a warp writes two (channel, tap) rows per step, 16 lanes x two output rows (one 4-byte store) each; an odd last
+      // row is paired with the operand's zero padding (rows_pad >= r0 + 32)
+      const int half = lane >> 4, l2 = (lane & 15) * 2;
+      for (int pr = 2 * warp + half; pr < pairs; pr += 16) {
         const int c = pr / en.taps, tap = pr - c * en.taps;
         h16* drow = dst + static_cast<long long>(en.row0 + ci0 + c) * en.dst_ld + en.col0 + tap * en.rows_pad + r0;
-        if (lane < nr) drow[lane] = f2h(tile[lane][pr]);
+        if (l2 < nr) *reinterpret_cast<h162*>(drow + l2) = f22h2(tile[l2][pr], l2 + 1 < nr ? tile[l2 + 1][pr] : 0.f);
       }
     }
     return;

@@ -72,12 +72,15 @@ class _Encoder(nn.Module):              # model.py:368-435
         self.conv_out = nn.Conv2d(block_in, 2 * z_channels if double_z else z_channels, 3, 1, 1)
 
 
-class VQEncoder(nn.Module):
+class VQEncoder(_lib.NativeStateMixin, nn.Module):
     """``VQEncoder(embed_dim=3, ddconfig={...})`` — the encode half of the reference's ``VQModelInterface``; ``encode(x)`` /
     ``forward(x)``: images [B, 3, R, R] in [-1, 1] -> latents [B, embed_dim, R/4, R/4] (f4)."""
 
+    _NATIVE_KEYS = ("_h", "_lib", "_bound_key", "_packed", "_ws")
+
     def __init__(self, embed_dim, ddconfig=None, **ddkw):
         super().__init__()
+        self._record_ctor(dict(embed_dim=embed_dim, ddconfig=ddconfig, **ddkw))
         dd = dict(ddconfig or {})
         dd.update(ddkw)
         ch, ch_mult = int(dd["ch"]), tuple(int(v) for v in dd.get("ch_mult", (1, 2, 4, 8)))
@@ -213,15 +216,19 @@ class _Quantize(nn.Module):             # holder of taming's VectorQuantizer2.em
         self.embedding = nn.Embedding(n_embed, embed_dim)
 
 
-class VQDecoder(nn.Module):
+class VQDecoder(_lib.NativeStateMixin, nn.Module):
     """The decode half of the reference's ``VQModelInterface`` (ldm/models/autoencoder.py:328-369):
     ``decode(h, force_not_quantize=False, disentangled_repr=None)`` = nearest-code quantisation (unless told not to), concat of
     the disentangled representation over the latent grid (when built with ``use_disentangled_concat``; zeros if none is
     given), ``post_quant_conv`` and the ``Decoder``.  Parameter names ``decoder.*``, ``quantize.embedding.weight``,
     ``post_quant_conv.*`` as in a reference checkpoint.  Inference only, CUDA only."""
 
+    _NATIVE_KEYS = ("_h", "_lib", "_bound_key", "_packed", "_ws")
+
     def __init__(self, embed_dim, n_embed=0, ddconfig=None, use_disentangled_concat=False, disentangled_dim=0, **ddkw):
         super().__init__()
+        self._record_ctor(dict(embed_dim=embed_dim, n_embed=n_embed, ddconfig=ddconfig,
+                               use_disentangled_concat=use_disentangled_concat, disentangled_dim=disentangled_dim, **ddkw))
         dd = dict(ddconfig or {})
         dd.update(ddkw)
         ch, ch_mult = int(dd["ch"]), tuple(int(v) for v in dd.get("ch_mult", (1, 2, 4, 8)))

@@ -51,16 +51,21 @@ class _UNetFn(torch.autograd.Function):
         return (None, dx, None, dctx) + tuple(g if need else None for g, need in zip(grads, ctx.need_param))
 
 
-class UNetModel(nn.Module):
+class UNetModel(_lib.NativeStateMixin, nn.Module):
     """The full UNet with spatial transformers and timestep embedding; same constructor as the reference
     (openaimodel_enc.py:443-470).  Combinations the CUDA plan does not implement raise instead of silently differing."""
+
+    _NATIVE_KEYS = ("_h", "_lib", "_bound_key", "_packed", "_gflat", "_grad_views", "_ws", "_fwd_id", "_planned", "_auto",
+                    "_prof_on", "_packed_valid")
 
     def __init__(self, image_size, in_channels, model_channels, out_channels, num_res_blocks, attention_resolutions,
                  latent_unit, dropout=0, channel_mult=(1, 2, 4, 8), conv_resample=True, dims=2, num_classes=None,
                  use_checkpoint=False, use_fp16=False, num_heads=-1, num_head_channels=-1, num_heads_upsample=-1,
                  use_scale_shift_norm=False, resblock_updown=False, use_new_attention_order=False,
                  use_spatial_transformer=False, transformer_depth=1, context_dim=None, n_embed=None, legacy=True):
+        kw = dict(locals())
         super().__init__()
+        self._record_ctor(kw)
         if not use_spatial_transformer:
             raise NotImplementedError("encdiff_b200.UNetModel: use_spatial_transformer=False (AttentionBlock) is not supported")
         if context_dim is None:
