@@ -255,18 +255,33 @@ int launch_nhwc_to_nchw(const float* y, float* out, int B, int C, int H, int W, 
   launch_k(nhwc_to_nchw_kernel, grid_for(static_cast<long long>(B) * C * H * W, 256), 256, 0, s, y, out, B, C, H * W);
   return static_cast<int>(cudaGetLastError());
 }
-__global__ void grad_scale_kernel(const float* __restrict__ x, long long n, float* __restrict__ gscale) {
+// gscale[0] = power of two that puts max|x| at 2^-4..2^-3, gscale[1] = its inverse (fp16 build; 1 / 1 in the bf16 build).
+// Many blocks (the single-block version took 33 us for the 0.2 M gradients of a B = 256 step, on the critical path of the
+// backward): block maxima meet in scratch[0] (float bits through atomicMax), the last block to arrive (ticket in scratch[1])
+// publishes the scale.  scratch = gscale + 2, zeroed by the launcher.
+__global__ void __launch_bounds__(256) grad_scale_kernel(const float* __restrict__ x, long long n, float* __restrict__ gscale) {
   pdl_enter();
+  unsigned* scratch = reinterpret_cast<unsigned*>(gscale + 2);
   float m = 0.f;
-  for (long long i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, fabsf(x[i]));
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    m = fmaxf(m, fabsf(x[i]));
   m = warp_max(m);
-  __shared__ float red[32];
+  __shared__ float red[8];
+  __shared__ bool last;
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
   __syncthreads();
-  if (threadIdx.x < 32) {
-    float t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
-    t = warp_max(t);
-    if (threadIdx.x == 0) {
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) t = fmaxf(t, red[w]);
+    if (!(t == t) || t > 3.0e38f) t = __uint_as_float(0x7f800000u);     // NaN / inf anywhere: reported as inf below
+    atomicMax(scratch, __float_as_uint(t));
+    __threadfence();
+    last = atomicAdd(scratch + 1, 1u) == gridDim.x - 1;
+    if (last) {
+      __threadfence();
+      t = __uint_as_float(atomicExch(scratch, 0u));
+      scratch[1] = 0u;
       float sc = 1.f;
 #ifndef EDB_ACT_BF16
       if (t > 0.f && isfinite(t)) {
@@ -281,7 +296,9 @@ __global__ void grad_scale_kernel(const float* __restrict__ x, long long n, floa
   }
 }
 int launch_grad_scale(const float* x, long long n, float* gscale, cudaStream_t s) {
-  launch_k(grad_scale_kernel, 1, 1024, 0, s, x, n, gscale);
+  cudaError_t e = cudaMemsetAsync(gscale + 2, 0, 2 * sizeof(unsigned), s);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  launch_k(grad_scale_kernel, grid_for(n, 256 * 4, 148), 256, 0, s, x, n, gscale);
   return static_cast<int>(cudaGetLastError());
 }
 __global__ void nchw_to_nhwc_h16_kernel(const float* __restrict__ x, h16* __restrict__ out,

@@ -66,7 +66,7 @@ int unet_plan(UNet* u, int B, char* ws, bool training) {
     u->wg_dev = reinterpret_cast<Wgrad2Params*>((reinterpret_cast<uintptr_t>(u->wg_dev) + 63) & ~uintptr_t(63));
     u->wg_prefix_dev = reinterpret_cast<int*>(a.take<char>((UNet::kWgCap + 2) * sizeof(int)));
     u->cp_dev = reinterpret_cast<CrossProjEntry*>(a.take<char>(64 * sizeof(CrossProjEntry)));
-    u->gs = a.take<float>(2);
+    u->gs = a.take<float>(8);      // {scale, 1 / scale} + the two scratch words of grad_scale_kernel
     u->dfilm = a.take<h16>(static_cast<size_t>(B) * u->film_cols);
     u->dyH = a.take<h16>(M0 * 8);
   }
