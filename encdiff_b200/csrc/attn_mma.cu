@@ -192,7 +192,16 @@ __global__ void __launch_bounds__(512) self_attn_bwd_mma_kernel(const h16* __res
                                                                 const h16* __restrict__ dout,
                                                                 const float* __restrict__ lse, h16* __restrict__ dqkv,
                                                                 int N, int heads, int G, float scale) {
-  pdl_enter();
+  pdl_launch_dependents();
+  // q | k | v, O and the log-sum-exp of this sample were saved by the forward; only dO comes from the previous kernel:
+  // the sample's first head group pulls them into L2 before the wait
+  if (threadIdx.x == 0 && blockIdx.x % (heads / G) == 0) {
+    const long long b0 = blockIdx.x / (heads / G);
+    const int Cc = heads * D;
+    l2_prefetch_bulk(qkv + b0 * N * 3 * Cc, static_cast<uint32_t>(N * 3 * Cc * 2));
+    l2_prefetch_bulk(out + b0 * N * Cc, static_cast<uint32_t>(N * Cc * 2));
+  }
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t smraw[];
   const int NP = N + 8;
   h16* Qs = reinterpret_cast<h16*>(smraw);   // [G][N][D]

@@ -288,6 +288,14 @@ __device__ __forceinline__ void pdl_enter() {
   pdl_wait();
 }
 
+// L2 prefetches for the part of a kernel's input that does NOT depend on the previous kernel (weights; in the backward the
+// activations saved by the forward): issued between pdl_launch_dependents() and pdl_wait(), they turn the first dependent
+// round trip after the wait into L2 hits.  `bytes` a multiple of 16, `p` 16-byte aligned.
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void l2_prefetch_line(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 bool pdl_enabled();   // host.cu: false when ENCDIFF_NO_PDL is set
 // Measurement aid (host.cu, tools/exp_ablate.py): true when ENCDIFF_DEBUG_SKIP_KERNELS holds a comma-separated list of
 // substrings and the (mangled) name of `func` contains one of them.  launch_k then enqueues nothing, so the marginal

@@ -97,7 +97,20 @@ __global__ void __launch_bounds__(256) geglu_fwd_kernel(const h16* __restrict__ 
 }
 __global__ void __launch_bounds__(256) geglu_bwd_kernel(const h16* __restrict__ g, const h16* __restrict__ dout,
                                                         h16* __restrict__ dg, unsigned total, int inner, RowSplit rs) {
-  pdl_enter();
+  pdl_launch_dependents();
+  {   // the FF1 pre-activations were saved by the forward: first iteration's lines go to L2 before the wait
+    if ((threadIdx.x & 7) == 0) {
+      unsigned idx0 = blockIdx.x * blockDim.x + threadIdx.x;
+      for (int it = 0; it < 4 && idx0 < total; ++it, idx0 += gridDim.x * blockDim.x) {
+        unsigned row, ch;
+        rs.split(idx0, &row, &ch);
+        const long long o2 = static_cast<long long>(row) * 2 * inner + static_cast<int>(ch) * 8;
+        l2_prefetch_line(g + o2);
+        l2_prefetch_line(g + o2 + inner);
+      }
+    }
+  }
+  pdl_wait();
   for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
     unsigned row, ch;
     rs.split(idx, &row, &ch);

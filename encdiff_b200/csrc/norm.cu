@@ -277,7 +277,14 @@ __device__ __forceinline__ void gather_resampled(const h16* g, int C, int resamp
 }
 
 __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
-  pdl_enter();
+  pdl_launch_dependents();
+  // the sample's forward input was saved by the forward: pull it into L2 while the previous backward kernel drains
+  if (threadIdx.x == 0) {
+    const long long hw = static_cast<long long>(p.H) * p.W;
+    l2_prefetch_bulk(p.x0 + blockIdx.x * hw * p.C0, static_cast<uint32_t>(hw * p.C0 * 2));
+    if (p.x1) l2_prefetch_bulk(p.x1 + blockIdx.x * hw * p.C1, static_cast<uint32_t>(hw * p.C1 * 2));
+  }
+  pdl_wait();
   extern __shared__ float sm[];
   const int b = blockIdx.x;
   const GnThread t = gn_thread(p, b);
@@ -644,7 +651,18 @@ __global__ void __launch_bounds__(256, CPL == 1 ? 3 : 1) ln_bwd_kernel(const h16
                                                      const h16* __restrict__ dres, h16* __restrict__ dx,
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                      const float* __restrict__ gscale, int M, int C, int lpr) {
-  pdl_enter();
+  pdl_launch_dependents();
+  {   // x and its statistics were saved by the forward: the block's first rows go to L2 before the wait
+    // (thread k takes the block's k-th sweep of the persistent row loop)
+    const long long rpb = blockDim.x / lpr;
+    const long long r0 = (static_cast<long long>(blockIdx.x) + static_cast<long long>(threadIdx.x) * gridDim.x) * rpb;
+    if (threadIdx.x < 16 && r0 < M) {
+      const long long nr = min(rpb, M - r0);
+      l2_prefetch_bulk(x + r0 * C, static_cast<uint32_t>(nr * C * 2));
+      l2_prefetch_bulk(stats + r0 * 2, static_cast<uint32_t>(((nr * 8) + 15) & ~15LL));
+    }
+  }
+  pdl_wait();
   extern __shared__ float sm[];  // [rows_per_block][2*C] partial sums of dgamma | dbeta
   const int nchunks = C >> 3;
   const int rows_per_block = blockDim.x / lpr;
