@@ -659,7 +659,7 @@ __global__ void __launch_bounds__(256, CPL == 1 ? 3 : 1) ln_bwd_kernel(const h16
     if (threadIdx.x < 16 && r0 < M) {
       const long long nr = min(rpb, M - r0);
       l2_prefetch_bulk(x + r0 * C, static_cast<uint32_t>(nr * C * 2));
-      l2_prefetch_bulk(stats + r0 * 2, static_cast<uint32_t>(((nr * 8) + 15) & ~15LL));
+      if (nr >= 2) l2_prefetch_bulk(stats + r0 * 2, static_cast<uint32_t>((nr * 8) & ~15LL));   // never past the array
     }
   }
   pdl_wait();
