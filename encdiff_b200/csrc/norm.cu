@@ -85,8 +85,23 @@ __device__ __forceinline__ void gn_channel_reduce(const GnThread& t, bool active
 __device__ __forceinline__ void load8(const h16* p, float* f) { unpack8(*reinterpret_cast<const uint4*>(p), f); }
 __device__ __forceinline__ void store8(h16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
 
+// Parameter vectors (and the FiLM row / saved statistics of sample b) do not depend on the previous kernel and are HBM-cold
+// at every launch: their lines go to L2 before the programmatic-launch wait.
+__device__ __forceinline__ void gn_prefetch_params(const GnParams& p, int b, bool with_stats) {
+  const int C = p.C0 + p.C1;
+  const int i = threadIdx.x * 32;            // one 128-byte line of floats per thread
+  if (i < C) {
+    l2_prefetch_line(p.gamma + i);
+    l2_prefetch_line(p.beta + i);
+  }
+  if (p.film && i < 2 * C) l2_prefetch_line(p.film + static_cast<long long>(b) * p.ldfilm + p.film_off + i);
+  if (with_stats && i < 64) l2_prefetch_line(p.stats + b * 64 + i);
+}
+
 __global__ void __launch_bounds__(512) gn_fwd_kernel(const GnParams p) {
-  pdl_enter();
+  pdl_launch_dependents();
+  gn_prefetch_params(p, blockIdx.x, false);
+  pdl_wait();
   extern __shared__ float sm[];
   const int b = blockIdx.x;
   const GnThread t = gn_thread(p, b);
@@ -284,6 +299,7 @@ __global__ void __launch_bounds__(512) gn_bwd_kernel(const GnParams p) {
     l2_prefetch_bulk(p.x0 + blockIdx.x * hw * p.C0, static_cast<uint32_t>(hw * p.C0 * 2));
     if (p.x1) l2_prefetch_bulk(p.x1 + blockIdx.x * hw * p.C1, static_cast<uint32_t>(hw * p.C1 * 2));
   }
+  gn_prefetch_params(p, blockIdx.x, true);
   pdl_wait();
   extern __shared__ float sm[];
   const int b = blockIdx.x;
@@ -585,7 +601,12 @@ template <int CPL>
 __global__ void __launch_bounds__(256) ln_fwd_kernel(const h16* __restrict__ x, const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, float eps, h16* __restrict__ y,
                                                      float* __restrict__ stats, int M, int C, int lpr) {
-  pdl_enter();
+  pdl_launch_dependents();
+  if (static_cast<int>(threadIdx.x) * 32 < C) {      // gamma / beta: HBM-cold parameters, independent of the previous kernel
+    l2_prefetch_line(gamma + threadIdx.x * 32);
+    l2_prefetch_line(beta + threadIdx.x * 32);
+  }
+  pdl_wait();
   const int nchunks = C >> 3;
   const int rows_per_block = blockDim.x / lpr;
   const int lane_in_row = threadIdx.x % lpr;
@@ -652,6 +673,7 @@ __global__ void __launch_bounds__(256, CPL == 1 ? 3 : 1) ln_bwd_kernel(const h16
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                      const float* __restrict__ gscale, int M, int C, int lpr) {
   pdl_launch_dependents();
+  if (static_cast<int>(threadIdx.x) >= 32 && (static_cast<int>(threadIdx.x) - 32) * 32 < C) l2_prefetch_line(gamma + (threadIdx.x - 32) * 32);
   {   // x and its statistics were saved by the forward: the block's first rows go to L2 before the wait
     // (thread k takes the block's k-th sweep of the persistent row loop)
     const long long rpb = blockDim.x / lpr;
