@@ -136,6 +136,9 @@ struct UNet {
   bool side_on = true;       // ENCDIFF_NO_SIDE_STREAM disables
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_side_done[2] = {nullptr, nullptr};
+  // forward: the timestep-embedding / FiLM chain and the context K|V projection run on the side stream next to the stem and
+  // the first layers; their first consumers wait for ev_side_done[0] (FiLM) / ev_side_done[1] (K|V) while these flags are set
+  bool pend_film = false, pend_kv = false;
   // tensor-map caches
   std::map<std::tuple<const void*, int, int, int, int>, CUtensorMap> act_maps;
   std::map<std::tuple<const void*, long long, long long, int>, CUtensorMap> w_maps;

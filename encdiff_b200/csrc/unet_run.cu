@@ -255,6 +255,17 @@ struct Exec {
     side_layer = side_any = true;
     return u->side;
   }
+  // forward: first consumers of the FiLM table / projected context wait for the side stream's events (unet_forward)
+  void wait_side_results(bool film, bool kv) {
+    if (film && u->pend_film) {
+      cudaStreamWaitEvent(s, u->ev_side_done[0], 0);
+      u->pend_film = false;
+    }
+    if (kv && u->pend_kv) {
+      cudaStreamWaitEvent(s, u->ev_side_done[1], 0);
+      u->pend_kv = false;
+    }
+  }
   void join() {
     if (!side_any) return;
     cudaEventRecord(u->ev_join, u->side);
@@ -577,6 +588,7 @@ static void res_forward(ResLayer& l, Exec& e) {
   const int cin = l.c0 + l.c1;
   e.fail(launch_gn_fwd(gn_res1(l, e), e.B, e.s), "gn1");
   e.gemm({{l.a1, cin, 9}}, l.Hout, l.Wout, l.w1f, 0, l.cout, 1, e.P(l.conv1_b), nullptr, 0, ACT_NONE, false, l.h1, l.cout);
+  e.wait_side_results(true, false);
   e.fail(launch_gn_fwd(gn_res2(l, e), e.B, e.s), "gn2");
   if (l.skipconv) {
     const float* bias = e.u->pf32() + l.bias2_off;
@@ -620,6 +632,7 @@ static void st_forward(StLayer& l, const float* ctx, Exec& e) {
   // attn2 (cross, concept tokens)
   e.fail(launch_ln_fwd(l.t1, e.P(l.ln2_w), e.P(l.ln2_b), 1e-5f, l.l2, l.ls2, M, C, e.s), "ln2");
   e.gemm({{l.l2, C, 1}}, H, W, l.q2f, 0, C, 1, nullptr, nullptr, 0, ACT_NONE, false, l.q2, C);
+  e.wait_side_results(false, true);
   e.fail(launch_cross_attn_fwd(l.q2, ctx, e.P(l.k2_w), e.P(l.v2_w), l.att2, e.B, N, l.heads, l.D, c.latent_unit,
                                c.context_dim, e.s, l.kv),
          "cross_attn");
@@ -640,14 +653,27 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
   Exec e{u, B, s};
   e.mark("(begin)");
   const int mc = c.model_channels, S = c.image_size, E = u->emb_ch;
+  // The embedding chain (7 small launches, ~0.1 ms) does not depend on x: it runs on the side stream while the main stream
+  // does the stem and the first GroupNorm / convolution; FiLM is first needed by the first ResBlock's second GroupNorm, the
+  // projected context by the first SpatialTransformer.
+  const bool forked = e.side_ready();
+  if (forked) {
+    cudaEventRecord(u->ev_fork, s);
+    cudaStreamWaitEvent(u->side, u->ev_fork, 0);
+    e.s = u->side;
+  }
   // timestep embedding MLP + all 28 FiLM projections (openaimodel_enc.py:726-727, 218-224, 264)
-  e.fail(launch_temb(t, u->temb, B, mc, s), "temb");
+  e.fail(launch_temb(t, u->temb, B, mc, e.s), "temb");
   e.gemm({{u->temb, mc, 1}}, 1, 1, u->te0f, 0, E, 1, e.P(u->te0_b), nullptr, 0, ACT_NONE, true, u->z1, E);
-  e.fail(launch_silu_fwd(u->z1, u->a1e, static_cast<long long>(B) * E, s), "silu");
+  e.fail(launch_silu_fwd(u->z1, u->a1e, static_cast<long long>(B) * E, e.s), "silu");
   e.gemm({{u->a1e, E, 1}}, 1, 1, u->te2f, 0, E, 1, e.P(u->te2_b), nullptr, 0, ACT_NONE, true, u->z2, E);
-  e.fail(launch_silu_fwd(u->z2, u->a2e, static_cast<long long>(B) * E, s), "silu");
+  e.fail(launch_silu_fwd(u->z2, u->a2e, static_cast<long long>(B) * E, e.s), "silu");
   e.gemm({{u->a2e, E, 1}}, 1, 1, u->filmf, 0, u->film_cols, 1, u->pf32() + u->film_bias_off, nullptr, 0, ACT_NONE, true,
          u->film, u->film_cols);
+  if (forked) {
+    cudaEventRecord(u->ev_side_done[0], e.s);
+    u->pend_film = true;
+  }
   // to_k / to_v of the context for all cross-attention layers at once (attention.py:174-176; one launch, not 16 x 8)
   EDB_REQUIRE(u->st.size() <= 64, "forward: more than 64 SpatialTransformer layers");
   if (!u->st.empty()) {
@@ -659,8 +685,13 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
       EDB_CHECK_CUDA(cudaStreamSynchronize(s));
       u->ckv_dirty = false;
     }
-    e.fail(launch_cross_kv_project(u->ckv_dev, static_cast<int>(u->st.size()), ctx, B, c.latent_unit, c.context_dim, s),
+    e.fail(launch_cross_kv_project(u->ckv_dev, static_cast<int>(u->st.size()), ctx, B, c.latent_unit, c.context_dim, e.s),
            "cross_attn.kv");
+  }
+  if (forked) {
+    cudaEventRecord(u->ev_side_done[1], e.s);
+    u->pend_kv = true;
+    e.s = s;
   }
   // stem conv as one K=64 GEMM over the im2col'd 3-channel input (q_sample fused when noise != null)
   e.fail(launch_stem_im2col(x, noise, sa, sb, xt, u->cols, B, c.in_channels, S, S, s), "stem");
@@ -674,6 +705,7 @@ int unet_forward(UNet* u, int B, const float* x, const float* noise, const float
   for (size_t i = 1; i < u->in_blocks.size(); ++i) run(u->in_blocks[i]);
   run(u->mid);
   for (auto& blk : u->out_blocks) run(blk);
+  e.wait_side_results(true, true);      // (a network without ResBlocks / transformers: join before the call returns)
   // head: GN -> SiLU -> conv3x3 (openaimodel_enc.py:684-688,748)
   Tn& last = u->tn.back();
   GnParams p;
