@@ -106,3 +106,13 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".inc", ".h")):
                 src = open(os.path.join(dirpath, f), errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), os.path.join(dirpath, f)
+
+
+def test_build_dependency_tracking_sees_inc_files():
+    """The in-tree build recompiles a translation unit when anything it #includes changes (transitively): the launch
+    sequences live in .inc files included by unet_run.cu, and every API file sees the public header."""
+    from encdiff_b200 import _build
+    names = {p.name for p in _build._includes(_build.CSRC / "unet_run.cu")}
+    assert {"unet_bwd.inc", "vq_enc.inc", "enc4.inc", "kernels.cuh", "common.cuh", "unet.cuh"} <= names
+    assert "encdiff_b200.h" in {p.name for p in _build._includes(_build.CSRC / "api_unet.cu")}
+    assert "enc4.inc" not in {p.name for p in _build._includes(_build.CSRC / "gemm2.cu")}
